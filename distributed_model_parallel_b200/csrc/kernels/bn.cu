@@ -1,0 +1,352 @@
+// BatchNorm (train mode) for channels-last activations x[M, C] (M = N*H*W rows, C contiguous).
+// Replaces the 57 nn.BatchNorm2d layers of the reference model
+// (/root/reference/code/distributed_training/model/mobilenetv2.py:18,20,22,28,53,56) and is split so that
+// SyncBatchNorm can insert its cross-GPU combine between the statistics and the finalize step
+// (torch/nn/modules/_functions.py:39-122 is the behaviour being matched):
+//   bn_stats      : per-channel sum / sum-of-squares (double accumulators in global scratch)
+//   bn_finalize   : mean, invstd, running-stat update, fused scale/shift
+//   bn_apply      : y = act(x*scale + shift (+ residual))
+//   bn_bwd_reduce : per-channel sum(dy_m), sum(dy_m * xhat)       (dy_m = dy masked by the fused ReLU)
+//   bn_bwd_dx     : dx = gamma*invstd*(dy_m - s1/n - xhat*s2/n), optional d(residual) = dy_m
+//   bn_bwd_params : dgamma, dbeta
+// The activation tensor is treated as a flat array of 16-byte vectors.  The grid is sized so that
+// (threads * VEC) is a multiple of C, therefore every thread sees the same VEC channels on every
+// iteration and keeps its partial sums / affine coefficients in registers.
+#include "../common.cuh"
+
+namespace {
+
+constexpr int BN_THREADS = 256;
+
+template <typename T>
+struct Vec;
+template <>
+struct Vec<bf16> {
+    static constexpr int N = 8;
+    __device__ static void load(const bf16* p, long long v, float* out) {
+        int4 raw = *(const int4*)(p + v * 8);
+        bf16x8 b = *(bf16x8*)&raw;
+        bf16x8_to_float(b, out);
+    }
+    __device__ static void store(bf16* p, long long v, const float* in) {
+        bf16x8 b = float_to_bf16x8(in);
+        *(int4*)(p + v * 8) = *(int4*)&b;
+    }
+};
+template <>
+struct Vec<float> {
+    static constexpr int N = 4;
+    __device__ static void load(const float* p, long long v, float* out) {
+        float4 r = *(const float4*)(p + v * 4);
+        out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
+    }
+    __device__ static void store(float* p, long long v, const float* in) {
+        *(float4*)(p + v * 4) = make_float4(in[0], in[1], in[2], in[3]);
+    }
+};
+
+// Block-level reduction of per-thread channel partials into global double accumulators.
+// vals[k*VEC + j] is the k-th statistic of channel (ch0 + j).  Threads whose ch0 is equal are combined
+// through shared memory; one double atomic per (block, channel, statistic) reaches global memory.
+template <int VEC, int NSTAT>
+__device__ void block_channel_reduce(const float* vals, int ch0, int C, double* __restrict__ accum, float* sm) {
+    // sm: [BN_THREADS][NSTAT*VEC] floats
+    float* mine = sm + threadIdx.x * (NSTAT * VEC);
+#pragma unroll
+    for (int i = 0; i < NSTAT * VEC; ++i) mine[i] = vals[i];
+    __shared__ int s_ch0[BN_THREADS];
+    s_ch0[threadIdx.x] = ch0;
+    __syncthreads();
+    // groups repeat with period P = C / VEC threads (or all threads distinct if P >= blockDim)
+    const int P = C / VEC;
+    const int ngroups = P < BN_THREADS ? P : BN_THREADS;
+    for (int item = threadIdx.x; item < ngroups * NSTAT * VEC; item += BN_THREADS) {
+        const int g = item / (NSTAT * VEC);  // first thread of this group
+        const int i = item % (NSTAT * VEC);
+        float s = 0.f;
+        for (int t = g; t < BN_THREADS; t += P) s += sm[t * (NSTAT * VEC) + i];
+        const int k = i / VEC, j = i % VEC;
+        atomicAdd(&accum[(long long)k * C + s_ch0[g] + j], (double)s);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_stats_kernel(const T* __restrict__ x, long long nvec, int C, double* __restrict__ accum) {
+    constexpr int VEC = Vec<T>::N;
+    extern __shared__ float sm[];
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    float acc[2 * VEC];
+#pragma unroll
+    for (int i = 0; i < 2 * VEC; ++i) acc[i] = 0.f;
+    for (long long v = tid; v < nvec; v += stride) {
+        float f[VEC];
+        Vec<T>::load(x, v, f);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            acc[j] += f[j];
+            acc[VEC + j] += f[j] * f[j];
+        }
+    }
+    block_channel_reduce<VEC, 2>(acc, ch0, C, accum, sm);
+}
+
+__global__ void bn_finalize_kernel(const double* __restrict__ accum, double count, const float* __restrict__ gamma,
+                                   const float* __restrict__ beta, float* __restrict__ running_mean,
+                                   float* __restrict__ running_var, float momentum, float eps, float* __restrict__ mean,
+                                   float* __restrict__ invstd, float* __restrict__ scale, float* __restrict__ shift,
+                                   int C) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    double m = accum[c] / count;
+    double var = accum[C + c] / count - m * m;
+    if (var < 0.0) var = 0.0;
+    float is = (float)(1.0 / sqrt(var + (double)eps));
+    float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+    mean[c] = (float)m;
+    invstd[c] = is;
+    scale[c] = g * is;
+    shift[c] = b - (float)m * g * is;
+    if (running_mean != nullptr) {
+        double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_kernel(const T* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
+                const T* __restrict__ residual, T* __restrict__ y, long long nvec, int C, int relu) {
+    constexpr int VEC = Vec<T>::N;
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    float sc[VEC], sh[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        sc[j] = scale[ch0 + j];
+        sh[j] = shift[ch0 + j];
+    }
+    for (long long v = tid; v < nvec; v += stride) {
+        float f[VEC];
+        Vec<T>::load(x, v, f);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) f[j] = f[j] * sc[j] + sh[j];
+        if (residual != nullptr) {
+            float r[VEC];
+            Vec<T>::load(residual, v, r);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) f[j] += r[j];
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        Vec<T>::store(y, v, f);
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_reduce_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x,
+                     const float* __restrict__ mean, const float* __restrict__ invstd, long long nvec, int C, int relu,
+                     double* __restrict__ accum) {
+    constexpr int VEC = Vec<T>::N;
+    extern __shared__ float sm[];
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    float mu[VEC], is[VEC], acc[2 * VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        mu[j] = mean[ch0 + j];
+        is[j] = invstd[ch0 + j];
+        acc[j] = 0.f;
+        acc[VEC + j] = 0.f;
+    }
+    for (long long v = tid; v < nvec; v += stride) {
+        float g[VEC], xv[VEC];
+        Vec<T>::load(dy, v, g);
+        Vec<T>::load(x, v, xv);
+        if (relu) {
+            float yv[VEC];
+            Vec<T>::load(y, v, yv);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            acc[j] += g[j];
+            acc[VEC + j] += g[j] * (xv[j] - mu[j]) * is[j];
+        }
+    }
+    block_channel_reduce<VEC, 2>(acc, ch0, C, accum, sm);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_dx_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x,
+                 const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                 const double* __restrict__ accum, double count, T* __restrict__ dx, T* __restrict__ dres,
+                 long long nvec, int C, int relu) {
+    constexpr int VEC = Vec<T>::N;
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    float mu[VEC], is[VEC], a[VEC], b[VEC], c[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        mu[j] = mean[ch0 + j];
+        is[j] = invstd[ch0 + j];
+        a[j] = (gamma ? gamma[ch0 + j] : 1.f) * is[j];
+        b[j] = (float)(accum[ch0 + j] / count);
+        c[j] = (float)(accum[C + ch0 + j] / count);
+    }
+    for (long long v = tid; v < nvec; v += stride) {
+        float g[VEC], xv[VEC];
+        Vec<T>::load(dy, v, g);
+        Vec<T>::load(x, v, xv);
+        if (relu) {
+            float yv[VEC];
+            Vec<T>::load(y, v, yv);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+        }
+        if (dres != nullptr) Vec<T>::store(dres, v, g);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            float xh = (xv[j] - mu[j]) * is[j];
+            g[j] = a[j] * (g[j] - b[j] - xh * c[j]);
+        }
+        Vec<T>::store(dx, v, g);
+    }
+}
+
+__global__ void bn_bwd_params_kernel(const double* __restrict__ accum_local, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta, int C, int accumulate) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float db = (float)accum_local[c], dg = (float)accum_local[C + c];
+    if (dgamma) dgamma[c] = accumulate ? dgamma[c] + dg : dg;
+    if (dbeta) dbeta[c] = accumulate ? dbeta[c] + db : db;
+}
+
+int bn_grid(long long nvec, int C, int vec) {
+    // smallest multiple q of blocks such that (blocks * BN_THREADS * vec) % C == 0
+    long long per_block = (long long)BN_THREADS * vec;
+    long long a = C, b = per_block;
+    while (b) { long long t = a % b; a = b; b = t; }
+    int q = (int)(C / a);
+    long long want = (nvec + BN_THREADS * 4 - 1) / (BN_THREADS * 4);
+    long long cap = (long long)dmp_num_sms() * 4;
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    long long g = ((want + q - 1) / q) * q;
+    return (int)g;
+}
+
+int bn_check(const char* name, long long M, int C, int dtype) {
+    const int vec = dtype == 1 ? 8 : 4;
+    DMP_REQUIRE(M > 0 && C > 0, "%s: empty tensor", name);
+    DMP_REQUIRE(C % vec == 0, "%s: C=%d must be a multiple of %d", name, C, vec);
+    DMP_REQUIRE(C <= 8192, "%s: C=%d too large", name, C);
+    return 0;
+}
+
+}  // namespace
+
+// dtype: 0 = fp32 activations, 1 = bf16 activations.  accum: double[2*C] scratch, zeroed here.
+DMP_API int dmp_bn_stats(const void* x, int dtype, long long M, int C, double* accum, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_stats", M, C, dtype)) return rc;
+    DMP_CHECK_CUDA(cudaMemsetAsync(accum, 0, sizeof(double) * 2 * C, stream));
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    const size_t smem = (size_t)BN_THREADS * 2 * vec * sizeof(float);
+    if (dtype == 1) bn_stats_kernel<bf16><<<grid, BN_THREADS, smem, stream>>>((const bf16*)x, nvec, C, accum);
+    else bn_stats_kernel<float><<<grid, BN_THREADS, smem, stream>>>((const float*)x, nvec, C, accum);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_bn_finalize(const double* accum, double count, const float* gamma, const float* beta, float* running_mean,
+                            float* running_var, float momentum, float eps, float* mean, float* invstd, float* scale,
+                            float* shift, int C, cudaStream_t stream) {
+    bn_finalize_kernel<<<dmp_ceil_div(C, 128), 128, 0, stream>>>(accum, count, gamma, beta, running_mean, running_var,
+                                                                 momentum, eps, mean, invstd, scale, shift, C);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_bn_apply(const void* x, int dtype, const float* scale, const float* shift, const void* residual, void* y,
+                         long long M, int C, int relu, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_apply", M, C, dtype)) return rc;
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    if (dtype == 1)
+        bn_apply_kernel<bf16><<<grid, BN_THREADS, 0, stream>>>((const bf16*)x, scale, shift, (const bf16*)residual,
+                                                               (bf16*)y, nvec, C, relu);
+    else
+        bn_apply_kernel<float><<<grid, BN_THREADS, 0, stream>>>((const float*)x, scale, shift, (const float*)residual,
+                                                                (float*)y, nvec, C, relu);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// accum: double[2*C] scratch, zeroed here; receives {sum dy_m, sum dy_m*xhat}. y may be null when relu == 0.
+DMP_API int dmp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int dtype, const float* mean,
+                              const float* invstd, long long M, int C, int relu, double* accum, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_bwd_reduce", M, C, dtype)) return rc;
+    DMP_REQUIRE(!relu || y != nullptr, "dmp_bn_bwd_reduce: relu mask needs the saved output");
+    DMP_CHECK_CUDA(cudaMemsetAsync(accum, 0, sizeof(double) * 2 * C, stream));
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    const size_t smem = (size_t)BN_THREADS * 2 * vec * sizeof(float);
+    if (dtype == 1)
+        bn_bwd_reduce_kernel<bf16><<<grid, BN_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)y, (const bf16*)x,
+                                                                       mean, invstd, nvec, C, relu, accum);
+    else
+        bn_bwd_reduce_kernel<float><<<grid, BN_THREADS, smem, stream>>>((const float*)dy, (const float*)y,
+                                                                        (const float*)x, mean, invstd, nvec, C, relu,
+                                                                        accum);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// accum_global: the (possibly cross-GPU reduced) sums with their total element count.
+DMP_API int dmp_bn_bwd_dx(const void* dy, const void* y, const void* x, int dtype, const float* mean, const float* invstd,
+                          const float* gamma, const double* accum_global, double count, void* dx, void* dres, long long M,
+                          int C, int relu, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_bwd_dx", M, C, dtype)) return rc;
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    if (dtype == 1)
+        bn_bwd_dx_kernel<bf16><<<grid, BN_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)y, (const bf16*)x, mean,
+                                                                invstd, gamma, accum_global, count, (bf16*)dx, (bf16*)dres,
+                                                                nvec, C, relu);
+    else
+        bn_bwd_dx_kernel<float><<<grid, BN_THREADS, 0, stream>>>((const float*)dy, (const float*)y, (const float*)x, mean,
+                                                                 invstd, gamma, accum_global, count, (float*)dx,
+                                                                 (float*)dres, nvec, C, relu);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* dbeta, int C, int accumulate,
+                              cudaStream_t stream) {
+    bn_bwd_params_kernel<<<dmp_ceil_div(C, 128), 128, 0, stream>>>(accum_local, dgamma, dbeta, C, accumulate);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}

@@ -1,0 +1,239 @@
+// Depthwise 3x3 convolution (groups == channels), channels-last, pad 1, stride 1 or 2: forward, data
+// gradient and weight gradient.  This is the op behind the 17 `groups=planes` convolutions of the
+// reference MobileNetV2 (/root/reference/code/distributed_training/model/mobilenetv2.py:19,33).  It has
+// no reduction over channels, so it is a CUDA-core stencil (not a tensor-core GEMM): each thread owns
+// 8 contiguous channels (one 16-byte vector) of one output pixel, so every global access is a 128-bit
+// coalesced load/store and neighbouring pixels are served from L1/L2.
+#include "../common.cuh"
+
+namespace {
+
+constexpr int DW_THREADS = 256;
+
+template <typename WT>
+__device__ __forceinline__ void load_w72(const WT* __restrict__ w, int ch0, float* out /*[8][9]*/) {
+#pragma unroll
+    for (int i = 0; i < 72; ++i) out[i] = to_f32<WT>(w[ch0 * 9 + i]);
+}
+
+__device__ __forceinline__ void load8(const bf16* p, float* f) {
+    int4 raw = *(const int4*)p;
+    bf16x8_to_float(*(bf16x8*)&raw, f);
+}
+__device__ __forceinline__ void store8(bf16* p, const float* f) {
+    bf16x8 b = float_to_bf16x8(f);
+    *(int4*)p = *(int4*)&b;
+}
+
+// y[n,ho,wo,c] = sum_{kh,kw} x[n, ho*s+kh-1, wo*s+kw-1, c] * w[c,kh,kw]
+template <typename WT>
+__global__ void __launch_bounds__(DW_THREADS)
+dw_fwd_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
+              int Ho, int Wo, int stride) {
+    const int P = C >> 3;
+    const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
+    const long long total = (long long)N * Ho * Wo * P;
+    if (idx >= total) return;
+    const int cv = (int)(idx % P);
+    long long pix = idx / P;
+    const int wo = (int)(pix % Wo); pix /= Wo;
+    const int ho = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    const int ch0 = cv * 8;
+    float wt[72];
+    load_w72<WT>(w, ch0, wt);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+        const int hi = ho * stride + kh - 1;
+        if (hi < 0 || hi >= H) continue;
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+            const int wi = wo * stride + kw - 1;
+            if (wi < 0 || wi >= W) continue;
+            float f[8];
+            load8(x + (((long long)n * H + hi) * W + wi) * C + ch0, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j] * wt[j * 9 + kh * 3 + kw];
+        }
+    }
+    store8(y + (((long long)n * Ho + ho) * Wo + wo) * C + ch0, acc);
+}
+
+// dx[n,h,w,c] = sum_{kh,kw} dy[n,(h+1-kh)/s,(w+1-kw)/s,c] * w[c,kh,kw]   (only exact divisions)
+template <typename WT>
+__global__ void __launch_bounds__(DW_THREADS)
+dw_dgrad_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __restrict__ dx, int N, int H, int W, int C,
+                int Ho, int Wo, int stride) {
+    const int P = C >> 3;
+    const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
+    const long long total = (long long)N * H * W * P;
+    if (idx >= total) return;
+    const int cv = (int)(idx % P);
+    long long pix = idx / P;
+    const int wi = (int)(pix % W); pix /= W;
+    const int hi = (int)(pix % H);
+    const int n = (int)(pix / H);
+    const int ch0 = cv * 8;
+    float wt[72];
+    load_w72<WT>(w, ch0, wt);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+        const int th = hi + 1 - kh;
+        if (th < 0 || (th % stride) != 0) continue;
+        const int ho = th / stride;
+        if (ho >= Ho) continue;
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+            const int tw = wi + 1 - kw;
+            if (tw < 0 || (tw % stride) != 0) continue;
+            const int wo = tw / stride;
+            if (wo >= Wo) continue;
+            float f[8];
+            load8(dy + (((long long)n * Ho + ho) * Wo + wo) * C + ch0, f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += f[j] * wt[j * 9 + kh * 3 + kw];
+        }
+    }
+    store8(dx + (((long long)n * H + hi) * W + wi) * C + ch0, acc);
+}
+
+// dw[c,kh,kw] = sum_{n,ho,wo} dy[n,ho,wo,c] * x[n,ho*s+kh-1,wo*s+kw-1,c]
+// Each thread keeps 8x9 partial sums for its channel vector over a strided subset of output pixels,
+// partials are combined per block in shared memory and flushed with one fp32 atomic per (block, weight).
+__global__ void __launch_bounds__(DW_THREADS)
+dw_wgrad_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, float* __restrict__ dw, int N, int H, int W,
+                int C, int Ho, int Wo, int stride) {
+    extern __shared__ float sm[];  // [groups_in_block][72]
+    const int P = C >> 3;
+    const int groups = P < DW_THREADS ? P : DW_THREADS;
+    for (int i = threadIdx.x; i < groups * 72; i += DW_THREADS) sm[i] = 0.f;
+    __syncthreads();
+    const long long tid = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
+    const long long nthreads = (long long)gridDim.x * DW_THREADS;  // multiple of P (host guarantees)
+    const int cv = (int)(tid % P);
+    const long long pstride = nthreads / P;
+    const long long npix = (long long)N * Ho * Wo;
+    const int ch0 = cv * 8;
+    float acc[72];
+#pragma unroll
+    for (int i = 0; i < 72; ++i) acc[i] = 0.f;
+    for (long long pix = tid / P; pix < npix; pix += pstride) {
+        long long t = pix;
+        const int wo = (int)(t % Wo); t /= Wo;
+        const int ho = (int)(t % Ho);
+        const int n = (int)(t / Ho);
+        float g[8];
+        load8(dy + pix * C + ch0, g);
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int hi = ho * stride + kh - 1;
+            if (hi < 0 || hi >= H) continue;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int wi = wo * stride + kw - 1;
+                if (wi < 0 || wi >= W) continue;
+                float f[8];
+                load8(x + (((long long)n * H + hi) * W + wi) * C + ch0, f);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j * 9 + kh * 3 + kw] += g[j] * f[j];
+            }
+        }
+    }
+    // group slot inside this block: threads with equal cv share a slot
+    const int slot = (P < DW_THREADS) ? cv : threadIdx.x;
+#pragma unroll
+    for (int i = 0; i < 72; ++i) atomicAdd(&sm[slot * 72 + i], acc[i]);
+    __syncthreads();
+    __shared__ int s_cv[DW_THREADS];
+    s_cv[(P < DW_THREADS) ? cv : threadIdx.x] = cv;  // identical value from every writer of a slot
+    __syncthreads();
+    for (int i = threadIdx.x; i < groups * 72; i += DW_THREADS) {
+        const int sl = i / 72, k = i % 72;
+        const float v = sm[i];
+        if (v != 0.f) atomicAdd(&dw[(long long)s_cv[sl] * 72 + k], v);
+    }
+}
+
+}  // namespace
+
+static int dw_check(const char* name, int N, int H, int W, int C, int stride) {
+    DMP_REQUIRE(N > 0 && H > 0 && W > 0 && C > 0, "%s: empty tensor", name);
+    DMP_REQUIRE(C % 8 == 0, "%s: C=%d must be a multiple of 8", name, C);
+    DMP_REQUIRE(stride == 1 || stride == 2, "%s: stride %d unsupported", name, stride);
+    return 0;
+}
+
+// w_dtype: 0 = fp32 weights [C,1,3,3], 1 = bf16.  x,y bf16 NHWC.
+DMP_API int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int stride,
+                              cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_fwd", N, H, W, C, stride)) return rc;
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    const long long total = (long long)N * Ho * Wo * (C / 8);
+    const int grid = dmp_ceil_div(total, DW_THREADS);
+    if (w_dtype == 0)
+        dw_fwd_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo,
+                                                              stride);
+    else
+        dw_fwd_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo,
+                                                             stride);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void* dx, int N, int H, int W, int C,
+                                int stride, cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_dgrad", N, H, W, C, stride)) return rc;
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    const long long total = (long long)N * H * W * (C / 8);
+    const int grid = dmp_ceil_div(total, DW_THREADS);
+    if (w_dtype == 0)
+        dw_dgrad_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, Ho,
+                                                                Wo, stride);
+    else
+        dw_dgrad_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, Ho,
+                                                               Wo, stride);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// dw: fp32 [C,1,3,3]; overwritten unless accumulate != 0.
+DMP_API int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int stride,
+                                int accumulate, cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_wgrad", N, H, W, C, stride)) return rc;
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)C, stream));
+    const int P = C / 8;
+    // grid * threads must be a multiple of P
+    int a = P, b = DW_THREADS;
+    while (b) { int t = a % b; a = b; b = t; }
+    const int q = P / a;
+    const long long npix = (long long)N * Ho * Wo;
+    long long want = (npix * P + (long long)DW_THREADS * 16 - 1) / ((long long)DW_THREADS * 16);  // ~16 pixels per thread
+    const long long cap = (long long)dmp_num_sms() * 4;
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    const int grid = (int)(((want + q - 1) / q) * q);
+    const int groups = P < DW_THREADS ? P : DW_THREADS;
+    const size_t smem = (size_t)groups * 72 * sizeof(float);
+    if (smem > 48 * 1024) {
+        static int configured_mask = 0;
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (!(configured_mask & (1 << dev))) {
+            DMP_CHECK_CUDA(cudaFuncSetAttribute(dw_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
+            configured_mask |= 1 << dev;
+        }
+    }
+    dw_wgrad_kernel<<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo, stride);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}

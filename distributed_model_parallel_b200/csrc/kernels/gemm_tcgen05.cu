@@ -1,0 +1,437 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a.
+//
+//   D[M,N] (+)= A * B   with bf16 operands, fp32 accumulation in tensor memory.
+//
+// Three operand-layout variants cover every GEMM-shaped op of the training step
+// (1x1 convolutions in NHWC are plain GEMMs; BERT linears):
+//   NT  : A[M,K] K-major,            B[N,K] K-major     -> forward   Y  = X * W^T
+//   NN  : A[M,K] K-major,            B[K,N] N-contiguous -> data grad dX = dY * W
+//   TN  : A[K,M] M-contiguous,       B[K,N] N-contiguous -> weight grad dW = dY^T * X (split-K, fp32 atomics)
+//
+// Structure (one 128 x BN output tile per CTA, 192 threads):
+//   warp 0   : TMA producer   (cp.async.bulk.tensor.2d, SWIZZLE_128B, mbarrier complete_tx)
+//   warp 1   : TMEM allocator + single elected thread issuing tcgen05.mma.cta_group::1.kind::f16
+//   warps 2-5: epilogue       (tcgen05.ld 32x32b -> registers -> bias/convert -> global / red.add)
+// A 3-stage smem ring (full/empty mbarriers) decouples TMA from the tensor core; tcgen05.commit releases
+// ring slots and finally signals the epilogue.  K tails rely on TMA out-of-bounds zero fill; M/N tails are
+// masked in the epilogue.
+#include "../common.cuh"
+#include <cuda.h>
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one SWIZZLE_128B atom row
+constexpr int STAGES = 3;
+constexpr int NUM_THREADS = 192;
+constexpr unsigned long long WAIT_TIMEOUT_NS = 4000000000ull;  // 4 s: turn a deadlock into a trap
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    if (mbar_try_wait(bar, parity)) return;
+    unsigned long long t0 = globaltimer_ns();
+    while (!mbar_try_wait(bar, parity)) {
+        if (globaltimer_ns() - t0 > WAIT_TIMEOUT_NS) {
+            printf("dmp gemm_tcgen05: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
+                   blockIdx.z, threadIdx.x);
+            __trap();
+        }
+    }
+}
+__device__ __forceinline__ void fence_barrier_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* tmap, uint64_t* bar, int c0, int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+        ::"r"(smem_u32(smem_dst)),
+        "l"(tmap), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+        : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* tmap) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t ncols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_dst)),
+                 "r"(ncols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+                 : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_16(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout), SWIZZLE_128B, sm_100 version.
+//   [0,14) start>>4  [16,30) LBO>>4  [32,46) SBO>>4  [46,48) version=1  [61,64) layout=2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+
+// Instruction descriptor (cute::UMMA::InstrDescriptor): bf16 x bf16 -> fp32, M=128, N=BN.
+__host__ __device__ constexpr uint32_t make_idesc(int n, int a_mn_major, int b_mn_major) {
+    return (1u << 4)                      // c_format = F32
+           | (1u << 7)                    // a_format = BF16
+           | (1u << 10)                   // b_format = BF16
+           | ((uint32_t)a_mn_major << 15)  // a_major (0 = K, 1 = MN)
+           | ((uint32_t)b_mn_major << 16)  // b_major
+           | ((uint32_t)(n >> 3) << 17)    // n_dim
+           | ((uint32_t)(BM >> 4) << 24);  // m_dim
+}
+
+struct GemmParams {
+    int M, N, K;
+    int k_blocks_per_split;  // split-K: each blockIdx.z handles this many BK blocks
+    void* D;
+    long long ldd;
+    const float* bias;  // per-column (N) fp32 bias, nullable
+    int epi;            // 0: store bf16, 1: store fp32, 2: atomic add fp32
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const GemmParams p) {
+    constexpr int A_BYTES = BM * BK * 2;  // 16 KB
+    constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
+    constexpr int B_BYTES = B_ROWS * BK * 2;
+    constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    uint64_t* full_bar = (uint64_t*)(smem + STAGES * STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint32_t* tmem_ptr_smem = (uint32_t*)(tmem_full_bar + 1);
+
+    const int warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31;
+    const int m0 = blockIdx.x * BM;
+    const int n0 = blockIdx.y * BN;
+    const int total_kb = (p.K + BK - 1) / BK;
+    const int kb_begin = blockIdx.z * p.k_blocks_per_split;
+    int kb_end = kb_begin + p.k_blocks_per_split;
+    if (kb_end > total_kb) kb_end = total_kb;
+    const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        mbar_init(tmem_full_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_ptr_smem, TMEM_COLS);
+    tcgen05_fence_before();
+    __syncthreads();
+    tcgen05_fence_after();
+    const uint32_t tmem_base = *tmem_ptr_smem;
+
+    if (warp == 0) {
+        // ------------------------------------------------------------------ TMA producer
+        if (lane == 0) {
+            for (int i = 0; i < num_kb; ++i) {
+                const int s = i % STAGES;
+                const uint32_t ph = (i / STAGES) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                uint8_t* sa = smem + s * STAGE_BYTES;
+                uint8_t* sb = sa + A_BYTES;
+                const int k0 = (kb_begin + i) * BK;
+                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                if (A_MN) {
+                    // global A^T stored [K, M] (M contiguous): two boxes of {64 m, 64 k}
+                    tma_load_2d(sa, &tmA, &full_bar[s], m0, k0);
+                    tma_load_2d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0);
+                } else {
+                    tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);  // box {64 k, 128 m}
+                }
+                if (B_MN) {
+#pragma unroll
+                    for (int c = 0; c < B_ROWS / 64; ++c)
+                        tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0);
+                } else {
+                    tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);  // box {64 k, BN n}
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------------------------------------------ MMA issuer
+        if (lane == 0) {
+            constexpr uint32_t idesc = make_idesc(BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+            for (int i = 0; i < num_kb; ++i) {
+                const int s = i % STAGES;
+                const uint32_t ph = (i / STAGES) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tcgen05_fence_after();
+                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+                const uint32_t sb = sa + A_BYTES;
+                const int k0 = (kb_begin + i) * BK;
+                int ksteps = (p.K - k0 + 15) / 16;  // skip the zero-filled K tail
+                if (ksteps > BK / 16) ksteps = BK / 16;
+                for (int k = 0; k < ksteps; ++k) {
+                    // K-major: 16 bf16 = 32 B inside the 128 B swizzle row.  MN-major: 16 k-rows = 2 KB.
+                    const uint64_t adesc = A_MN ? make_smem_desc(sa + k * 2048, A_BYTES / 2, 1024)
+                                                : make_smem_desc(sa + k * 32, 16, 1024);
+                    const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024)
+                                                : make_smem_desc(sb + k * 32, 16, 1024);
+                    umma_bf16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+                }
+                umma_commit(&empty_bar[s]);  // frees the smem slot once the MMAs above have read it
+            }
+            umma_commit(tmem_full_bar);  // accumulator complete -> epilogue
+        }
+    } else {
+        // ------------------------------------------------------------------ epilogue (warps 2..5)
+        const int lane_grp = warp & 3;  // TMEM lane quarter this warp may access
+        const int row = m0 + lane_grp * 32 + lane;
+        mbar_wait(tmem_full_bar, 0);
+        tcgen05_fence_after();
+        const uint32_t taddr_row = tmem_base + ((uint32_t)(lane_grp * 32) << 16);
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += 16) {
+            if (n0 + c0 >= p.N) break;  // warp-uniform
+            uint32_t r[16];
+            tmem_ld_16(taddr_row + c0, r);
+            tmem_ld_wait();
+            if (row < p.M) {
+                float v[16];
+#pragma unroll
+                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+                const int n = n0 + c0;
+                if (p.bias != nullptr) {
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (n + j < p.N) v[j] += p.bias[n + j];
+                }
+                if (p.epi == 0) {
+                    bf16* d = (bf16*)p.D + (long long)row * p.ldd + n;
+                    if (n + 16 <= p.N && ((p.ldd & 7) == 0)) {
+                        bf16x8 o0 = float_to_bf16x8(v), o1 = float_to_bf16x8(v + 8);
+                        *(bf16x8*)d = o0;
+                        *(bf16x8*)(d + 8) = o1;
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (n + j < p.N) d[j] = __float2bfloat16_rn(v[j]);
+                    }
+                } else if (p.epi == 1) {
+                    float* d = (float*)p.D + (long long)row * p.ldd + n;
+                    if (n + 16 <= p.N && ((p.ldd & 3) == 0)) {
+#pragma unroll
+                        for (int j = 0; j < 16; j += 4) *(float4*)(d + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j)
+                            if (n + j < p.N) d[j] = v[j];
+                    }
+                } else {
+                    float* d = (float*)p.D + (long long)row * p.ldd + n;
+#pragma unroll
+                    for (int j = 0; j < 16; ++j)
+                        if (n + j < p.N) atomicAdd(d + j, v[j]);
+                }
+            }
+        }
+        tcgen05_fence_before();
+    }
+    __syncthreads();
+    if (warp == 1) {
+        tcgen05_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*PFN_tmapEncodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+PFN_tmapEncodeTiled get_encode_fn() {
+    static PFN_tmapEncodeTiled fn = nullptr;
+    if (fn) return fn;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess || p == nullptr)
+        return nullptr;
+    fn = (PFN_tmapEncodeTiled)p;
+    return fn;
+}
+
+// 2D bf16 tensor map: dim0 (contiguous) = inner, dim1 = outer with row pitch ld (elements).
+int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems, uint32_t box_inner,
+                 uint32_t box_outer) {
+    PFN_tmapEncodeTiled enc = get_encode_fn();
+    DMP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled driver entry point unavailable");
+    DMP_REQUIRE(((uintptr_t)base & 15) == 0, "TMA operand base must be 16-byte aligned");
+    DMP_REQUIRE((ld_elems * 2) % 16 == 0, "TMA operand row pitch must be a multiple of 16 bytes (ld=%llu elements)",
+                (unsigned long long)ld_elems);
+    cuuint64_t gdim[2] = {inner, outer};
+    cuuint64_t gstride[1] = {ld_elems * 2};
+    cuuint32_t box[2] = {box_inner, box_outer};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    DMP_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu ld=%llu)", (int)r,
+                (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld_elems);
+    return 0;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
+    constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
+    constexpr int smem_bytes = STAGES * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ + 128 /*barriers*/;
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+    static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
+    static int configured_dev_mask = 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!configured || !(configured_dev_mask & (1 << dev))) {
+        DMP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+        configured = true;
+        configured_dev_mask |= (1 << dev);
+    }
+    dim3 grid(dmp_ceil_div(p.M, BM), dmp_ceil_div(p.N, BN), splits);
+    kern<<<grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, p);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+template <bool A_MN, bool B_MN>
+int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t s) {
+    switch (bn) {
+        case 32: return launch_gemm<32, A_MN, B_MN>(tmA, tmB, p, splits, s);
+        case 64: return launch_gemm<64, A_MN, B_MN>(tmA, tmB, p, splits, s);
+        default: return launch_gemm<128, A_MN, B_MN>(tmA, tmB, p, splits, s);
+    }
+}
+
+}  // namespace
+
+// layout: 0 = NT (A[M,K], B[N,K]); 1 = NN (A[M,K], B[K,N]); 2 = TN (A[K,M], B[K,N])
+// out_mode: 0 = bf16 store, 1 = fp32 store, 2 = fp32 atomic accumulate (D must be pre-zeroed / hold the addend)
+// splits <= 0 lets the library choose (only out_mode 2 may use more than one split).
+DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd,
+                          int M, int N, int K, const float* bias, int out_mode, int splits, cudaStream_t stream) {
+    DMP_REQUIRE(layout >= 0 && layout <= 2, "dmp_gemm_bf16: bad layout %d", layout);
+    DMP_REQUIRE(M > 0 && N > 0 && K > 0, "dmp_gemm_bf16: empty problem %dx%dx%d", M, N, K);
+    DMP_REQUIRE(out_mode >= 0 && out_mode <= 2, "dmp_gemm_bf16: bad out_mode %d", out_mode);
+    const bool a_mn = (layout == 2);
+    const bool b_mn = (layout != 0);
+    int bn = N > 64 ? 128 : (N > 32 ? 64 : 32);
+    if (b_mn && bn < 64) bn = 64;
+
+    CUtensorMap tmA, tmB;
+    int rc;
+    if (a_mn) rc = make_tmap_2d(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK);
+    else rc = make_tmap_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM);
+    if (rc) return rc;
+    if (b_mn) rc = make_tmap_2d(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK);
+    else rc = make_tmap_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)bn);
+    if (rc) return rc;
+
+    const int total_kb = dmp_ceil_div(K, BK);
+    if (out_mode != 2) splits = 1;
+    if (splits <= 0) {
+        const int tiles = dmp_ceil_div(M, BM) * dmp_ceil_div(N, bn);
+        int want = dmp_ceil_div(2 * dmp_num_sms(), tiles);
+        int max_by_k = total_kb / 4 > 0 ? total_kb / 4 : 1;  // at least 4 k-blocks per split
+        splits = want < max_by_k ? want : max_by_k;
+        if (splits < 1) splits = 1;
+    }
+    if (splits > total_kb) splits = total_kb;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.k_blocks_per_split = dmp_ceil_div(total_kb, splits);
+    splits = dmp_ceil_div(total_kb, p.k_blocks_per_split);  // no empty splits
+    p.D = D; p.ldd = ldd; p.bias = bias; p.epi = out_mode;
+
+    if (!a_mn && !b_mn) return dispatch_bn<false, false>(bn, tmA, tmB, p, splits, stream);
+    if (!a_mn && b_mn) return dispatch_bn<false, true>(bn, tmA, tmB, p, splits, stream);
+    return dispatch_bn<true, true>(bn, tmA, tmB, p, splits, stream);
+}
+
+// ------------------------------------------------------------------ CUDA-core oracle (tests / debugging only)
+__global__ void gemm_ref_kernel(int layout, const bf16* A, long long lda, const bf16* B, long long ldb, float* D,
+                                long long ldd, int M, int N, int K, const float* bias, int accumulate) {
+    int n = blockIdx.x * blockDim.x + threadIdx.x;
+    int m = blockIdx.y * blockDim.y + threadIdx.y;
+    if (m >= M || n >= N) return;
+    float acc = 0.f;
+    for (int k = 0; k < K; ++k) {
+        float a = __bfloat162float(layout == 2 ? A[(long long)k * lda + m] : A[(long long)m * lda + k]);
+        float b = __bfloat162float(layout == 0 ? B[(long long)n * ldb + k] : B[(long long)k * ldb + n]);
+        acc += a * b;
+    }
+    if (bias) acc += bias[n];
+    if (accumulate) D[(long long)m * ldd + n] += acc;
+    else D[(long long)m * ldd + n] = acc;
+}
+DMP_API int dmp_gemm_ref_f32out(int layout, const void* A, long long lda, const void* B, long long ldb, float* D,
+                                long long ldd, int M, int N, int K, const float* bias, int accumulate,
+                                cudaStream_t stream) {
+    dim3 block(32, 8), grid(dmp_ceil_div(N, 32), dmp_ceil_div(M, 8));
+    gemm_ref_kernel<<<grid, block, 0, stream>>>(layout, (const bf16*)A, lda, (const bf16*)B, ldb, D, ldd, M, N, K, bias,
+                                                accumulate);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}

@@ -1,0 +1,322 @@
+// Small ops around the GEMM/BN core: stem convolution (Cin <= 4), global average pool, skinny
+// classifier linear, elementwise add/ReLU.  Reference call sites:
+//   stem conv 3->32    /root/reference/code/distributed_training/model/mobilenetv2.py:52,69
+//   avg_pool2d(4)+view mobilenetv2.py:73-74,155-157 (Reshape1)
+//   Linear(1280,10)    mobilenetv2.py:57,75
+#include "../common.cuh"
+
+namespace {
+
+__device__ __forceinline__ void load8(const bf16* p, float* f) {
+    int4 raw = *(const int4*)p;
+    bf16x8_to_float(*(bf16x8*)&raw, f);
+}
+__device__ __forceinline__ void store8(bf16* p, const float* f) {
+    bf16x8 b = float_to_bf16x8(f);
+    *(int4*)p = *(int4*)&b;
+}
+
+// ----------------------------------------------------------------------------- stem convolution
+// x: layout 0 = fp32 NCHW (raw images), 1 = bf16 NHWC.
+__device__ __forceinline__ float stem_x(const void* x, int layout, int n, int ci, int h, int w, int Cin, int H, int W) {
+    if (layout == 0) return ((const float*)x)[(((long long)n * Cin + ci) * H + h) * W + w];
+    return __bfloat162float(((const bf16*)x)[(((long long)n * H + h) * W + w) * Cin + ci]);
+}
+
+// y[n,ho,wo,co] = sum_{ci,kh,kw} x[n,ci,ho*s+kh-p,wo*s+kw-p] * w[co,ci,kh,kw];  thread = (pixel, 8 couts)
+template <typename WT>
+__global__ void stem_fwd_kernel(const void* __restrict__ x, int layout, const WT* __restrict__ w, bf16* __restrict__ y,
+                                int N, int Cin, int H, int W, int Cout, int KH, int KW, int stride, int pad, int Ho,
+                                int Wo) {
+    extern __shared__ float sw[];  // [T][Cout]
+    const int T = Cin * KH * KW;
+    for (int i = threadIdx.x; i < T * Cout; i += blockDim.x) {
+        const int co = i / T, tap = i % T;
+        sw[tap * Cout + co] = to_f32<WT>(w[i]);
+    }
+    __syncthreads();
+    const int G = Cout >> 3;
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long total = (long long)N * Ho * Wo * G;
+    if (idx >= total) return;
+    const int cg = (int)(idx % G);
+    long long pix = idx / G;
+    const int wo = (int)(pix % Wo); pix /= Wo;
+    const int ho = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int ci = 0; ci < Cin; ++ci)
+        for (int kh = 0; kh < KH; ++kh) {
+            const int hi = ho * stride + kh - pad;
+            if (hi < 0 || hi >= H) continue;
+            for (int kw = 0; kw < KW; ++kw) {
+                const int wi = wo * stride + kw - pad;
+                if (wi < 0 || wi >= W) continue;
+                const float xv = stem_x(x, layout, n, ci, hi, wi, Cin, H, W);
+                const float* wr = sw + ((ci * KH + kh) * KW + kw) * Cout + cg * 8;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[j] += xv * wr[j];
+            }
+        }
+    store8(y + (((long long)n * Ho + ho) * Wo + wo) * Cout + cg * 8, acc);
+}
+
+// dw[co,tap] += sum_pix dy[pix,co] * x[pix (+) tap];  thread = (tap, 8 couts), block strides over pixels
+__global__ void stem_wgrad_kernel(const bf16* __restrict__ dy, const void* __restrict__ x, int layout,
+                                  float* __restrict__ dw, int N, int Cin, int H, int W, int Cout, int KH, int KW,
+                                  int stride, int pad, int Ho, int Wo) {
+    const int T = Cin * KH * KW;
+    const int G = Cout >> 3;
+    const int tap = threadIdx.x / G, cg = threadIdx.x % G;
+    if (tap >= T) return;
+    const int ci = tap / (KH * KW), kh = (tap / KW) % KH, kw = tap % KW;
+    const long long npix = (long long)N * Ho * Wo;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (long long pix = blockIdx.x; pix < npix; pix += gridDim.x) {
+        long long t = pix;
+        const int wo = (int)(t % Wo); t /= Wo;
+        const int ho = (int)(t % Ho);
+        const int n = (int)(t / Ho);
+        const int hi = ho * stride + kh - pad, wi = wo * stride + kw - pad;
+        if (hi < 0 || hi >= H || wi < 0 || wi >= W) continue;
+        const float xv = stem_x(x, layout, n, ci, hi, wi, Cin, H, W);
+        float g[8];
+        load8(dy + pix * Cout + cg * 8, g);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += g[j] * xv;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&dw[(long long)(cg * 8 + j) * T + tap], acc[j]);
+}
+
+// ----------------------------------------------------------------------------- global average pool
+__global__ void avgpool_fwd_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int N, int HW, int C, int relu) {
+    const int P = C >> 3;
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (idx >= (long long)N * P) return;
+    const int cv = (int)(idx % P), n = (int)(idx / P);
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int i = 0; i < HW; ++i) {
+        float f[8];
+        load8(x + ((long long)n * HW + i) * C + cv * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[j] += relu ? fmaxf(f[j], 0.f) : f[j];
+    }
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] *= inv;
+    store8(y + (long long)n * C + cv * 8, acc);
+}
+// dx[n,i,c] = dy[n,c] / HW  (masked by x > 0 when the pool had a fused ReLU in front)
+__global__ void avgpool_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, bf16* __restrict__ dx, int N,
+                                   int HW, int C, int relu) {
+    const int P = C >> 3;
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (idx >= (long long)N * HW * P) return;
+    const int cv = (int)(idx % P);
+    const long long row = idx / P;  // n*HW + i
+    const int n = (int)(row / HW);
+    float g[8];
+    load8(dy + (long long)n * C + cv * 8, g);
+    const float inv = 1.f / (float)HW;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) g[j] *= inv;
+    if (relu) {
+        float f[8];
+        load8(x + row * C + cv * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = f[j] > 0.f ? g[j] : 0.f;
+    }
+    store8(dx + row * C + cv * 8, g);
+}
+
+// ----------------------------------------------------------------------------- skinny linear (N small, e.g. 10 classes)
+// y[b,n] = sum_k x[b,k] * w[n,k] + bias[n];  one warp per (b,n)
+template <typename WT>
+__global__ void linear_small_fwd_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, const float* __restrict__ bias,
+                                        float* __restrict__ y, int B, int N, int K) {
+    const int gw = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (gw >= B * N) return;
+    const int b = gw / N, n = gw % N;
+    float acc = 0.f;
+    for (int k = lane; k < K; k += 32) acc += __bfloat162float(x[(long long)b * K + k]) * to_f32<WT>(w[(long long)n * K + k]);
+    acc = warp_sum(acc);
+    if (lane == 0) y[(long long)b * N + n] = acc + (bias ? bias[n] : 0.f);
+}
+// dx[b,k] = sum_n dy[b,n] * w[n,k]
+template <typename WT>
+__global__ void linear_small_dx_kernel(const float* __restrict__ dy, const WT* __restrict__ w, bf16* __restrict__ dx, int B,
+                                       int N, int K) {
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (idx >= (long long)B * K) return;
+    const int b = (int)(idx / K), k = (int)(idx % K);
+    float acc = 0.f;
+    for (int n = 0; n < N; ++n) acc += dy[(long long)b * N + n] * to_f32<WT>(w[(long long)n * K + k]);
+    dx[idx] = __float2bfloat16_rn(acc);
+}
+// dw[n,k] = sum_b dy[b,n] * x[b,k];  db[n] = sum_b dy[b,n]
+__global__ void linear_small_dw_kernel(const float* __restrict__ dy, const bf16* __restrict__ x, float* __restrict__ dw,
+                                       float* __restrict__ db, int B, int N, int K, int accumulate) {
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (idx < (long long)N * K) {
+        const int n = (int)(idx / K), k = (int)(idx % K);
+        float acc = 0.f;
+        for (int b = 0; b < B; ++b) acc += dy[(long long)b * N + n] * __bfloat162float(x[(long long)b * K + k]);
+        dw[idx] = accumulate ? dw[idx] + acc : acc;
+    } else if (db != nullptr && idx < (long long)N * K + N) {
+        const int n = (int)(idx - (long long)N * K);
+        float acc = 0.f;
+        for (int b = 0; b < B; ++b) acc += dy[(long long)b * N + n];
+        db[n] = accumulate ? db[n] + acc : acc;
+    }
+}
+
+// ----------------------------------------------------------------------------- elementwise
+// y = act(a + b) (b nullable), bf16; relu_bwd: dx = (y > 0) ? dy : 0
+__global__ void add_act_kernel(const bf16* __restrict__ a, const bf16* __restrict__ b, bf16* __restrict__ y, long long nvec,
+                               int relu) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += stride) {
+        float f[8];
+        load8(a + v * 8, f);
+        if (b != nullptr) {
+            float g[8];
+            load8(b + v * 8, g);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] += g[j];
+        }
+        if (relu) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) f[j] = fmaxf(f[j], 0.f);
+        }
+        store8(y + v * 8, f);
+    }
+}
+__global__ void relu_bwd_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, bf16* __restrict__ dx, long long nvec) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += stride) {
+        float g[8], f[8];
+        load8(dy + v * 8, g);
+        load8(y + v * 8, f);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) g[j] = f[j] > 0.f ? g[j] : 0.f;
+        store8(dx + v * 8, g);
+    }
+}
+
+}  // namespace
+
+DMP_API int dmp_stem_conv_fwd(const void* x, int x_layout, const void* w, int w_dtype, void* y, int N, int Cin, int H, int W,
+                              int Cout, int KH, int KW, int stride, int pad, cudaStream_t stream) {
+    DMP_REQUIRE(Cin >= 1 && Cin <= 4 && Cout % 8 == 0, "dmp_stem_conv_fwd: needs Cin<=4 and Cout%%8==0 (Cin=%d Cout=%d)", Cin,
+                Cout);
+    const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+    const int T = Cin * KH * KW;
+    const size_t smem = (size_t)T * Cout * sizeof(float);
+    DMP_REQUIRE(smem <= 48 * 1024, "dmp_stem_conv_fwd: filter too large for shared memory (%zu bytes)", smem);
+    const long long total = (long long)N * Ho * Wo * (Cout / 8);
+    const int grid = dmp_ceil_div(total, 256);
+    if (w_dtype == 0)
+        stem_fwd_kernel<float><<<grid, 256, smem, stream>>>(x, x_layout, (const float*)w, (bf16*)y, N, Cin, H, W, Cout, KH, KW,
+                                                            stride, pad, Ho, Wo);
+    else
+        stem_fwd_kernel<bf16><<<grid, 256, smem, stream>>>(x, x_layout, (const bf16*)w, (bf16*)y, N, Cin, H, W, Cout, KH, KW,
+                                                           stride, pad, Ho, Wo);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, float* dw, int N, int Cin, int H, int W,
+                                int Cout, int KH, int KW, int stride, int pad, int accumulate, cudaStream_t stream) {
+    DMP_REQUIRE(Cin >= 1 && Cin <= 4 && Cout % 8 == 0, "dmp_stem_conv_wgrad: needs Cin<=4 and Cout%%8==0");
+    const int T = Cin * KH * KW;
+    const int threads = T * (Cout / 8);
+    DMP_REQUIRE(threads <= 1024, "dmp_stem_conv_wgrad: taps*Cout/8 = %d exceeds 1024 threads", threads);
+    const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+    if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)T * Cout, stream));
+    const int block = ((threads + 31) / 32) * 32;
+    const int grid = dmp_num_sms() * 2;
+    stem_wgrad_kernel<<<grid, block, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, Cin, H, W, Cout, KH, KW, stride, pad,
+                                                  Ho, Wo);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int relu, cudaStream_t stream) {
+    DMP_REQUIRE(C % 8 == 0, "dmp_avgpool_fwd: C %% 8 != 0");
+    const long long total = (long long)N * (C / 8);
+    avgpool_fwd_kernel<<<dmp_ceil_div(total, 128), 128, 0, stream>>>((const bf16*)x, (bf16*)y, N, HW, C, relu);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+DMP_API int dmp_avgpool_bwd(const void* dy, const void* x, void* dx, int N, int HW, int C, int relu, cudaStream_t stream) {
+    DMP_REQUIRE(C % 8 == 0, "dmp_avgpool_bwd: C %% 8 != 0");
+    const long long total = (long long)N * HW * (C / 8);
+    avgpool_bwd_kernel<<<dmp_ceil_div(total, 256), 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (bf16*)dx, N, HW, C,
+                                                                     relu);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+DMP_API int dmp_linear_small_fwd(const void* x, const void* w, int w_dtype, const float* bias, float* y, int B, int N, int K,
+                                 cudaStream_t stream) {
+    const long long warps = (long long)B * N;
+    const int grid = dmp_ceil_div(warps * 32, 256);
+    if (w_dtype == 0) linear_small_fwd_kernel<float><<<grid, 256, 0, stream>>>((const bf16*)x, (const float*)w, bias, y, B, N, K);
+    else linear_small_fwd_kernel<bf16><<<grid, 256, 0, stream>>>((const bf16*)x, (const bf16*)w, bias, y, B, N, K);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+DMP_API int dmp_linear_small_bwd(const float* dy, const void* x, const void* w, int w_dtype, void* dx, float* dw, float* db,
+                                 int B, int N, int K, int accumulate, cudaStream_t stream) {
+    if (dx != nullptr) {
+        const int grid = dmp_ceil_div((long long)B * K, 256);
+        if (w_dtype == 0) linear_small_dx_kernel<float><<<grid, 256, 0, stream>>>(dy, (const float*)w, (bf16*)dx, B, N, K);
+        else linear_small_dx_kernel<bf16><<<grid, 256, 0, stream>>>(dy, (const bf16*)w, (bf16*)dx, B, N, K);
+        DMP_LAUNCH_CHECK();
+        DMP_COUNT_LAUNCH(1);
+    }
+    if (dw != nullptr) {
+        const int grid = dmp_ceil_div((long long)N * K + N, 256);
+        linear_small_dw_kernel<<<grid, 256, 0, stream>>>(dy, (const bf16*)x, dw, db, B, N, K, accumulate);
+        DMP_LAUNCH_CHECK();
+        DMP_COUNT_LAUNCH(1);
+    }
+    return 0;
+}
+
+DMP_API int dmp_add_act(const void* a, const void* b, void* y, long long n, int relu, cudaStream_t stream) {
+    DMP_REQUIRE(n % 8 == 0, "dmp_add_act: n %% 8 != 0");
+    const long long nvec = n / 8;
+    int grid = dmp_ceil_div(nvec, 256 * 2);
+    const int cap = dmp_num_sms() * 8;
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    add_act_kernel<<<grid, 256, 0, stream>>>((const bf16*)a, (const bf16*)b, (bf16*)y, nvec, relu);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+DMP_API int dmp_relu_bwd(const void* dy, const void* y, void* dx, long long n, cudaStream_t stream) {
+    DMP_REQUIRE(n % 8 == 0, "dmp_relu_bwd: n %% 8 != 0");
+    const long long nvec = n / 8;
+    int grid = dmp_ceil_div(nvec, 256 * 2);
+    const int cap = dmp_num_sms() * 8;
+    if (grid > cap) grid = cap;
+    if (grid < 1) grid = 1;
+    relu_bwd_kernel<<<grid, 256, 0, stream>>>((const bf16*)dy, (const bf16*)y, (bf16*)dx, nvec);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}

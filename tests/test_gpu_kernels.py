@@ -1,0 +1,314 @@
+"""Numerics of every compute kernel against a plain PyTorch fp32 restatement of the same op.
+
+The kernels are called through the C ABI (ctypes) exactly as the Python op layer calls them.
+Tolerances are bf16-level where the kernel reads/writes bf16 and fp32-level otherwise.
+"""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from distributed_model_parallel_b200 import _native
+
+    return _native
+
+
+def _sp():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _close(a, b, rtol, atol, what=""):
+    a = a.float()
+    b = b.float()
+    err = (a - b).abs()
+    tol = atol + rtol * b.abs()
+    bad = (err > tol).sum().item()
+    assert bad == 0, "%s: %d/%d mismatches, max abs err %.4g (ref max %.4g)" % (
+        what, bad, a.numel(), err.max().item(), b.abs().max().item())
+
+
+GEMM_SHAPES = [
+    # (M, N, K)
+    (128, 128, 64), (256, 64, 128), (128, 32, 16), (1000, 96, 24), (4096, 144, 24), (2048, 1280, 320),
+    (333, 200, 72), (8192, 16, 32), (512, 960, 160), (128, 256, 1024),
+]
+
+
+@pytest.mark.parametrize("layout", [0, 1, 2])
+@pytest.mark.parametrize("shape", GEMM_SHAPES)
+def test_gemm_tcgen05(layout, shape):
+    nat = _lib()
+    lib = nat.kernels()
+    M, N, K = shape
+    if layout != 0 and N % 8:
+        pytest.skip("N-contiguous B needs N % 8 == 0")
+    if layout == 2 and M % 8:
+        pytest.skip("M-contiguous A needs M % 8 == 0")
+    if layout != 2 and K % 8:
+        pytest.skip("K-contiguous A needs K % 8 == 0")
+    torch.manual_seed(layout * 100 + M + N + K)
+    dev = "cuda"
+    a = (torch.randn(M, K, device=dev) * 0.5).bfloat16()
+    b = (torch.randn(N, K, device=dev) * 0.5).bfloat16()
+    ref = a.float() @ b.float().t()
+    if layout == 0:
+        A, lda, B, ldb = a, K, b, K
+    elif layout == 1:
+        A, lda, B, ldb = a, K, b.t().contiguous(), N
+    else:
+        A, lda, B, ldb = a.t().contiguous(), M, b.t().contiguous(), N
+    for out_mode in (0, 1, 2):
+        if out_mode == 0:
+            if N % 8:
+                continue
+            D = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+        elif out_mode == 1:
+            D = torch.empty(M, N, device=dev, dtype=torch.float32)
+        else:
+            D = torch.full((M, N), 1.0, device=dev, dtype=torch.float32)
+        nat.check(lib.dmp_gemm_bf16(layout, A.data_ptr(), lda, B.data_ptr(), ldb, D.data_ptr(), N, M, N, K, None,
+                                    out_mode, 0, _sp()), "gemm")
+        torch.cuda.synchronize()
+        want = ref + 1.0 if out_mode == 2 else ref
+        tol = 2e-2 if out_mode == 0 else 2e-3
+        _close(D, want, tol, tol * max(1.0, K ** 0.5 * 0.25), "gemm layout=%d mode=%d %s" % (layout, out_mode, shape))
+
+
+def test_gemm_bias_and_ref():
+    nat = _lib()
+    lib = nat.kernels()
+    M, N, K = 300, 768, 256
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bias = torch.randn(N, device="cuda")
+    D = torch.empty(M, N, device="cuda")
+    nat.check(lib.dmp_gemm_bf16(0, a.data_ptr(), K, b.data_ptr(), K, D.data_ptr(), N, M, N, K, bias.data_ptr(), 1, 0, _sp()))
+    R = torch.empty(M, N, device="cuda")
+    nat.check(lib.dmp_gemm_ref_f32out(0, a.data_ptr(), K, b.data_ptr(), K, R.data_ptr(), N, M, N, K, bias.data_ptr(), 0, _sp()))
+    torch.cuda.synchronize()
+    _close(D, a.float() @ b.float().t() + bias, 2e-3, 2e-2, "gemm+bias")
+    _close(R, a.float() @ b.float().t() + bias, 2e-3, 2e-2, "gemm ref")
+
+
+@pytest.mark.parametrize("gdtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("n", [1, 7, 1024, 2296922])
+def test_sgd_flat(gdtype, n):
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(n)
+    p = torch.randn(n, device="cuda")
+    g = torch.randn(n, device="cuda").to(gdtype)
+    m = torch.randn(n, device="cuda") * 0.1
+    shadow = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    lr, mu, wd, gs = 0.4, 0.9, 1e-4, 0.5
+    hp = torch.tensor([lr, mu, wd, gs], device="cuda")
+    p_ref, m_ref = p.clone(), m.clone()
+    d = g.float() * gs + wd * p_ref
+    m_ref = mu * m_ref + d
+    p_ref = p_ref - lr * m_ref
+    nat.check(lib.dmp_sgd_flat(p.data_ptr(), shadow.data_ptr(), g.data_ptr(), 0 if gdtype == torch.float32 else 1,
+                               m.data_ptr(), n, hp.data_ptr(), 0, 1, _sp()))
+    torch.cuda.synchronize()
+    _close(p, p_ref, 1e-5, 1e-6, "sgd p")
+    _close(m, m_ref, 1e-5, 1e-6, "sgd m")
+    _close(shadow, p_ref.bfloat16(), 1e-2, 1e-3, "sgd shadow")
+    assert g.float().abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,C", [(128, 10), (1000, 10), (37, 1000)])
+def test_xent(dtype, B, C):
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(B + C)
+    x = (torch.randn(B, C, device="cuda") * 3).to(dtype)
+    t = torch.randint(0, C, (B,), device="cuda")
+    dx = torch.empty_like(x)
+    rows = torch.empty(3 * B, device="cuda")
+    out = torch.empty(3, device="cuda")
+    nat.check(lib.dmp_xent_fwd_bwd(x.data_ptr(), t.data_ptr(), dx.data_ptr(), rows.data_ptr(), out.data_ptr(), B, C,
+                                   0 if dtype == torch.float32 else 1, 1.0 / B, _sp()))
+    torch.cuda.synchronize()
+    xr = x.float().clone().requires_grad_()
+    loss = F.cross_entropy(xr, t)
+    loss.backward()
+    tol = 1e-4 if dtype == torch.float32 else 2e-2
+    _close(out[0:1], loss.detach().reshape(1), 1e-4, 1e-5, "xent loss")
+    _close(dx, xr.grad, tol, tol * 0.1, "xent grad")
+    top1 = (x.float().argmax(1) == t).sum().item()
+    assert abs(out[1].item() - top1) <= (0 if dtype == torch.float32 else 2)
+    k = min(5, C)
+    top5 = (x.float().topk(k, 1).indices == t[:, None]).any(1).sum().item()
+    assert abs(out[2].item() - top5) <= (0 if dtype == torch.float32 else 2)
+
+
+@pytest.mark.parametrize("M,C", [(128 * 32 * 32, 32), (128 * 16 * 16, 144), (128 * 4 * 4, 1280), (1000, 24), (4096, 960)])
+@pytest.mark.parametrize("relu,res", [(1, 0), (0, 1), (1, 1), (0, 0)])
+def test_batchnorm_train(M, C, relu, res):
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(M + C)
+    x = (torch.randn(M, C, device="cuda") * 2 + 0.5).bfloat16()
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.1
+    rm = torch.zeros(C, device="cuda")
+    rv = torch.ones(C, device="cuda")
+    resid = torch.randn(M, C, device="cuda").bfloat16() if res else None
+    accum = torch.empty(2 * C, device="cuda", dtype=torch.float64)
+    mean = torch.empty(C, device="cuda"); invstd = torch.empty_like(mean)
+    scale = torch.empty_like(mean); shift = torch.empty_like(mean)
+    y = torch.empty_like(x)
+    eps, mom = 1e-5, 0.1
+    sp = _sp()
+    nat.check(lib.dmp_bn_stats(x.data_ptr(), 1, M, C, accum.data_ptr(), sp))
+    nat.check(lib.dmp_bn_finalize(accum.data_ptr(), float(M), gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(),
+                                  rv.data_ptr(), mom, eps, mean.data_ptr(), invstd.data_ptr(), scale.data_ptr(),
+                                  shift.data_ptr(), C, sp))
+    nat.check(lib.dmp_bn_apply(x.data_ptr(), 1, scale.data_ptr(), shift.data_ptr(), nat.ptr(resid), y.data_ptr(), M, C,
+                               relu, sp))
+    # reference (fp32 math on the same bf16 inputs)
+    xr = x.float().clone().requires_grad_()
+    g_r = gamma.clone().requires_grad_(); b_r = beta.clone().requires_grad_()
+    rm_r = torch.zeros(C, device="cuda"); rv_r = torch.ones(C, device="cuda")
+    rr = resid.float().clone().requires_grad_() if res else None
+    z = F.batch_norm(xr, rm_r, rv_r, g_r, b_r, True, mom, eps)
+    if res:
+        z = z + rr
+    yr = F.relu(z) if relu else z
+    torch.cuda.synchronize()
+    _close(mean, x.float().mean(0), 1e-4, 1e-4, "bn mean")
+    _close(rm, rm_r, 1e-4, 1e-5, "bn running_mean")
+    _close(rv, rv_r, 1e-3, 1e-4, "bn running_var")
+    _close(y, yr, 2e-2, 2e-2, "bn y")
+    # backward
+    dy = torch.randn(M, C, device="cuda").bfloat16()
+    yr.backward(dy.float())
+    acc2 = torch.empty(2 * C, device="cuda", dtype=torch.float64)
+    dx = torch.empty_like(x); dres = torch.empty_like(x) if res else None
+    dgamma = torch.empty(C, device="cuda"); dbeta = torch.empty(C, device="cuda")
+    # the kernel masks with its own bf16 output y (what the op layer saves)
+    nat.check(lib.dmp_bn_bwd_reduce(dy.data_ptr(), y.data_ptr(), x.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(), M, C,
+                                    relu, acc2.data_ptr(), sp))
+    nat.check(lib.dmp_bn_bwd_dx(dy.data_ptr(), y.data_ptr(), x.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(),
+                                gamma.data_ptr(), acc2.data_ptr(), float(M), dx.data_ptr(), nat.ptr(dres), M, C, relu, sp))
+    nat.check(lib.dmp_bn_bwd_params(acc2.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), C, 0, sp))
+    torch.cuda.synchronize()
+    scale_g = max(1.0, (M ** 0.5) * 0.02)
+    _close(dbeta, b_r.grad, 2e-2, 0.05 * scale_g, "bn dbeta")
+    _close(dgamma, g_r.grad, 2e-2, 0.05 * scale_g, "bn dgamma")
+    _close(dx, xr.grad, 3e-2, 3e-2, "bn dx")
+    if res:
+        _close(dres, rr.grad, 1e-2, 1e-2, "bn dres")
+
+
+@pytest.mark.parametrize("N,H,C,stride", [(8, 32, 32, 1), (4, 16, 144, 2), (2, 8, 960, 1), (3, 9, 24, 2), (128, 32, 96, 1)])
+@pytest.mark.parametrize("wdt", [torch.float32, torch.bfloat16])
+def test_dwconv3x3(N, H, C, stride, wdt):
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(N * H + C)
+    W = H
+    x = torch.randn(N, H, W, C, device="cuda").bfloat16()
+    w = (torch.randn(C, 1, 3, 3, device="cuda") * 0.3).to(wdt)
+    Ho = (H + 2 - 3) // stride + 1
+    y = torch.empty(N, Ho, Ho, C, device="cuda", dtype=torch.bfloat16)
+    sp = _sp()
+    wd = 0 if wdt == torch.float32 else 1
+    nat.check(lib.dmp_dwconv3x3_fwd(x.data_ptr(), w.data_ptr(), wd, y.data_ptr(), N, H, W, C, stride, sp))
+    xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_()
+    wr = w.float().clone().requires_grad_()
+    yr = F.conv2d(xr, wr, None, stride, 1, 1, C)
+    torch.cuda.synchronize()
+    _close(y, yr.permute(0, 2, 3, 1), 2e-2, 2e-2, "dw fwd")
+    dy = torch.randn(N, Ho, Ho, C, device="cuda").bfloat16()
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    dx = torch.empty_like(x)
+    dw = torch.empty(C, 1, 3, 3, device="cuda")
+    nat.check(lib.dmp_dwconv3x3_dgrad(dy.data_ptr(), w.data_ptr(), wd, dx.data_ptr(), N, H, W, C, stride, sp))
+    nat.check(lib.dmp_dwconv3x3_wgrad(dy.data_ptr(), x.data_ptr(), dw.data_ptr(), N, H, W, C, stride, 0, sp))
+    torch.cuda.synchronize()
+    _close(dx, xr.grad.permute(0, 2, 3, 1), 2e-2, 2e-2, "dw dgrad")
+    _close(dw, wr.grad, 1e-2, 1e-2 * max(1.0, (N * Ho * Ho) ** 0.5 * 0.1), "dw wgrad")
+
+
+@pytest.mark.parametrize("layout", [0, 1])
+@pytest.mark.parametrize("N,H,Cout,k,stride,pad", [(16, 32, 32, 3, 1, 1), (4, 32, 64, 3, 1, 1), (2, 17, 32, 3, 2, 1)])
+def test_stem_conv(layout, N, H, Cout, k, stride, pad):
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(N + H + Cout)
+    x = torch.randn(N, 3, H, H, device="cuda")
+    if layout == 1:
+        xin = x.permute(0, 2, 3, 1).contiguous().bfloat16()
+        x = xin.float().permute(0, 3, 1, 2).contiguous()
+    else:
+        xin = x
+    w = torch.randn(Cout, 3, k, k, device="cuda") * 0.2
+    Ho = (H + 2 * pad - k) // stride + 1
+    y = torch.empty(N, Ho, Ho, Cout, device="cuda", dtype=torch.bfloat16)
+    sp = _sp()
+    nat.check(lib.dmp_stem_conv_fwd(xin.data_ptr(), layout, w.data_ptr(), 0, y.data_ptr(), N, 3, H, H, Cout, k, k, stride,
+                                    pad, sp))
+    wr = w.clone().requires_grad_()
+    yr = F.conv2d(x, wr, None, stride, pad)
+    torch.cuda.synchronize()
+    _close(y, yr.permute(0, 2, 3, 1), 2e-2, 2e-2, "stem fwd")
+    dy = torch.randn(N, Ho, Ho, Cout, device="cuda").bfloat16()
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    dw = torch.empty_like(w)
+    nat.check(lib.dmp_stem_conv_wgrad(dy.data_ptr(), xin.data_ptr(), layout, dw.data_ptr(), N, 3, H, H, Cout, k, k, stride,
+                                      pad, 0, sp))
+    torch.cuda.synchronize()
+    _close(dw, wr.grad, 1e-2, 1e-2 * max(1.0, (N * Ho * Ho) ** 0.5 * 0.1), "stem wgrad")
+
+
+def test_pool_linear_elementwise():
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(0)
+    sp = _sp()
+    N, HW, Cc = 128, 16, 1280
+    x = torch.randn(N, HW, Cc, device="cuda").bfloat16()
+    for relu in (0, 1):
+        y = torch.empty(N, Cc, device="cuda", dtype=torch.bfloat16)
+        nat.check(lib.dmp_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, HW, Cc, relu, sp))
+        xr = x.float().clone().requires_grad_()
+        yr = (F.relu(xr) if relu else xr).mean(1)
+        dy = torch.randn(N, Cc, device="cuda").bfloat16()
+        yr.backward(dy.float())
+        dx = torch.empty_like(x)
+        nat.check(lib.dmp_avgpool_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), N, HW, Cc, relu, sp))
+        torch.cuda.synchronize()
+        _close(y, yr, 1e-2, 1e-2, "avgpool fwd")
+        _close(dx, xr.grad, 1e-2, 1e-3, "avgpool bwd")
+    # skinny linear
+    B, K, Nc = 128, 1280, 10
+    xl = torch.randn(B, K, device="cuda").bfloat16()
+    w = torch.randn(Nc, K, device="cuda") * 0.05
+    bias = torch.randn(Nc, device="cuda")
+    out = torch.empty(B, Nc, device="cuda")
+    nat.check(lib.dmp_linear_small_fwd(xl.data_ptr(), w.data_ptr(), 0, bias.data_ptr(), out.data_ptr(), B, Nc, K, sp))
+    xr = xl.float().clone().requires_grad_(); wr = w.clone().requires_grad_(); br = bias.clone().requires_grad_()
+    outr = F.linear(xr, wr, br)
+    dyl = torch.randn(B, Nc, device="cuda")
+    outr.backward(dyl)
+    dxl = torch.empty_like(xl); dwl = torch.empty_like(w); dbl = torch.empty_like(bias)
+    nat.check(lib.dmp_linear_small_bwd(dyl.data_ptr(), xl.data_ptr(), w.data_ptr(), 0, dxl.data_ptr(), dwl.data_ptr(),
+                                       dbl.data_ptr(), B, Nc, K, 0, sp))
+    torch.cuda.synchronize()
+    _close(out, outr, 1e-3, 1e-3, "linear fwd")
+    _close(dxl, xr.grad, 1e-2, 1e-2, "linear dx")
+    _close(dwl, wr.grad, 1e-3, 1e-3, "linear dw")
+    _close(dbl, br.grad, 1e-3, 1e-3, "linear db")
+    # elementwise
+    a = torch.randn(4096 * 8, device="cuda").bfloat16(); b = torch.randn_like(a)
+    o = torch.empty_like(a)
+    nat.check(lib.dmp_add_act(a.data_ptr(), b.data_ptr(), o.data_ptr(), a.numel(), 1, sp))
+    g = torch.empty_like(a)
+    nat.check(lib.dmp_relu_bwd(b.data_ptr(), o.data_ptr(), g.data_ptr(), a.numel(), sp))
+    torch.cuda.synchronize()
+    _close(o, F.relu(a.float() + b.float()), 1e-2, 1e-2, "add_act")
+    _close(g, torch.where(o.float() > 0, b.float(), torch.zeros_like(b.float())), 0, 0, "relu_bwd")
