@@ -1,0 +1,556 @@
+"""Functional op layer: every hot op of the training step, with two implementations each.
+
+* CUDA tensors run the hand-written sm_100a kernels of ``libdmp_b200.so`` (tcgen05 GEMM for 1x1
+  convolutions / linears, depthwise stencil, fused BatchNorm statistics + apply(+residual,+ReLU), fused
+  cross-entropy).  Activations are bf16 ``channels_last`` tensors (logical NCHW, physical NHWC), weights are
+  fp32 masters with an optional bf16 shadow maintained by the fused optimizer (``param._dmp_shadow``).
+* CPU tensors run a plain PyTorch restatement -- the oracle of the numerics tests and the path the gloo/CPU
+  plumbing tests exercise.
+
+There is no silent fallback on a GPU: if the native library cannot be loaded the CUDA path raises.
+The ops mirror what the reference model calls (/root/reference/code/distributed_training/model/
+mobilenetv2.py:31-36,68-76: conv -> bn -> relu chains, residual add, avg_pool2d, view, linear) and its
+loss (utils.py:58, data_parallel.py:109).
+"""
+from __future__ import annotations
+
+import threading
+from collections import Counter
+from typing import Optional
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from .. import _native
+
+# which implementation served each op call (reported by bench.py / tests; keys like "conv_pw:tcgen05")
+path_counts: Counter = Counter()
+_tls = threading.local()
+
+# Callbacks fired when an op has accumulated a gradient straight into ``param.grad`` (bypassing
+# autograd's AccumulateGrad).  DistributedDataParallel registers its Reducer here.
+grad_ready_callbacks: list = []
+
+
+def _note(key: str) -> None:
+    path_counts[key] += 1
+
+
+def _sp() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _k():
+    return _native.kernels()
+
+
+def _ck(rc, what):
+    if rc != 0:
+        _native.check(rc, what)
+
+
+def _cl_empty(n, c, h, w, device, dtype=torch.bfloat16):
+    return torch.empty((n, c, h, w), device=device, dtype=dtype, memory_format=torch.channels_last)
+
+
+def _as_cl_bf16(x: torch.Tensor) -> torch.Tensor:
+    if x.dtype != torch.bfloat16:
+        x = x.to(torch.bfloat16)
+    if x.dim() == 4 and not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.contiguous(memory_format=torch.channels_last)
+    return x
+
+
+def weight_bf16(w: torch.Tensor) -> torch.Tensor:
+    """bf16 view of a weight: the optimizer-maintained shadow when present, else a cast."""
+    sh = getattr(w, "_dmp_shadow", None)
+    if sh is not None:
+        return sh
+    return w.detach().to(torch.bfloat16)
+
+
+def _deliver_grad(param: Optional[torch.Tensor], writer):
+    """Produce the gradient of ``param``.
+
+    ``writer(dst, accumulate)`` launches the kernel(s) writing the fp32 gradient into ``dst``.
+    If ``param.grad`` is a pre-allocated fp32 buffer flagged ``_dmp_direct`` (a Reducer bucket view), the
+    kernel accumulates straight into it, grad-ready callbacks fire and ``None`` is returned to autograd;
+    otherwise a fresh tensor is returned and autograd accumulates as usual.
+    """
+    if param is None or not param.requires_grad:
+        return None
+    g = param.grad
+    if g is not None and getattr(param, "_dmp_direct", False) and g.dtype == torch.float32 and g.is_contiguous():
+        writer(g, True)
+        for cb in grad_ready_callbacks:
+            cb(param)
+        return None
+    dst = torch.empty_like(param, dtype=torch.float32, memory_format=torch.contiguous_format)
+    writer(dst, False)
+    return dst if param.dtype == torch.float32 else dst.to(param.dtype)
+
+
+# ----------------------------------------------------------------------------------------------------
+# convolution kinds
+# ----------------------------------------------------------------------------------------------------
+def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
+    kh, kw = conv.kernel_size
+    cin, cout, g = conv.in_channels, conv.out_channels, conv.groups
+    if conv.bias is not None or conv.dilation != (1, 1) or conv.padding_mode != "zeros":
+        return "generic"
+    if (kh, kw) == (1, 1) and g == 1 and conv.padding == (0, 0) and cin % 8 == 0 and cout % 8 == 0:
+        return "pw"
+    if (kh, kw) == (3, 3) and g == cin == cout and conv.padding == (1, 1) and conv.stride in ((1, 1), (2, 2)) \
+            and cin % 8 == 0:
+        return "dw"
+    if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
+            and cin * kh * kw * cout * 4 <= 48 * 1024 and cin * kh * kw * (cout // 8) <= 1024:
+        return "stem"
+    return "generic"
+
+
+def _conv_fwd_cuda(x, w, conv, kind):
+    lib = _k()
+    sp = _sp()
+    N = x.shape[0]
+    if kind == "pw":
+        if conv.stride != (1, 1):
+            x = x[:, :, ::conv.stride[0], ::conv.stride[1]].contiguous(memory_format=torch.channels_last)
+        _, cin, H, W = x.shape
+        cout = conv.out_channels
+        y = _cl_empty(N, cout, H, W, x.device)
+        wb = weight_bf16(w)
+        _ck(lib.dmp_gemm_bf16(0, x.data_ptr(), cin, wb.data_ptr(), cin, y.data_ptr(), cout, N * H * W, cout, cin, None, 0,
+                              1, sp), "conv1x1 fwd gemm")
+        _note("conv_pw:tcgen05")
+        return y, x
+    if kind == "dw":
+        _, C, H, W = x.shape
+        s = conv.stride[0]
+        Ho, Wo = (H + 2 - 3) // s + 1, (W + 2 - 3) // s + 1
+        y = _cl_empty(N, C, Ho, Wo, x.device)
+        wb = weight_bf16(w)
+        _ck(lib.dmp_dwconv3x3_fwd(x.data_ptr(), wb.data_ptr(), 1, y.data_ptr(), N, H, W, C, s, sp), "dwconv fwd")
+        _note("conv_dw:stencil")
+        return y, x
+    if kind == "stem":
+        _, cin, H, W = x.shape
+        kh, kw = conv.kernel_size
+        s, p = conv.stride[0], conv.padding[0]
+        Ho, Wo = (H + 2 * p - kh) // s + 1, (W + 2 * p - kw) // s + 1
+        if x.dtype == torch.float32 and x.is_contiguous():
+            layout = 0
+        else:
+            x = _as_cl_bf16(x)
+            layout = 1
+        y = _cl_empty(N, conv.out_channels, Ho, Wo, x.device)
+        _ck(lib.dmp_stem_conv_fwd(x.data_ptr(), layout, w.data_ptr(), 0, y.data_ptr(), N, cin, H, W, conv.out_channels, kh, kw,
+                                  s, p, sp), "stem conv fwd")
+        _note("conv_stem:direct")
+        return y, x
+    # generic: library convolution (dense 3x3 / 7x7 until the implicit-GEMM kernel covers them)
+    x = _as_cl_bf16(x)
+    y = F.conv2d(x, weight_bf16(w), None, conv.stride, conv.padding, conv.dilation, conv.groups)
+    _note("conv_generic:cudnn")
+    return y.contiguous(memory_format=torch.channels_last), x
+
+
+def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
+    """dy: [N,Cout,Ho,Wo] channels_last bf16. Returns (dx or None, dw_writer)."""
+    lib = _k()
+    sp = _sp()
+    N = x.shape[0]
+    dx = None
+    if kind == "pw":
+        _, cin, H, W = x.shape  # x is the (possibly strided-subsampled) GEMM input saved by forward
+        cout = conv.out_channels
+        M = N * H * W
+        if need_dx:
+            wb = weight_bf16(w)
+            dxs = _cl_empty(N, cin, H, W, x.device)
+            _ck(lib.dmp_gemm_bf16(1, dy.data_ptr(), cout, wb.data_ptr(), cin, dxs.data_ptr(), cin, M, cin, cout, None, 0, 1,
+                                  sp), "conv1x1 dgrad gemm")
+            if conv.stride != (1, 1):
+                s0, s1 = conv.stride
+                dx = torch.zeros((N, cin, (H - 1) * s0 + 1 + (conv._dmp_in_hw[0] - ((H - 1) * s0 + 1)),
+                                  conv._dmp_in_hw[1]), device=x.device, dtype=torch.bfloat16,
+                                 memory_format=torch.channels_last)
+                dx[:, :, ::s0, ::s1] = dxs
+            else:
+                dx = dxs
+
+        def write_dw(dst, accumulate):
+            if not accumulate:
+                dst.zero_()
+            _ck(lib.dmp_gemm_bf16(2, dy.data_ptr(), cout, x.data_ptr(), cin, dst.data_ptr(), cin, cout, cin, M, None, 2, 0,
+                                  sp), "conv1x1 wgrad gemm")
+
+        return dx, write_dw
+    if kind == "dw":
+        _, C, H, W = x.shape
+        s = conv.stride[0]
+        if need_dx:
+            wb = weight_bf16(w)
+            dx = _cl_empty(N, C, H, W, x.device)
+            _ck(lib.dmp_dwconv3x3_dgrad(dy.data_ptr(), wb.data_ptr(), 1, dx.data_ptr(), N, H, W, C, s, sp), "dwconv dgrad")
+
+        def write_dw(dst, accumulate):
+            _ck(lib.dmp_dwconv3x3_wgrad(dy.data_ptr(), x.data_ptr(), dst.data_ptr(), N, H, W, C, s, 1 if accumulate else 0, sp),
+                "dwconv wgrad")
+
+        return dx, write_dw
+    if kind == "stem":
+        _, cin, H, W = x.shape
+        kh, kw = conv.kernel_size
+        s, p = conv.stride[0], conv.padding[0]
+        layout = 0 if x.dtype == torch.float32 else 1
+        if need_dx:
+            raise RuntimeError("stem convolution does not provide an input gradient")
+
+        def write_dw(dst, accumulate):
+            _ck(lib.dmp_stem_conv_wgrad(dy.data_ptr(), x.data_ptr(), layout, dst.data_ptr(), N, cin, H, W, conv.out_channels,
+                                        kh, kw, s, p, 1 if accumulate else 0, sp), "stem conv wgrad")
+
+        return None, write_dw
+    # generic
+    wb = weight_bf16(w)
+    gi, gw, _ = torch.ops.aten.convolution_backward(dy, x, wb, None, conv.stride, conv.padding, conv.dilation, False, (0, 0),
+                                                    conv.groups, (need_dx, True, False))
+
+    def write_dw(dst, accumulate):
+        if accumulate:
+            dst.add_(gw.to(torch.float32))
+        else:
+            dst.copy_(gw)
+
+    return gi, write_dw
+
+
+# ----------------------------------------------------------------------------------------------------
+# fused conv -> (BatchNorm) -> (+residual) -> (ReLU)
+# ----------------------------------------------------------------------------------------------------
+class _ConvBNAct(torch.autograd.Function):
+    """CUDA path. Inputs: x, conv weight, bn weight, bn bias, residual (the last three may be None)."""
+
+    @staticmethod
+    def forward(ctx, x, w, gamma, beta, residual, conv, bn, relu, sync):
+        lib = _k()
+        sp = _sp()
+        kind = conv_kind(conv, x)
+        if kind != "stem":
+            x = _as_cl_bf16(x)
+        if kind == "pw" and conv.stride != (1, 1):
+            conv._dmp_in_hw = (x.shape[2], x.shape[3])
+        y_raw, x_saved = _conv_fwd_cuda(x, w, conv, kind)
+        N, C, Ho, Wo = y_raw.shape
+        M = N * Ho * Wo
+        dev = y_raw.device
+        ctx.conv, ctx.bn, ctx.relu, ctx.kind, ctx.sync = conv, bn, relu, kind, sync
+        ctx.has_res = residual is not None
+        ctx.x_needs_grad = ctx.needs_input_grad[0]
+        if residual is not None:
+            residual = _as_cl_bf16(residual)
+        if bn is None:
+            if relu or residual is not None:
+                out = torch.empty_like(y_raw)
+                _ck(lib.dmp_add_act(y_raw.data_ptr(), _native.ptr(residual), out.data_ptr(), y_raw.numel(), 1 if relu else 0,
+                                    sp), "add_act")
+            else:
+                out = y_raw
+            ctx.save_for_backward(x_saved, w, out if relu else None)
+            ctx.bn_train = False
+            return out
+        training = bn.training or (bn.running_mean is None)
+        scale = torch.empty(C, device=dev, dtype=torch.float32)
+        shift = torch.empty(C, device=dev, dtype=torch.float32)
+        if training:
+            accum = torch.empty(2 * C, device=dev, dtype=torch.float64)
+            mean = torch.empty(C, device=dev, dtype=torch.float32)
+            invstd = torch.empty(C, device=dev, dtype=torch.float32)
+            _ck(lib.dmp_bn_stats(y_raw.data_ptr(), 1, M, C, accum.data_ptr(), sp), "bn stats")
+            count = float(M)
+            if sync is not None:
+                accum, count = sync.reduce_stats(accum, M)
+            mom = bn.momentum
+            if bn.track_running_stats and bn.num_batches_tracked is not None:
+                bn.num_batches_tracked.add_(1)
+                if mom is None:
+                    mom = 1.0 / float(bn.num_batches_tracked)
+            rm = bn.running_mean if bn.track_running_stats else None
+            rv = bn.running_var if bn.track_running_stats else None
+            _ck(lib.dmp_bn_finalize(accum.data_ptr(), count, _native.ptr(gamma), _native.ptr(beta), _native.ptr(rm),
+                                    _native.ptr(rv), float(mom if mom is not None else 0.1), float(bn.eps), mean.data_ptr(),
+                                    invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(), C, sp), "bn finalize")
+            ctx.count = count
+        else:
+            invstd = torch.rsqrt(bn.running_var + bn.eps)
+            mean = bn.running_mean
+            g = gamma if gamma is not None else torch.ones_like(invstd)
+            scale = (g * invstd).float()
+            shift = ((beta if beta is not None else 0) - mean * scale).float()
+            ctx.count = float(M)
+        out = torch.empty_like(y_raw)
+        _ck(lib.dmp_bn_apply(y_raw.data_ptr(), 1, scale.data_ptr(), shift.data_ptr(), _native.ptr(residual), out.data_ptr(), M, C,
+                             1 if relu else 0, sp), "bn apply")
+        _note("bn:fused")
+        ctx.bn_train = training
+        ctx.save_for_backward(x_saved, w, out if relu else None, y_raw, mean, invstd, gamma)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        lib = _k()
+        sp = _sp()
+        conv, bn, relu, kind = ctx.conv, ctx.bn, ctx.relu, ctx.kind
+        dout = _as_cl_bf16(dout)
+        dres = None
+        if bn is None:
+            x, w, out = ctx.saved_tensors
+            if relu:
+                dy = torch.empty_like(dout)
+                _ck(lib.dmp_relu_bwd(dout.data_ptr(), out.data_ptr(), dy.data_ptr(), dout.numel(), sp), "relu bwd")
+            else:
+                dy = dout
+            if ctx.has_res:
+                dres = dy
+            dgamma = dbeta = None
+        else:
+            x, w, out, y_raw, mean, invstd, gamma = ctx.saved_tensors
+            N, C, Ho, Wo = y_raw.shape
+            M = N * Ho * Wo
+            dy = torch.empty_like(y_raw)
+            dres_t = torch.empty_like(y_raw) if ctx.has_res else None
+            if ctx.bn_train:
+                accum = torch.empty(2 * C, device=y_raw.device, dtype=torch.float64)
+                _ck(lib.dmp_bn_bwd_reduce(dout.data_ptr(), _native.ptr(out), y_raw.data_ptr(), 1, mean.data_ptr(),
+                                          invstd.data_ptr(), M, C, 1 if relu else 0, accum.data_ptr(), sp), "bn bwd reduce")
+                accum_g = accum
+                if ctx.sync is not None:
+                    accum_g = ctx.sync.reduce_grads(accum)
+                _ck(lib.dmp_bn_bwd_dx(dout.data_ptr(), _native.ptr(out), y_raw.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(),
+                                      _native.ptr(gamma), accum_g.data_ptr(), ctx.count, dy.data_ptr(), _native.ptr(dres_t), M, C,
+                                      1 if relu else 0, sp), "bn bwd dx")
+
+                def write_dgamma(dst, accumulate):
+                    _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), dst.data_ptr(), None, C, 1 if accumulate else 0, sp), "bn dgamma")
+
+                def write_dbeta(dst, accumulate):
+                    _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), None, dst.data_ptr(), C, 1 if accumulate else 0, sp), "bn dbeta")
+
+                dgamma = _deliver_grad(bn.weight, write_dgamma) if ctx.needs_input_grad[2] else None
+                dbeta = _deliver_grad(bn.bias, write_dbeta) if ctx.needs_input_grad[3] else None
+            else:
+                # eval-mode BN: y = x*scale + shift with constant statistics
+                g = dout.float()
+                if relu:
+                    g = torch.where(out > 0, g, torch.zeros_like(g))
+                if ctx.has_res:
+                    dres_t = g.to(torch.bfloat16)
+                sc = (gamma if gamma is not None else 1.0) * invstd
+                dy = (g * sc.view(1, -1, 1, 1)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+                xh = (y_raw.float() - mean.view(1, -1, 1, 1)) * invstd.view(1, -1, 1, 1)
+                dgamma = (g * xh).sum((0, 2, 3)) if ctx.needs_input_grad[2] else None
+                dbeta = g.sum((0, 2, 3)) if ctx.needs_input_grad[3] else None
+            dres = dres_t
+        dx, write_dw = _conv_bwd_cuda(dy, x, w, conv, kind, ctx.x_needs_grad)
+        dw = _deliver_grad(conv.weight, write_dw) if ctx.needs_input_grad[1] else None
+        return dx, dw, dgamma, dbeta, dres, None, None, None, None
+
+
+def _conv_bn_act_reference(x, conv, bn, relu, residual):
+    y = F.conv2d(x, conv.weight, conv.bias, conv.stride, conv.padding, conv.dilation, conv.groups)
+    if bn is not None:
+        y = bn(y)
+    if residual is not None:
+        y = y + residual
+    return F.relu(y) if relu else y
+
+
+def conv_bn_act(x: torch.Tensor, conv: nn.Conv2d, bn: Optional[nn.Module] = None, relu: bool = False,
+                residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``act(bn(conv(x)) + residual)`` with optional pieces.  ``bn`` may be BatchNorm2d or our SyncBatchNorm."""
+    if not x.is_cuda:
+        _note("conv_bn_act:reference")
+        return _conv_bn_act_reference(x, conv, bn, relu, residual)
+    sync = getattr(bn, "_dmp_sync", None) if bn is not None else None
+    if sync is not None and not (bn.training and sync.world_size > 1):
+        sync = None
+    gamma = bn.weight if bn is not None else None
+    beta = bn.bias if bn is not None else None
+    return _ConvBNAct.apply(x, conv.weight, gamma, beta, residual, conv, bn, relu, sync)
+
+
+# ----------------------------------------------------------------------------------------------------
+# pooling / flatten
+# ----------------------------------------------------------------------------------------------------
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, relu):
+        x = _as_cl_bf16(x)
+        N, C, H, W = x.shape
+        y = torch.empty((N, C), device=x.device, dtype=torch.bfloat16)
+        _ck(_k().dmp_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, H * W, C, 1 if relu else 0, _sp()), "avgpool fwd")
+        ctx.relu = relu
+        ctx.shape = (N, C, H, W)
+        ctx.save_for_backward(x if relu else None)
+        _note("avgpool:kernel")
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        N, C, H, W = ctx.shape
+        dy = dy.to(torch.bfloat16).contiguous()
+        dx = _cl_empty(N, C, H, W, dy.device)
+        _ck(_k().dmp_avgpool_bwd(dy.data_ptr(), _native.ptr(x), dx.data_ptr(), N, H * W, C, 1 if ctx.relu else 0, _sp()),
+            "avgpool bwd")
+        return dx, None
+
+
+def global_avgpool_flatten(x: torch.Tensor, relu: bool = False) -> torch.Tensor:
+    """``flatten(avg_pool2d(relu?(x), full spatial extent))`` -> [N, C] (the reference's Reshape1 / forward tail)."""
+    if x.is_cuda and x.shape[1] % 8 == 0:
+        return _GlobalAvgPool.apply(x, relu)
+    _note("avgpool:reference")
+    if relu:
+        x = F.relu(x)
+    return F.adaptive_avg_pool2d(x, 1).flatten(1)
+
+
+# ----------------------------------------------------------------------------------------------------
+# linear
+# ----------------------------------------------------------------------------------------------------
+class _Linear(torch.autograd.Function):
+    """y = x W^T + b.  Wide layers use the tcgen05 GEMM (bf16 out); skinny classifiers (out_features < 64
+    or not a multiple of 8) use the warp-dot kernel with fp32 logits."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, lin):
+        lib = _k()
+        sp = _sp()
+        shp = x.shape
+        x2 = x.reshape(-1, shp[-1])
+        if x2.dtype != torch.bfloat16 or not x2.is_contiguous():
+            x2 = x2.to(torch.bfloat16).contiguous()
+        B, K = x2.shape
+        Nf = w.shape[0]
+        skinny = Nf < 64 or Nf % 8 != 0 or K % 8 != 0
+        ctx.skinny, ctx.lin, ctx.shape_in = skinny, lin, shp
+        if skinny:
+            y = torch.empty((B, Nf), device=x.device, dtype=torch.float32)
+            _ck(lib.dmp_linear_small_fwd(x2.data_ptr(), w.data_ptr(), 0, _native.ptr(b), y.data_ptr(), B, Nf, K, sp), "linear fwd")
+            _note("linear:skinny")
+        else:
+            y = torch.empty((B, Nf), device=x.device, dtype=torch.bfloat16)
+            wb = weight_bf16(w)
+            bf = b if (b is None or b.dtype == torch.float32) else b.float()
+            _ck(lib.dmp_gemm_bf16(0, x2.data_ptr(), K, wb.data_ptr(), K, y.data_ptr(), Nf, B, Nf, K, _native.ptr(bf), 0, 1, sp),
+                "linear fwd gemm")
+            _note("linear:tcgen05")
+        ctx.save_for_backward(x2, w)
+        return y.reshape(*shp[:-1], Nf)
+
+    @staticmethod
+    def backward(ctx, dy):
+        lib = _k()
+        sp = _sp()
+        x2, w = ctx.saved_tensors
+        lin = ctx.lin
+        B, K = x2.shape
+        Nf = w.shape[0]
+        need_dx = ctx.needs_input_grad[0]
+        dx = None
+        if ctx.skinny:
+            dy2 = dy.reshape(B, Nf).float().contiguous()
+            if need_dx:
+                dx = torch.empty((B, K), device=dy.device, dtype=torch.bfloat16)
+                _ck(lib.dmp_linear_small_bwd(dy2.data_ptr(), x2.data_ptr(), w.data_ptr(), 0, dx.data_ptr(), None, None, B, Nf, K, 0,
+                                             sp), "linear dx")
+
+            def write_dw(dst, accumulate):
+                _ck(lib.dmp_linear_small_bwd(dy2.data_ptr(), x2.data_ptr(), w.data_ptr(), 0, None, dst.data_ptr(), None, B, Nf, K,
+                                             1 if accumulate else 0, sp), "linear dw")
+
+            def write_db(dst, accumulate):
+                if accumulate:
+                    dst.add_(dy2.sum(0))
+                else:
+                    torch.sum(dy2, 0, out=dst)
+        else:
+            dy2 = dy.reshape(B, Nf)
+            if dy2.dtype != torch.bfloat16 or not dy2.is_contiguous():
+                dy2 = dy2.to(torch.bfloat16).contiguous()
+            if need_dx:
+                wb = weight_bf16(w)
+                dx = torch.empty((B, K), device=dy.device, dtype=torch.bfloat16)
+                _ck(lib.dmp_gemm_bf16(1, dy2.data_ptr(), Nf, wb.data_ptr(), K, dx.data_ptr(), K, B, K, Nf, None, 0, 1, sp),
+                    "linear dgrad gemm")
+
+            def write_dw(dst, accumulate):
+                if not accumulate:
+                    dst.zero_()
+                _ck(lib.dmp_gemm_bf16(2, dy2.data_ptr(), Nf, x2.data_ptr(), K, dst.data_ptr(), K, Nf, K, B, None, 2, 0, sp),
+                    "linear wgrad gemm")
+
+            def write_db(dst, accumulate):
+                s = dy2.float().sum(0)
+                if accumulate:
+                    dst.add_(s)
+                else:
+                    dst.copy_(s)
+        dw = _deliver_grad(lin.weight, write_dw) if ctx.needs_input_grad[1] else None
+        db = _deliver_grad(lin.bias, write_db) if (lin.bias is not None and ctx.needs_input_grad[2]) else None
+        if dx is not None:
+            dx = dx.reshape(ctx.shape_in)
+        return dx, dw, db, None
+
+
+def linear(x: torch.Tensor, lin: nn.Linear) -> torch.Tensor:
+    if not x.is_cuda:
+        _note("linear:reference")
+        return F.linear(x, lin.weight, lin.bias)
+    return _Linear.apply(x, lin.weight, lin.bias, lin)
+
+
+# ----------------------------------------------------------------------------------------------------
+# loss
+# ----------------------------------------------------------------------------------------------------
+class _CrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target, stats_out):
+        B, C = logits.shape
+        if logits.dtype not in (torch.float32, torch.bfloat16) or not logits.is_contiguous():
+            logits = logits.float().contiguous()
+        dl = torch.empty_like(logits)
+        rows = torch.empty(3 * B, device=logits.device, dtype=torch.float32)
+        out = stats_out if stats_out is not None else torch.empty(3, device=logits.device, dtype=torch.float32)
+        _ck(_k().dmp_xent_fwd_bwd(logits.data_ptr(), target.data_ptr(), dl.data_ptr(), rows.data_ptr(), out.data_ptr(), B, C,
+                                  0 if logits.dtype == torch.float32 else 1, 1.0 / B, _sp()), "cross entropy")
+        ctx.save_for_backward(dl)
+        _note("xent:fused")
+        return out[0].clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        (dl,) = ctx.saved_tensors
+        return dl * g.to(dl.dtype), None, None
+
+
+def cross_entropy(logits: torch.Tensor, target: torch.Tensor, stats_out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Mean softmax cross-entropy.  On CUDA one fused kernel also produces dlogits and, if ``stats_out`` (3 floats)
+    is given, {loss, top-1 hits, top-5 hits} for the metrics the reference logs."""
+    if not logits.is_cuda:
+        _note("xent:reference")
+        loss = F.cross_entropy(logits.float(), target)
+        if stats_out is not None:
+            with torch.no_grad():
+                k = min(5, logits.shape[1])
+                top = logits.topk(k, 1).indices
+                stats_out[0] = loss.detach()
+                stats_out[1] = (top[:, 0] == target).sum()
+                stats_out[2] = (top == target[:, None]).any(1).sum()
+        return loss
+    if target.dtype != torch.int64:
+        target = target.long()
+    return _CrossEntropy.apply(logits, target.contiguous(), stats_out)
