@@ -1,0 +1,303 @@
+"""DistributedDataParallel: one process per GPU, bucketed gradient Reducer, peer-memory all-reduce.
+
+Same call shape as ``torch.nn.parallel.DistributedDataParallel`` (ctor signature at
+torch/nn/parallel/distributed.py:655-675; semantics inventoried in SURVEY.md section 2.5), which the reference
+only discusses in its README (/root/reference/Readme.md:10-15,145-157) and never calls.  Differences that
+matter on B200:
+
+* the per-bucket collective is our own NVLink peer-memory kernel (one-shot / two-shot by size) launched from
+  the autograd hooks on a high-priority side stream -- ``comm_backend="peer"`` (default on CUDA);
+  ``"torch"`` keeps ``torch.distributed.all_reduce`` (gloo on CPU, NCCL on GPU) as the baseline path;
+* ``fused_sgd=dict(lr=..., momentum=..., weight_decay=...)`` moves the parameters into flat fp32 master
+  arenas and fuses 1/W scaling, bf16 cast and the SGD-momentum update into that same kernel; ``self.optimizer``
+  is then a facade whose ``step()`` only publishes learning-rate changes.
+
+``state_dict()`` keys carry the ``module.`` prefix exactly like torch's wrappers, so checkpoints written by the
+reference's DP script (data_parallel.py:147-151) load unchanged.
+"""
+from __future__ import annotations
+
+import contextlib
+import itertools
+from typing import Any, Callable, List, Optional
+
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+
+from .comm import broadcast_coalesced_group
+from .reducer import DEFAULT_BUCKET_CAP_MB, DEFAULT_FIRST_BUCKET_BYTES, PeerBackend, Reducer, TorchDistBackend
+
+BROADCAST_BUCKET_BYTES = 250 * 1024 * 1024
+
+
+def _find_tensors(obj) -> List[torch.Tensor]:
+    if isinstance(obj, torch.Tensor):
+        return [obj]
+    if isinstance(obj, (list, tuple)):
+        return list(itertools.chain.from_iterable(map(_find_tensors, obj)))
+    if isinstance(obj, dict):
+        return list(itertools.chain.from_iterable(map(_find_tensors, obj.values())))
+    return []
+
+
+def _reachable_params(outputs) -> set:
+    """ids of the leaf tensors whose AccumulateGrad nodes are reachable from ``outputs``."""
+    seen, found, stack = set(), set(), []
+    for t in _find_tensors(outputs):
+        if t.grad_fn is not None:
+            stack.append(t.grad_fn)
+    while stack:
+        fn = stack.pop()
+        if fn in seen:
+            continue
+        seen.add(fn)
+        var = getattr(fn, "variable", None)
+        if var is not None:
+            found.add(id(var))
+        for nxt, _ in fn.next_functions:
+            if nxt is not None:
+                stack.append(nxt)
+        # custom Functions that deliver gradients directly list their parameters explicitly
+        for p in getattr(fn, "_dmp_params", ()):
+            found.add(id(p))
+    return found
+
+
+class FusedSGD:
+    """Optimizer facade for ``DistributedDataParallel(fused_sgd=...)``.
+
+    The update itself happens inside the bucket all-reduce kernel during backward, so ``step()`` has nothing
+    left to do except push hyper-parameter changes (LR schedulers mutate ``param_groups[0]['lr']``) to the
+    device-resident hyper-parameter block the kernel reads.  ``state_dict`` exposes the flat momentum buffers
+    per parameter in the usual ``torch.optim.SGD`` shape."""
+
+    def __init__(self, reducer: Reducer, cfg: dict):
+        self.reducer = reducer
+        self.defaults = dict(lr=cfg.get("lr", 0.1), momentum=cfg.get("momentum", 0.0), weight_decay=cfg.get("weight_decay", 0.0),
+                             nesterov=bool(cfg.get("nesterov", False)), dampening=0.0)
+        self.param_groups = [dict(self.defaults, params=list(reducer.params), initial_lr=self.defaults["lr"])]
+        self._pushed = None
+        self._host = torch.empty(4, dtype=torch.float32).pin_memory() if torch.cuda.is_available() else torch.empty(4)
+        self.push_hyperparameters()
+
+    def push_hyperparameters(self):
+        g = self.param_groups[0]
+        cur = (float(g["lr"]), float(g["momentum"]), float(g["weight_decay"]))
+        if cur != self._pushed:
+            self._host[0], self._host[1], self._host[2], self._host[3] = cur[0], cur[1], cur[2], 1.0
+            self.reducer.hp.copy_(self._host, non_blocking=True)
+            self._pushed = cur
+
+    def step(self, closure=None):
+        loss = closure() if closure is not None else None
+        self.push_hyperparameters()
+        return loss
+
+    def zero_grad(self, set_to_none: bool = False):
+        pass  # the fused kernel leaves the gradient buckets zeroed
+
+    def state_dict(self):
+        state = {}
+        for bk in self.reducer.buckets:
+            for i, p, off in zip(bk.param_indices, bk.params, bk.offsets):
+                state[i] = {"momentum_buffer": bk.fused.momentum[off: off + p.numel()].view_as(p).clone()}
+        groups = [{k: v for k, v in self.param_groups[0].items() if k != "params"}]
+        groups[0]["params"] = list(range(len(self.reducer.params)))
+        return {"state": state, "param_groups": groups}
+
+    def load_state_dict(self, sd):
+        for bk in self.reducer.buckets:
+            for i, p, off in zip(bk.param_indices, bk.params, bk.offsets):
+                st = sd["state"].get(i) or sd["state"].get(str(i))
+                if st is not None and st.get("momentum_buffer") is not None:
+                    bk.fused.momentum[off: off + p.numel()].view_as(p).copy_(st["momentum_buffer"])
+        for k, v in sd["param_groups"][0].items():
+            if k != "params":
+                self.param_groups[0][k] = v
+        self.push_hyperparameters()
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids=None, output_device=None, dim: int = 0, broadcast_buffers: bool = True,
+                 init_sync: bool = True, process_group=None, bucket_cap_mb: Optional[float] = None,
+                 find_unused_parameters: bool = False, check_reduction: bool = False, gradient_as_bucket_view: bool = False,
+                 static_graph: bool = False, *, comm_backend: Optional[str] = None, fused_sgd: Optional[dict] = None,
+                 first_bucket_bytes: int = DEFAULT_FIRST_BUCKET_BYTES):
+        super().__init__()
+        if not (dist.is_available() and dist.is_initialized()) and process_group is None:
+            if comm_backend != "peer" or (torch.cuda.is_available() and False):
+                pass
+        params_all = [p for p in module.parameters()]
+        if not any(p.requires_grad for p in params_all):
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any parameter that "
+                               "requires a gradient.")
+        if device_ids is not None and len(device_ids) > 1:
+            raise ValueError("device_ids can only be None or contain a single element.")
+        dev_types = {p.device.type for p in params_all}
+        if len(dev_types) != 1:
+            raise ValueError("DistributedDataParallel's input module must be on the same type of devices, but input "
+                             "module parameters locate in %s." % dev_types)
+        self.device_type = next(iter(dev_types))
+        devices = {p.device for p in params_all}
+        self.is_multi_device_module = len(devices) > 1
+        if self.is_multi_device_module and device_ids is not None:
+            raise ValueError("DistributedDataParallel device_ids and output_device arguments only work with "
+                             "single-device modules.")
+        self.device_ids = None if device_ids is None or self.device_type == "cpu" else [torch.device("cuda", d).index
+                                                                                         if not isinstance(d, torch.device)
+                                                                                         else d.index for d in device_ids]
+        self.output_device = output_device if output_device is not None else (self.device_ids[0] if self.device_ids else None)
+        self.module = module
+        self.dim = dim
+        self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = find_unused_parameters
+        self.static_graph = static_graph
+        self.gradient_as_bucket_view = gradient_as_bucket_view
+        self.require_backward_grad_sync = True
+        self.require_forward_param_sync = True
+        self.process_group = process_group if process_group is not None else (dist.group.WORLD if dist.is_initialized() else None)
+        self.world_size = dist.get_world_size(self.process_group) if self.process_group is not None else 1
+        self.rank = dist.get_rank(self.process_group) if self.process_group is not None else 0
+        self.bucket_bytes_cap = int((bucket_cap_mb if bucket_cap_mb is not None else DEFAULT_BUCKET_CAP_MB) * 1024 * 1024)
+        self.parameters_to_ignore = set(getattr(module, "_ddp_params_and_buffers_to_ignore", []))
+
+        # ---- parameter / buffer lists (torch: _build_params_for_reducer)
+        names, params, seen = [], [], set()
+        for mname, m in module.named_modules():
+            for pname, p in m.named_parameters(recurse=False):
+                full = "%s.%s" % (mname, pname) if mname else pname
+                if not p.requires_grad or full in self.parameters_to_ignore or id(p) in seen:
+                    continue
+                seen.add(id(p))
+                names.append(full)
+                params.append(p)
+        self._param_names, self._params = names, params
+        self.modules_buffers = [b for n, b in module.named_buffers() if n not in self.parameters_to_ignore]
+
+        # ---- init sync: verify shapes, then rank 0's params + buffers everywhere
+        if init_sync and self.world_size > 1:
+            self._verify_param_shape_across_processes()
+            self._sync_module_states()
+
+        # ---- reducer
+        if comm_backend is None:
+            comm_backend = "peer" if self.device_type == "cuda" else "torch"
+        if comm_backend == "peer":
+            if self.device_type != "cuda":
+                raise ValueError("comm_backend='peer' needs CUDA parameters")
+            self.backend = PeerBackend(self.process_group, params[0].device)
+        elif comm_backend == "torch":
+            if self.process_group is None:
+                raise RuntimeError("comm_backend='torch' needs an initialised process group")
+            self.backend = TorchDistBackend(self.process_group)
+        else:
+            raise ValueError("unknown comm_backend %r" % comm_backend)
+        if fused_sgd is not None and not self.backend.supports_fused:
+            raise ValueError("fused_sgd needs comm_backend='peer'")
+        self.reducer = Reducer(params, self.backend, self.bucket_bytes_cap, first_bucket_bytes, find_unused_parameters,
+                               gradient_as_bucket_view, names, fused_sgd, static_graph)
+        self.optimizer = FusedSGD(self.reducer, fused_sgd) if fused_sgd is not None else None
+        self._rebuild_checked = False
+        self.logger_data = {"backend": self.backend.name, "world_size": self.world_size,
+                            "bucket_cap_bytes": self.bucket_bytes_cap}
+
+    # ------------------------------------------------------------------------------------------ init helpers
+    def _verify_param_shape_across_processes(self):
+        shapes = [tuple(p.shape) for p in self._params]
+        gathered = [None] * self.world_size
+        dist.all_gather_object(gathered, shapes, group=self.process_group)
+        for r, s in enumerate(gathered):
+            if s != shapes:
+                raise RuntimeError("DDP parameter shapes differ between rank %d and rank %d" % (self.rank, r))
+
+    def _sync_module_states(self):
+        tensors = [p.detach() for p in self._params] + list(self.modules_buffers)
+        broadcast_coalesced_group(self.process_group, tensors, BROADCAST_BUCKET_BYTES, src=0)
+
+    def _sync_buffers(self):
+        if self.modules_buffers and self.world_size > 1:
+            with torch.no_grad():
+                broadcast_coalesced_group(self.process_group, self.modules_buffers, BROADCAST_BUCKET_BYTES, src=0)
+
+    # ------------------------------------------------------------------------------------------ forward
+    def forward(self, *inputs, **kwargs):
+        with torch.autograd.profiler.record_function("DistributedDataParallel.forward"):
+            will_sync = torch.is_grad_enabled() and self.require_backward_grad_sync
+            if will_sync and not self._rebuild_checked and self.reducer.stats["iterations"] >= 1:
+                self._rebuild_checked = True
+                if not self.static_graph or True:
+                    self.reducer.maybe_rebuild_buckets()
+            if self.require_forward_param_sync and self.broadcast_buffers and self.training:
+                self._sync_buffers()
+            if self.device_ids and self.device_type == "cuda":
+                dev = torch.device("cuda", self.device_ids[0])
+                inputs = _to_device(inputs, dev)
+                kwargs = _to_device(kwargs, dev)
+            out = self.module(*inputs, **kwargs)
+            if will_sync:
+                unused = ()
+                if self.find_unused_parameters:
+                    reach = _reachable_params(out)
+                    unused = [i for i, p in enumerate(self._params) if id(p) not in reach]
+                self.reducer.require_sync = True
+                self.reducer.prepare_for_backward(unused)
+            else:
+                self.reducer.require_sync = False
+            self.require_forward_param_sync = self.require_backward_grad_sync
+            return out
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Skip gradient synchronisation inside the context; gradients accumulate locally and the first
+        forward/backward after it synchronises the sum (torch distributed.py:1474-1500)."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    # ------------------------------------------------------------------------------------------ hooks / misc API
+    def register_comm_hook(self, state: Any, hook: Callable):
+        """``hook(state, bucket) -> Future[Tensor]``; replaces the built-in bucket all-reduce."""
+        if not callable(hook):
+            raise TypeError("Communication hook must be callable.")
+        if self.reducer.fused_cfg is not None:
+            raise RuntimeError("communication hooks cannot be combined with fused_sgd")
+        self.reducer.comm_hook = hook
+        self.reducer.comm_hook_state = state
+
+    def _set_static_graph(self):
+        self.static_graph = True
+
+    def check_health(self):
+        if hasattr(self.backend, "check_health"):
+            self.backend.check_health()
+
+    def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
+        r = super().load_state_dict(state_dict, strict=strict)
+        self.reducer.sync_shadow()
+        return r
+
+    def __getstate__(self):
+        d = self.__dict__.copy()
+        for k in ("reducer", "backend", "process_group", "optimizer"):
+            d.pop(k, None)
+        return d
+
+    def __setstate__(self, state):
+        self.__dict__.update(state)
+        self.process_group = dist.group.WORLD if dist.is_initialized() else None
+
+
+def _to_device(obj, dev):
+    if isinstance(obj, torch.Tensor):
+        return obj.to(dev, non_blocking=True) if obj.device != dev else obj
+    if isinstance(obj, tuple):
+        return tuple(_to_device(o, dev) for o in obj)
+    if isinstance(obj, list):
+        return [_to_device(o, dev) for o in obj]
+    if isinstance(obj, dict):
+        return {k: _to_device(v, dev) for k, v in obj.items()}
+    return obj

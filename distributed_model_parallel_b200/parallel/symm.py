@@ -1,0 +1,165 @@
+"""Peer-addressable ("symmetric") memory for the communication kernels.
+
+Two flavours, same interface (``SymmBuffer.local`` tensor + ``peer_ptrs`` for every rank):
+
+* ``ProcessSymmGroup``  -- one process per GPU (DistributedDataParallel, SyncBatchNorm).  Buffers are raw
+  ``cudaMalloc`` allocations exported with CUDA IPC; handles travel through the ``torch.distributed`` store
+  (control plane only) and every rank maps every peer's buffer into its own address space.
+* ``DeviceSymmGroup``   -- one process driving several GPUs (DataParallel).  Buffers are ordinary per-device
+  tensors; ``cudaDeviceEnablePeerAccess`` makes them addressable from kernels on the other devices.
+
+NVLink/NVSwitch does the rest: kernels in ``csrc/comm/collectives.cu`` dereference the peer pointers
+directly.  Nothing here has a counterpart in the reference, whose DP/DDP paths delegate all communication
+to torch/NCCL.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .. import _native
+
+_native.register_kernel_sigs({
+    "dmp_comm_state_bytes": (C.c_longlong, []),
+    "dmp_comm_max_ranks": (C.c_int, []),
+    "dmp_comm_max_blocks": (C.c_int, []),
+    "dmp_allreduce_fused": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_float,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                      C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_broadcast": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int,
+                                C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_gather_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "dmp_copy_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
+    "dmp_reduce_add_peer": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_symm_malloc": (C.c_int, [C.c_longlong, C.POINTER(C.c_void_p)]),
+    "dmp_symm_free": (C.c_int, [C.c_void_p]),
+    "dmp_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "dmp_ipc_import": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "dmp_ipc_close": (C.c_int, [C.c_void_p]),
+    "dmp_ipc_handle_bytes": (C.c_int, []),
+    "dmp_enable_peer_access": (C.c_int, [C.c_int]),
+    "dmp_comm_status": (C.c_int, [C.c_void_p, C.c_void_p]),
+})
+
+DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}
+
+
+def ptr_array(ptrs: Sequence[int]):
+    """ctypes ``void*[n]`` from integer addresses (kept alive by the caller)."""
+    arr = (C.c_void_p * len(ptrs))()
+    for i, p in enumerate(ptrs):
+        arr[i] = p
+    return arr
+
+
+class _RawCuda:
+    """Exposes a raw device allocation through ``__cuda_array_interface__`` so torch can alias it."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+        self._owner = owner
+
+
+class SymmBuffer:
+    """``nbytes`` of device memory on every rank; ``local`` aliases this rank's copy, ``peer_ptrs[r]`` is the
+    address of rank r's copy as seen from this rank."""
+
+    def __init__(self, local: torch.Tensor, peer_ptrs: List[int], rank: int, owner=None):
+        self.local = local
+        self.peer_ptrs = list(peer_ptrs)
+        self.rank = rank
+        self.nbytes = local.numel() * local.element_size()
+        self._ptr_array = ptr_array(self.peer_ptrs)
+        self._owner = owner
+
+    @property
+    def ptrs(self):
+        return self._ptr_array
+
+    def view(self, dtype: torch.dtype, numel: Optional[int] = None, byte_offset: int = 0) -> torch.Tensor:
+        t = self.local.view(torch.uint8)[byte_offset:]
+        if numel is not None:
+            t = t[: numel * torch.empty((), dtype=dtype).element_size()]
+        return t.view(dtype)
+
+    def sub(self, byte_offset: int, nbytes: int) -> "SymmBuffer":
+        loc = self.local.view(torch.uint8)[byte_offset: byte_offset + nbytes]
+        return SymmBuffer(loc, [p + byte_offset for p in self.peer_ptrs], self.rank, owner=self)
+
+
+class _IpcAllocation:
+    def __init__(self, lib, ptr, imported):
+        self.lib, self.ptr, self.imported = lib, ptr, imported
+
+    def __del__(self):
+        try:
+            for p in self.imported:
+                self.lib.dmp_ipc_close(p)
+            self.lib.dmp_symm_free(self.ptr)
+        except Exception:
+            pass
+
+
+class ProcessSymmGroup:
+    """Symmetric memory across the ranks of a ``torch.distributed`` process group (one process per GPU)."""
+
+    def __init__(self, group=None, device: Optional[torch.device] = None):
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world_size = dist.get_world_size(self.group)
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.lib = _native.kernels()
+        if self.world_size > self.lib.dmp_comm_max_ranks():
+            raise RuntimeError("world size %d exceeds the %d ranks the peer kernels support" %
+                               (self.world_size, self.lib.dmp_comm_max_ranks()))
+
+    def alloc(self, nbytes: int) -> SymmBuffer:
+        nbytes = max(256, (int(nbytes) + 255) // 256 * 256)
+        with torch.cuda.device(self.device):
+            p = C.c_void_p()
+            _native.check(self.lib.dmp_symm_malloc(nbytes, C.byref(p)), "symm_malloc")
+            hbytes = self.lib.dmp_ipc_handle_bytes()
+            handle = C.create_string_buffer(hbytes)
+            _native.check(self.lib.dmp_ipc_export(p, handle), "ipc_export")
+            gathered = [None] * self.world_size
+            dist.all_gather_object(gathered, (bytes(handle.raw), int(self.device.index or 0)), group=self.group)
+            ptrs, imported = [], []
+            for r, (h, _dev) in enumerate(gathered):
+                if r == self.rank:
+                    ptrs.append(p.value)
+                    continue
+                q = C.c_void_p()
+                hb = C.create_string_buffer(h, hbytes)
+                _native.check(self.lib.dmp_ipc_import(hb, C.byref(q)), "ipc_import")
+                ptrs.append(q.value)
+                imported.append(q.value)
+            owner = _IpcAllocation(self.lib, p.value, imported)
+            local = torch.as_tensor(_RawCuda(p.value, nbytes, owner), device=self.device)
+        dist.barrier(group=self.group)
+        return SymmBuffer(local, ptrs, self.rank, owner=owner)
+
+    def new_state(self) -> SymmBuffer:
+        """Fresh communicator state (flag pad + epochs + status) -- one per ordered stream of collectives."""
+        return self.alloc(int(self.lib.dmp_comm_state_bytes()))
+
+
+class DeviceSymmGroup:
+    """Peer-addressable buffers across several devices of one process (DataParallel)."""
+
+    def __init__(self, devices: Sequence[int]):
+        self.devices = [int(d) for d in devices]
+        self.world_size = len(self.devices)
+        self.lib = _native.kernels()
+        for d in self.devices:
+            with torch.cuda.device(d):
+                for e in self.devices:
+                    if e != d:
+                        _native.check(self.lib.dmp_enable_peer_access(e), "enable_peer_access")
+
+    def alloc(self, nbytes: int) -> List[torch.Tensor]:
+        nbytes = max(256, (int(nbytes) + 255) // 256 * 256)
+        return [torch.zeros(nbytes, dtype=torch.uint8, device=torch.device("cuda", d)) for d in self.devices]
