@@ -33,6 +33,28 @@ _tls = threading.local()
 grad_ready_callbacks: list = []
 
 
+_force_reference = False
+
+
+class use_reference_ops:
+    """Context manager: run the plain PyTorch restatement even for CUDA tensors (numerics oracle / A-B timing)."""
+
+    def __enter__(self):
+        global _force_reference
+        self._old = _force_reference
+        _force_reference = True
+        return self
+
+    def __exit__(self, *exc):
+        global _force_reference
+        _force_reference = self._old
+        return False
+
+
+def _use_kernels(x: torch.Tensor) -> bool:
+    return x.is_cuda and not _force_reference
+
+
 def _note(key: str) -> None:
     path_counts[key] += 1
 
@@ -173,9 +195,9 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
                                   sp), "conv1x1 dgrad gemm")
             if conv.stride != (1, 1):
                 s0, s1 = conv.stride
-                dx = torch.zeros((N, cin, (H - 1) * s0 + 1 + (conv._dmp_in_hw[0] - ((H - 1) * s0 + 1)),
-                                  conv._dmp_in_hw[1]), device=x.device, dtype=torch.bfloat16,
-                                 memory_format=torch.channels_last)
+                Hin, Win = conv._dmp_in_hw
+                dx = torch.zeros((N, cin, Hin, Win), device=x.device, dtype=torch.bfloat16).contiguous(
+                    memory_format=torch.channels_last)
                 dx[:, :, ::s0, ::s1] = dxs
             else:
                 dx = dxs
@@ -370,7 +392,7 @@ def _conv_bn_act_reference(x, conv, bn, relu, residual):
 def conv_bn_act(x: torch.Tensor, conv: nn.Conv2d, bn: Optional[nn.Module] = None, relu: bool = False,
                 residual: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``act(bn(conv(x)) + residual)`` with optional pieces.  ``bn`` may be BatchNorm2d or our SyncBatchNorm."""
-    if not x.is_cuda:
+    if not _use_kernels(x):
         _note("conv_bn_act:reference")
         return _conv_bn_act_reference(x, conv, bn, relu, residual)
     sync = getattr(bn, "_dmp_sync", None) if bn is not None else None
@@ -410,7 +432,7 @@ class _GlobalAvgPool(torch.autograd.Function):
 
 def global_avgpool_flatten(x: torch.Tensor, relu: bool = False) -> torch.Tensor:
     """``flatten(avg_pool2d(relu?(x), full spatial extent))`` -> [N, C] (the reference's Reshape1 / forward tail)."""
-    if x.is_cuda and x.shape[1] % 8 == 0:
+    if _use_kernels(x) and x.shape[1] % 8 == 0:
         return _GlobalAvgPool.apply(x, relu)
     _note("avgpool:reference")
     if relu:
@@ -507,9 +529,9 @@ class _Linear(torch.autograd.Function):
 
 
 def linear(x: torch.Tensor, lin: nn.Linear) -> torch.Tensor:
-    if not x.is_cuda:
+    if not _use_kernels(x):
         _note("linear:reference")
-        return F.linear(x, lin.weight, lin.bias)
+        return F.linear(x, lin.weight.to(x.dtype), lin.bias.to(x.dtype) if lin.bias is not None else None)
     return _Linear.apply(x, lin.weight, lin.bias, lin)
 
 
@@ -540,7 +562,7 @@ class _CrossEntropy(torch.autograd.Function):
 def cross_entropy(logits: torch.Tensor, target: torch.Tensor, stats_out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Mean softmax cross-entropy.  On CUDA one fused kernel also produces dlogits and, if ``stats_out`` (3 floats)
     is given, {loss, top-1 hits, top-5 hits} for the metrics the reference logs."""
-    if not logits.is_cuda:
+    if not _use_kernels(logits):
         _note("xent:reference")
         loss = F.cross_entropy(logits.float(), target)
         if stats_out is not None:
