@@ -1,0 +1,138 @@
+/* dmp_b200.h -- C ABI of libdmp_b200.so (sm_100a kernels) and libdmp_b200_rt.so (host runtime).
+ *
+ * Conventions
+ *   - every kernel entry point returns 0 on success, a CUDA error code or -1 on failure; dmp_last_error()
+ *     then holds a message (thread local);
+ *   - pointers are device pointers unless stated; `stream` is a cudaStream_t; work is enqueued, never synchronised;
+ *   - activations are channels-last: x[M, C] with C contiguous (M = N*H*W); dtype codes: 0 = fp32, 1 = bf16, 2 = fp64;
+ *   - "R/" cites /root/reference/code/distributed_training/, "T/" cites the installed torch sources.
+ */
+#ifndef DMP_B200_H
+#define DMP_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* dmp_stream_t; /* cudaStream_t */
+
+/* ------------------------------------------------------------------ library state */
+const char* dmp_last_error(void);
+unsigned long long dmp_launch_count(void); /* kernels launched by this library since the last reset */
+void dmp_reset_launch_count(void);
+int dmp_version(void);
+int dmp_device_cc(void);                                              /* e.g. 100 for sm_100 */
+int dmp_l2_flush(void* buf, long long bytes, dmp_stream_t stream);    /* benchmark helper */
+
+/* ------------------------------------------------------------------ tcgen05 GEMM (csrc/kernels/gemm_tcgen05.cu)
+ * bf16 x bf16 -> fp32 accumulate in TMEM.  layout 0: A[M,K] B[N,K] (1x1 conv / linear forward, R/model/mobilenetv2.py:17,21,55);
+ * layout 1: A[M,K] B[K,N] (data gradient); layout 2: A[K,M] B[K,N] (weight gradient, split-K).
+ * out_mode 0: bf16 store, 1: fp32 store, 2: fp32 atomic accumulate.  bias: optional fp32[N]. */
+int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd, int M,
+                  int N, int K, const float* bias, int out_mode, int splits, dmp_stream_t stream);
+int dmp_gemm_ref_f32out(int layout, const void* A, long long lda, const void* B, long long ldb, float* D, long long ldd,
+                        int M, int N, int K, const float* bias, int accumulate, dmp_stream_t stream); /* CUDA-core oracle */
+
+/* ------------------------------------------------------------------ optimizer (csrc/kernels/sgd.cu; R/data_parallel.py:90-91,111)
+ * hp_dev = device {lr, momentum, weight_decay, grad_scale}. */
+int dmp_sgd_flat(float* master, void* shadow_bf16, void* grad, int grad_dtype, float* momentum, long long n,
+                 const float* hp_dev, int nesterov, int zero_grad, dmp_stream_t stream);
+int dmp_cast_flat(const void* src, void* dst, long long n, int direction, dmp_stream_t stream);
+
+/* ------------------------------------------------------------------ loss (csrc/kernels/xent.cu; R/utils.py:58-65,215-229)
+ * rows: scratch of 3*B floats.  out: {mean loss, top-1 hits, top-5 hits}. */
+int dmp_xent_fwd_bwd(const void* logits, const long long* targets, void* dlogits, float* rows, float* out, int B, int C,
+                     int dtype, float grad_scale, dmp_stream_t stream);
+
+/* ------------------------------------------------------------------ BatchNorm (csrc/kernels/bn.cu; R/model/mobilenetv2.py:18-22,53,56)
+ * accum: caller-provided scratch of 2*C doubles (zeroed by the call). */
+int dmp_bn_stats(const void* x, int dtype, long long M, int C, double* accum, dmp_stream_t stream);
+int dmp_bn_finalize(const double* accum, double count, const float* gamma, const float* beta, float* running_mean,
+                    float* running_var, float momentum, float eps, float* mean, float* invstd, float* scale, float* shift,
+                    int C, dmp_stream_t stream);
+int dmp_bn_apply(const void* x, int dtype, const float* scale, const float* shift, const void* residual, void* y,
+                 long long M, int C, int relu, dmp_stream_t stream);
+int dmp_bn_bwd_reduce(const void* dy, const void* y, const void* x, int dtype, const float* mean, const float* invstd,
+                      long long M, int C, int relu, double* accum, dmp_stream_t stream);
+int dmp_bn_bwd_dx(const void* dy, const void* y, const void* x, int dtype, const float* mean, const float* invstd,
+                  const float* gamma, const double* accum_global, double count, void* dx, void* dres, long long M, int C,
+                  int relu, dmp_stream_t stream);
+int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* dbeta, int C, int accumulate, dmp_stream_t stream);
+
+/* ------------------------------------------------------------------ depthwise 3x3 (csrc/kernels/dwconv.cu; R/model/mobilenetv2.py:19,33) */
+int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int stride,
+                      dmp_stream_t stream);
+int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void* dx, int N, int H, int W, int C, int stride,
+                        dmp_stream_t stream);
+int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int stride, int accumulate,
+                        dmp_stream_t stream);
+
+/* ------------------------------------------------------------------ small ops (csrc/kernels/misc.cu; R/model/mobilenetv2.py:52,57,69-75) */
+int dmp_stem_conv_fwd(const void* x, int x_layout, const void* w, int w_dtype, void* y, int N, int Cin, int H, int W,
+                      int Cout, int KH, int KW, int stride, int pad, dmp_stream_t stream);
+int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, float* dw, int N, int Cin, int H, int W, int Cout,
+                        int KH, int KW, int stride, int pad, int accumulate, dmp_stream_t stream);
+int dmp_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int relu, dmp_stream_t stream);
+int dmp_avgpool_bwd(const void* dy, const void* x, void* dx, int N, int HW, int C, int relu, dmp_stream_t stream);
+int dmp_linear_small_fwd(const void* x, const void* w, int w_dtype, const float* bias, float* y, int B, int N, int K,
+                         dmp_stream_t stream);
+int dmp_linear_small_bwd(const float* dy, const void* x, const void* w, int w_dtype, void* dx, float* dw, float* db, int B,
+                         int N, int K, int accumulate, dmp_stream_t stream);
+int dmp_add_act(const void* a, const void* b, void* y, long long n, int relu, dmp_stream_t stream);
+int dmp_relu_bwd(const void* dy, const void* y, void* dx, long long n, dmp_stream_t stream);
+
+/* ------------------------------------------------------------------ peer-memory collectives (csrc/comm/collectives.cu)
+ * Pointer tables (`void* const*`) are HOST arrays of device addresses, one per rank, valid on the calling rank.
+ * state[r]: rank r's communicator state of dmp_comm_state_bytes() bytes, zero-initialised once.
+ * E3 DDP bucket all-reduce (T/nn/parallel/distributed.py:1255-1280 Reducer; default_hooks.py:26-32), D2 broadcast_coalesced
+ * (T/nn/parallel/comm.py:50-67), D4 gather (:258), D6 reduce_add_coalesced (:124-168). */
+long long dmp_comm_state_bytes(void);
+int dmp_comm_max_ranks(void);
+int dmp_comm_max_blocks(void);
+int dmp_allreduce_fused(int algo, int dtype, void* const* bufs, void* const* state, int rank, int W, long long n,
+                        float scale, void* out, float* master, float* momentum, void* shadow, const float* hp_dev,
+                        int nesterov, void* const* param_peers, void* const* shadow_peers, int zero_after, int max_blocks,
+                        dmp_stream_t stream);
+int dmp_broadcast(const void* src, void* const* dst, int n_dst, void* mc_dst, void* const* dst_bf16, long long bytes,
+                  void* const* state, int rank, int W, int is_src, int max_blocks, dmp_stream_t stream);
+int dmp_gather_peer(void* const* src, const long long* bytes, int n_src, void* dst, int max_blocks, dmp_stream_t stream);
+int dmp_copy_peer(const void* src, void* dst, long long bytes, int max_blocks, dmp_stream_t stream);
+int dmp_reduce_add_peer(int dtype, void* const* src, int W, long long n, float scale, float* out_f32, float* master,
+                        float* momentum, void* shadow, const float* hp_dev, int nesterov, int max_blocks,
+                        dmp_stream_t stream);
+int dmp_comm_status(void* state_local, dmp_stream_t stream); /* 0 healthy, 1+peer: barrier with that peer timed out */
+
+/* peer-memory plumbing */
+int dmp_symm_malloc(long long bytes, void** out);
+int dmp_symm_free(void* p);
+int dmp_ipc_export(void* p, void* handle64);
+int dmp_ipc_import(const void* handle64, void** out);
+int dmp_ipc_close(void* p);
+int dmp_ipc_handle_bytes(void);
+int dmp_enable_peer_access(int peer);
+
+/* ------------------------------------------------------------------ host runtime (libdmp_b200_rt.so; csrc/runtime/)
+ * Reducer bookkeeping (T/nn/parallel/distributed.py:1183-1304; studied at /root/reference/Readme.md:145-157) and the pipeline
+ * partitioner / schedules replacing R/model_parallel.py:102-103,129,143-144 and R/utils.py:34-210. */
+int dmp_rt_version(void);
+int dmp_bucket_assign(int n, const int64_t* nbytes, const int32_t* keys, const int64_t* limits, int n_limits,
+                      int32_t* out_bucket_of_param);
+void* dmp_reducer_create(int n_params, int n_buckets, const int32_t* bucket_of_param);
+void dmp_reducer_destroy(void* h);
+void dmp_reducer_prepare(void* h);
+int dmp_reducer_mark_ready(void* h, int p, int unused, int32_t* out, int cap);
+int dmp_reducer_finalize(void* h, int32_t* out_missing, int cap);
+int dmp_reducer_num_launched(void* h);
+long long dmp_reducer_iterations(void* h);
+int dmp_reducer_ready_order(void* h, int32_t* out, int cap);
+void dmp_reducer_unused_flags(void* h, int32_t* out);
+int dmp_partition_balanced(int n, const double* cost, int W, int32_t* out_bounds);
+int dmp_schedule_generate(int kind, int W, int s, int M, int32_t* out, int cap);
+double dmp_schedule_simulate(int kind, int W, int M, double tf, double tb, int32_t* out_peak_inflight);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DMP_B200_H */
