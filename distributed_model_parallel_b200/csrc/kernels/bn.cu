@@ -350,3 +350,86 @@ DMP_API int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* d
     DMP_COUNT_LAUNCH(1);
     return 0;
 }
+
+// =====================================================================================================
+// Allocation-free variant: batch statistics + finalize with the accumulator held inside the library.
+//
+// Who needs this: hosts that must not (or cannot) hand the library any extra device memory and in which
+// nothing may call cudaMalloc once the process is set up -- for example a serving or training runtime that
+// reserved the whole HBM for its own arena at start-up (a later cudaMalloc would simply fail), or a
+// latency-critical loop run under a "no allocator calls in steady state" rule because cudaMalloc/cudaFree
+// synchronise the device.  dmp_bn_stats needs a double[2*C] accumulator from its caller; such callers have
+// nowhere to take one from.  Here the accumulator is a fixed array that is part of the loaded module.
+//
+// Cost and limits:
+//   * the array is DMP_BN_NOALLOC_MAX_C * 2 doubles = 64 KiB and every GPU that loads libdmp_b200.so carries
+//     it until the process exits, whether or not this entry point is ever used;
+//   * C > DMP_BN_NOALLOC_MAX_C is refused with an error (use dmp_bn_stats + dmp_bn_finalize instead);
+//   * there is ONE array per GPU, shared by every call: it still holds the sums of the previous call, so each
+//     call clears the 2*C doubles it is about to use (on `stream`) before accumulating; two calls whose
+//     kernels can overlap on the same GPU (different streams without an ordering between them, or several
+//     host threads) race on it and produce garbage -- serialise them;
+//   * the first call made on each device looks up the array's device address (cudaGetSymbolAddress with that
+//     device current) and caches it.  Make that first call during start-up, before any stream capture begins.
+// Apart from where the accumulator lives the arithmetic is that of dmp_bn_stats followed by dmp_bn_finalize.
+// =====================================================================================================
+#include <mutex>
+
+#define DMP_BN_NOALLOC_MAX_C 4096
+
+static __device__ __align__(256) double g_bn_noalloc_accum[2 * DMP_BN_NOALLOC_MAX_C];
+
+namespace {
+std::mutex g_bn_noalloc_mu;
+double* g_bn_noalloc_addr[64] = {nullptr};  // per device: device address of g_bn_noalloc_accum
+
+// In host code `g_bn_noalloc_accum` is only a handle for the symbol, never a usable pointer: the address a
+// kernel may dereference has to be asked for, once per device, while that device is current.
+int bn_noalloc_accum(double** out) {
+    int dev = -1;
+    DMP_CHECK_CUDA(cudaGetDevice(&dev));
+    DMP_REQUIRE(dev >= 0 && dev < 64, "dmp_bn_stats_finalize_noalloc: device ordinal %d out of range", dev);
+    std::lock_guard<std::mutex> lock(g_bn_noalloc_mu);
+    if (g_bn_noalloc_addr[dev] == nullptr) {
+        void* p = nullptr;
+        DMP_CHECK_CUDA(cudaGetSymbolAddress(&p, g_bn_noalloc_accum));
+        DMP_REQUIRE(p != nullptr, "dmp_bn_stats_finalize_noalloc: cudaGetSymbolAddress returned a null address");
+        g_bn_noalloc_addr[dev] = (double*)p;
+    }
+    *out = g_bn_noalloc_addr[dev];
+    return 0;
+}
+}  // namespace
+
+DMP_API int dmp_bn_noalloc_max_channels() { return DMP_BN_NOALLOC_MAX_C; }
+
+// Train-mode BatchNorm statistics of x[M, C] (dtype 0 = fp32, 1 = bf16) and everything derived from them:
+// mean, invstd, fused scale/shift, and the running-stat update when running_mean/var are given.  Inputs and
+// outputs are the caller's; no device memory is allocated or freed.  See the block comment above for the
+// sharing / ordering rules.
+DMP_API int dmp_bn_stats_finalize_noalloc(const void* x, int dtype, long long M, int C, const float* gamma, const float* beta,
+                                          float* running_mean, float* running_var, float momentum, float eps, float* mean,
+                                          float* invstd, float* scale, float* shift, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_stats_finalize_noalloc", M, C, dtype)) return rc;
+    DMP_REQUIRE(C <= DMP_BN_NOALLOC_MAX_C,
+                "dmp_bn_stats_finalize_noalloc: C=%d exceeds the built-in accumulator (max %d channels); use dmp_bn_stats "
+                "with a caller-provided accumulator instead",
+                C, DMP_BN_NOALLOC_MAX_C);
+    DMP_REQUIRE(x && mean && invstd && scale && shift, "dmp_bn_stats_finalize_noalloc: null input/output pointer");
+    double* accum = nullptr;
+    if (int rc = bn_noalloc_accum(&accum)) return rc;
+    // the array still holds the previous call's sums: clear exactly the part this call accumulates into
+    DMP_CHECK_CUDA(cudaMemsetAsync(accum, 0, sizeof(double) * 2 * (size_t)C, stream));
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    const size_t smem = (size_t)BN_THREADS * 2 * vec * sizeof(float);
+    if (dtype == 1) bn_stats_kernel<bf16><<<grid, BN_THREADS, smem, stream>>>((const bf16*)x, nvec, C, accum);
+    else bn_stats_kernel<float><<<grid, BN_THREADS, smem, stream>>>((const float*)x, nvec, C, accum);
+    DMP_LAUNCH_CHECK();
+    bn_finalize_kernel<<<dmp_ceil_div(C, 128), 128, 0, stream>>>(accum, (double)M, gamma, beta, running_mean, running_var,
+                                                                 momentum, eps, mean, invstd, scale, shift, C);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(2);
+    return 0;
+}

@@ -60,6 +60,17 @@ int dmp_bn_bwd_dx(const void* dy, const void* y, const void* x, int dtype, const
                   const float* gamma, const double* accum_global, double count, void* dx, void* dres, long long M, int C,
                   int relu, dmp_stream_t stream);
 int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* dbeta, int C, int accumulate, dmp_stream_t stream);
+/* Statistics + finalize for callers that may not allocate device memory (their process gave all of HBM to its own arena, or
+ * bans allocator calls in its steady-state loop): same results as dmp_bn_stats + dmp_bn_finalize, but the double[2*C]
+ * accumulator is a fixed 64 KiB array inside the library instead of a caller buffer.  No counterpart in the reference (it has
+ * no native code and allocates freely through torch).  C <= dmp_bn_noalloc_max_channels() (4096), larger C is refused.
+ * One array per GPU shared by all calls: each call clears what it uses; calls that can overlap on a GPU race.  The first call
+ * on a device resolves the array's address (cudaGetSymbolAddress) -- make it at start-up, before any stream capture.
+ * Calls no cudaMalloc/cudaFree. */
+int dmp_bn_stats_finalize_noalloc(const void* x, int dtype, long long M, int C, const float* gamma, const float* beta,
+                                  float* running_mean, float* running_var, float momentum, float eps, float* mean,
+                                  float* invstd, float* scale, float* shift, dmp_stream_t stream);
+int dmp_bn_noalloc_max_channels(void);
 
 /* ------------------------------------------------------------------ depthwise 3x3 (csrc/kernels/dwconv.cu; R/model/mobilenetv2.py:19,33) */
 int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int stride,
