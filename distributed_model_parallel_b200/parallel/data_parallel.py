@@ -1,0 +1,113 @@
+"""DataParallel: single process, one thread per replica -- same call shape as ``torch.nn.DataParallel``.
+
+``DataParallel(module, device_ids=None, output_device=None, dim=0)`` is what the reference's DP trainer wraps its
+network in (/root/reference/code/distributed_training/data_parallel.py:77).  Forward = scatter inputs ->
+replicate module (coalesced broadcast of parameters + buffers) -> parallel_apply (threads) -> gather outputs;
+backward runs Gather.backward (scatter of the output gradient) and Broadcast.backward (reduce-add of replica
+gradients onto device 0).  torch/nn/parallel/data_parallel.py:136-290 is the behavioural model; every
+device-to-device transfer is one of our peer-memory kernels (``parallel/comm.py``).
+
+``state_dict()`` keys carry the ``module.`` prefix, so the reference's best-accuracy checkpoints
+(data_parallel.py:147-151) round-trip.  CPU "devices" are accepted so that the container logic is testable without
+GPUs.
+"""
+from __future__ import annotations
+
+import warnings
+from itertools import chain
+from typing import Any, Optional, Sequence
+
+import torch
+import torch.nn as nn
+
+from .comm import _dev
+from .parallel_apply import parallel_apply
+from .replicate import replicate
+from .scatter_gather import gather, scatter_kwargs
+
+
+def _check_balance(devices):
+    props = [torch.cuda.get_device_properties(d) for d in devices if d.type == "cuda"]
+    if len(props) < 2:
+        return
+    for name, values in (("memory", [p.total_memory for p in props]), ("cores", [p.multi_processor_count for p in props])):
+        lo, hi = min(values), max(values)
+        if lo / hi < 0.75:
+            warnings.warn("There is an imbalance between your GPUs (%s): device %d has less than 75%% of device %d. "
+                          "Exclude the weaker device via device_ids." % (name, values.index(lo), values.index(hi)))
+            return
+
+
+class DataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids: Optional[Sequence] = None, output_device=None, dim: int = 0):
+        super().__init__()
+        if device_ids is None:
+            if not torch.cuda.is_available():
+                self.module, self.device_ids = module, []
+                self.dim = dim
+                return
+            device_ids = list(range(torch.cuda.device_count()))
+        self.devices = [_dev(d) for d in device_ids]
+        self.device_ids = [d.index if d.type == "cuda" else d for d in self.devices]
+        self.output_device = _dev(output_device) if output_device is not None else self.devices[0]
+        self.src_device_obj = self.devices[0]
+        self.dim = dim
+        self.module = module
+        if all(d.type == "cuda" for d in self.devices):
+            _check_balance(self.devices)
+        if len(self.devices) == 1:
+            self.module.to(self.devices[0])
+
+    def forward(self, *inputs: Any, **kwargs: Any) -> Any:
+        with torch.autograd.profiler.record_function("DataParallel.forward"):
+            if not self.device_ids:
+                return self.module(*inputs, **kwargs)
+            for t in chain(self.module.parameters(), self.module.buffers()):
+                if t.device != self.src_device_obj:
+                    raise RuntimeError("module must have its parameters and buffers on device %s (device_ids[0]) but found "
+                                       "one of them on device: %s" % (self.src_device_obj, t.device))
+            inputs, module_kwargs = self.scatter(inputs, kwargs, self.devices)
+            if not inputs and not module_kwargs:  # forward without arguments
+                inputs, module_kwargs = ((),), ({},)
+            if len(self.devices) == 1:
+                return self.module(*inputs[0], **module_kwargs[0])
+            replicas = self.replicate(self.module, self.devices[: len(inputs)])
+            outputs = self.parallel_apply(replicas, inputs, module_kwargs)
+            return self.gather(outputs, self.output_device)
+
+    def replicate(self, module, devices):
+        return replicate(module, devices, not torch.is_grad_enabled())
+
+    def scatter(self, inputs, kwargs, devices):
+        return scatter_kwargs(inputs, kwargs, devices, dim=self.dim)
+
+    def parallel_apply(self, replicas, inputs, kwargs):
+        return parallel_apply(replicas, inputs, kwargs, self.devices[: len(replicas)])
+
+    def gather(self, outputs, output_device):
+        return gather(outputs, output_device, dim=self.dim)
+
+
+def data_parallel(module: nn.Module, inputs: Any, device_ids: Optional[Sequence] = None, output_device=None, dim: int = 0,
+                  module_kwargs: Optional[Any] = None) -> Any:
+    """Functional form: evaluate ``module(inputs)`` in parallel across ``device_ids``."""
+    if not isinstance(inputs, tuple):
+        inputs = (inputs,) if inputs is not None else ()
+    if device_ids is None:
+        device_ids = list(range(torch.cuda.device_count()))
+    devices = [_dev(d) for d in device_ids]
+    out_dev = _dev(output_device) if output_device is not None else devices[0]
+    src = devices[0]
+    for t in chain(module.parameters(), module.buffers()):
+        if t.device != src:
+            raise RuntimeError("module must have its parameters and buffers on device %s (device_ids[0]) but found one of "
+                               "them on device: %s" % (src, t.device))
+    inputs, module_kwargs = scatter_kwargs(inputs, module_kwargs, devices, dim)
+    if not inputs and not module_kwargs:
+        inputs, module_kwargs = ((),), ({},)
+    if len(devices) == 1:
+        return module(*inputs[0], **module_kwargs[0])
+    used = devices[: len(inputs)]
+    replicas = replicate(module, used, not torch.is_grad_enabled())
+    outputs = parallel_apply(replicas, inputs, module_kwargs, used)
+    return gather(outputs, out_dev, dim)

@@ -198,6 +198,9 @@ class DistributedDataParallel(nn.Module):
         self.reducer = Reducer(params, self.backend, self.bucket_bytes_cap, first_bucket_bytes, find_unused_parameters,
                                gradient_as_bucket_view, names, fused_sgd, static_graph)
         self.optimizer = FusedSGD(self.reducer, fused_sgd) if fused_sgd is not None else None
+        self._buffer_arena = None
+        if isinstance(self.backend, PeerBackend) and self.backend.symm is not None and self.modules_buffers and broadcast_buffers:
+            self._build_buffer_arena()
         self._rebuild_checked = False
         self.logger_data = {"backend": self.backend.name, "world_size": self.world_size,
                             "bucket_cap_bytes": self.bucket_bytes_cap}
@@ -215,7 +218,35 @@ class DistributedDataParallel(nn.Module):
         tensors = [p.detach() for p in self._params] + list(self.modules_buffers)
         broadcast_coalesced_group(self.process_group, tensors, BROADCAST_BUCKET_BYTES, src=0)
 
+    def _build_buffer_arena(self):
+        """Moves every buffer (BN running statistics, counters) into one peer-visible byte arena so that the per-forward
+        rank-0 buffer broadcast (torch distributed.py:2214-2257) is a single peer-store kernel instead of NCCL calls."""
+        offs, total = [], 0
+        for b in self.modules_buffers:
+            offs.append(total)
+            total += (b.numel() * b.element_size() + 15) // 16 * 16
+        arena = self.backend.symm.alloc(total)
+        raw = arena.local.view(torch.uint8)
+        for b, o in zip(self.modules_buffers, offs):
+            nb = b.numel() * b.element_size()
+            v = raw[o: o + nb].view(b.dtype).view(b.shape)
+            v.copy_(b)
+            b.data = v
+        self._buffer_arena = arena
+        self._buffer_bytes = total
+        self._buffer_state = self.backend.symm.new_state()
+        from .symm import ptr_array
+        self._buffer_dst = ptr_array([p for r, p in enumerate(arena.peer_ptrs) if r != 0])
+
     def _sync_buffers(self):
+        if self._buffer_arena is not None:
+            from .. import _native
+            dev = self._params[0].device
+            _native.check(self.backend.lib.dmp_broadcast(self._buffer_arena.peer_ptrs[0], self._buffer_dst, self.world_size - 1, None,
+                                                         None, self._buffer_bytes, self._buffer_state.ptrs, self.rank, self.world_size,
+                                                         1 if self.rank == 0 else 0, 8, torch.cuda.current_stream(dev).cuda_stream),
+                          "buffer broadcast")
+            return
         if self.modules_buffers and self.world_size > 1:
             with torch.no_grad():
                 broadcast_coalesced_group(self.process_group, self.modules_buffers, BROADCAST_BUCKET_BYTES, src=0)

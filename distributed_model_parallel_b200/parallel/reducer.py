@@ -442,10 +442,15 @@ class Reducer:
         self._in_backward = True
         self._callback_queued = False
         self._unused_local = list(unused_indices)
+        self._direct_marked = set()
 
     def _grad_ready(self, i: int, param, direct: bool = False):
         if not self.require_sync or not self._in_backward:
             return
+        if direct:
+            self._direct_marked.add(i)
+        elif i in self._direct_marked:
+            return  # autograd still visits AccumulateGrad (with an undefined gradient) after a direct delivery
         if not self._callback_queued:
             self._callback_queued = True
             torch.autograd.Variable._execution_engine.queue_callback(self.finalize_backward)
@@ -453,14 +458,13 @@ class Reducer:
                 self._mark(u, unused=True)
         bk, k = self.slot_of[i]
         view = bk.views[k]
-        if not direct:
-            g = param.grad
-            if g is None:
-                view.zero_()
-            elif g.data_ptr() != view.data_ptr():
-                view.copy_(g)
-                if self.grad_as_view:
-                    param.grad = view
+        g = param.grad
+        if g is None:
+            view.zero_()
+        elif g.data_ptr() != view.data_ptr():  # gradient lives elsewhere (plain autograd tensor, another arena)
+            view.copy_(g)
+            if self.grad_as_view and not direct:
+                param.grad = view
         self._mark(i, unused=False)
 
     def _mark(self, i: int, unused: bool):
