@@ -252,6 +252,91 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
 # ----------------------------------------------------------------------------------------------------
 # fused conv -> (BatchNorm) -> (+residual) -> (ReLU)
 # ----------------------------------------------------------------------------------------------------
+def _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync):
+    """Train/eval BatchNorm (+residual, +ReLU) of a channels-last bf16 tensor. Returns (out, mean, invstd, count, training)."""
+    lib = _k()
+    sp = _sp()
+    N, C, Ho, Wo = y_raw.shape
+    M = N * Ho * Wo
+    dev = y_raw.device
+    training = bn.training or (bn.running_mean is None)
+    if training:
+        accum = torch.empty(2 * C, device=dev, dtype=torch.float64)
+        mean = torch.empty(C, device=dev, dtype=torch.float32)
+        invstd = torch.empty(C, device=dev, dtype=torch.float32)
+        scale = torch.empty(C, device=dev, dtype=torch.float32)
+        shift = torch.empty(C, device=dev, dtype=torch.float32)
+        _ck(lib.dmp_bn_stats(y_raw.data_ptr(), 1, M, C, accum.data_ptr(), sp), "bn stats")
+        count = float(M)
+        if sync is not None:
+            accum, count = sync.reduce_stats(bn._dmp_key, accum, M)
+        mom = bn.momentum
+        if bn.track_running_stats and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked.add_(1)
+            if mom is None:
+                mom = 1.0 / float(bn.num_batches_tracked)
+        rm = bn.running_mean if bn.track_running_stats else None
+        rv = bn.running_var if bn.track_running_stats else None
+        _ck(lib.dmp_bn_finalize(accum.data_ptr(), count, _native.ptr(gamma), _native.ptr(beta), _native.ptr(rm), _native.ptr(rv),
+                                float(mom if mom is not None else 0.1), float(bn.eps), mean.data_ptr(), invstd.data_ptr(),
+                                scale.data_ptr(), shift.data_ptr(), C, sp), "bn finalize")
+    else:
+        invstd = torch.rsqrt(bn.running_var + bn.eps)
+        mean = bn.running_mean
+        g = gamma if gamma is not None else torch.ones_like(invstd)
+        scale = (g * invstd).float()
+        shift = ((beta if beta is not None else 0) - mean * scale).float()
+        count = float(M)
+    out = torch.empty_like(y_raw)
+    _ck(lib.dmp_bn_apply(y_raw.data_ptr(), 1, scale.data_ptr(), shift.data_ptr(), _native.ptr(residual), out.data_ptr(), M, C,
+                         1 if relu else 0, sp), "bn apply")
+    _note("bn:fused")
+    return out, mean, invstd, count, training
+
+
+def _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu, needs_gamma, needs_beta):
+    """Returns (dy wrt the BN input, dres or None, dgamma, dbeta)."""
+    lib = _k()
+    sp = _sp()
+    N, C, Ho, Wo = y_raw.shape
+    M = N * Ho * Wo
+    dres_t = None
+    if ctx.bn_train:
+        dy = torch.empty_like(y_raw)
+        dres_t = torch.empty_like(y_raw) if ctx.has_res else None
+        accum = torch.empty(2 * C, device=y_raw.device, dtype=torch.float64)
+        _ck(lib.dmp_bn_bwd_reduce(dout.data_ptr(), _native.ptr(out), y_raw.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(), M, C,
+                                  1 if relu else 0, accum.data_ptr(), sp), "bn bwd reduce")
+        accum_g = accum
+        if ctx.sync is not None:
+            accum_g = ctx.sync.reduce_grads(bn._dmp_key, accum)
+        _ck(lib.dmp_bn_bwd_dx(dout.data_ptr(), _native.ptr(out), y_raw.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(),
+                              _native.ptr(gamma), accum_g.data_ptr(), ctx.count, dy.data_ptr(), _native.ptr(dres_t), M, C,
+                              1 if relu else 0, sp), "bn bwd dx")
+
+        def write_dgamma(dst, accumulate):
+            _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), dst.data_ptr(), None, C, 1 if accumulate else 0, sp), "bn dgamma")
+
+        def write_dbeta(dst, accumulate):
+            _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), None, dst.data_ptr(), C, 1 if accumulate else 0, sp), "bn dbeta")
+
+        dgamma = _deliver_grad(bn.weight, write_dgamma) if needs_gamma else None
+        dbeta = _deliver_grad(bn.bias, write_dbeta) if needs_beta else None
+        return dy, dres_t, dgamma, dbeta
+    # eval-mode BN: y = x*scale + shift with constant statistics
+    g = dout.float()
+    if relu:
+        g = torch.where(out > 0, g, torch.zeros_like(g))
+    if ctx.has_res:
+        dres_t = g.to(torch.bfloat16)
+    sc = (gamma if gamma is not None else 1.0) * invstd
+    dy = (g * sc.view(1, -1, 1, 1)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    xh = (y_raw.float() - mean.view(1, -1, 1, 1)) * invstd.view(1, -1, 1, 1)
+    dgamma = (g * xh).sum((0, 2, 3)) if needs_gamma else None
+    dbeta = g.sum((0, 2, 3)) if needs_beta else None
+    return dy, dres_t, dgamma, dbeta
+
+
 class _ConvBNAct(torch.autograd.Function):
     """CUDA path. Inputs: x, conv weight, bn weight, bn bias, residual (the last three may be None)."""
 
@@ -265,9 +350,6 @@ class _ConvBNAct(torch.autograd.Function):
         if kind == "pw" and conv.stride != (1, 1):
             conv._dmp_in_hw = (x.shape[2], x.shape[3])
         y_raw, x_saved = _conv_fwd_cuda(x, w, conv, kind)
-        N, C, Ho, Wo = y_raw.shape
-        M = N * Ho * Wo
-        dev = y_raw.device
         ctx.conv, ctx.bn, ctx.relu, ctx.kind, ctx.sync = conv, bn, relu, kind, sync
         ctx.has_res = residual is not None
         ctx.x_needs_grad = ctx.needs_input_grad[0]
@@ -283,40 +365,7 @@ class _ConvBNAct(torch.autograd.Function):
             ctx.save_for_backward(x_saved, w, out if relu else None)
             ctx.bn_train = False
             return out
-        training = bn.training or (bn.running_mean is None)
-        scale = torch.empty(C, device=dev, dtype=torch.float32)
-        shift = torch.empty(C, device=dev, dtype=torch.float32)
-        if training:
-            accum = torch.empty(2 * C, device=dev, dtype=torch.float64)
-            mean = torch.empty(C, device=dev, dtype=torch.float32)
-            invstd = torch.empty(C, device=dev, dtype=torch.float32)
-            _ck(lib.dmp_bn_stats(y_raw.data_ptr(), 1, M, C, accum.data_ptr(), sp), "bn stats")
-            count = float(M)
-            if sync is not None:
-                accum, count = sync.reduce_stats(accum, M)
-            mom = bn.momentum
-            if bn.track_running_stats and bn.num_batches_tracked is not None:
-                bn.num_batches_tracked.add_(1)
-                if mom is None:
-                    mom = 1.0 / float(bn.num_batches_tracked)
-            rm = bn.running_mean if bn.track_running_stats else None
-            rv = bn.running_var if bn.track_running_stats else None
-            _ck(lib.dmp_bn_finalize(accum.data_ptr(), count, _native.ptr(gamma), _native.ptr(beta), _native.ptr(rm),
-                                    _native.ptr(rv), float(mom if mom is not None else 0.1), float(bn.eps), mean.data_ptr(),
-                                    invstd.data_ptr(), scale.data_ptr(), shift.data_ptr(), C, sp), "bn finalize")
-            ctx.count = count
-        else:
-            invstd = torch.rsqrt(bn.running_var + bn.eps)
-            mean = bn.running_mean
-            g = gamma if gamma is not None else torch.ones_like(invstd)
-            scale = (g * invstd).float()
-            shift = ((beta if beta is not None else 0) - mean * scale).float()
-            ctx.count = float(M)
-        out = torch.empty_like(y_raw)
-        _ck(lib.dmp_bn_apply(y_raw.data_ptr(), 1, scale.data_ptr(), shift.data_ptr(), _native.ptr(residual), out.data_ptr(), M, C,
-                             1 if relu else 0, sp), "bn apply")
-        _note("bn:fused")
-        ctx.bn_train = training
+        out, mean, invstd, ctx.count, ctx.bn_train = _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync)
         ctx.save_for_backward(x_saved, w, out if relu else None, y_raw, mean, invstd, gamma)
         return out
 
@@ -339,45 +388,34 @@ class _ConvBNAct(torch.autograd.Function):
             dgamma = dbeta = None
         else:
             x, w, out, y_raw, mean, invstd, gamma = ctx.saved_tensors
-            N, C, Ho, Wo = y_raw.shape
-            M = N * Ho * Wo
-            dy = torch.empty_like(y_raw)
-            dres_t = torch.empty_like(y_raw) if ctx.has_res else None
-            if ctx.bn_train:
-                accum = torch.empty(2 * C, device=y_raw.device, dtype=torch.float64)
-                _ck(lib.dmp_bn_bwd_reduce(dout.data_ptr(), _native.ptr(out), y_raw.data_ptr(), 1, mean.data_ptr(),
-                                          invstd.data_ptr(), M, C, 1 if relu else 0, accum.data_ptr(), sp), "bn bwd reduce")
-                accum_g = accum
-                if ctx.sync is not None:
-                    accum_g = ctx.sync.reduce_grads(accum)
-                _ck(lib.dmp_bn_bwd_dx(dout.data_ptr(), _native.ptr(out), y_raw.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(),
-                                      _native.ptr(gamma), accum_g.data_ptr(), ctx.count, dy.data_ptr(), _native.ptr(dres_t), M, C,
-                                      1 if relu else 0, sp), "bn bwd dx")
-
-                def write_dgamma(dst, accumulate):
-                    _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), dst.data_ptr(), None, C, 1 if accumulate else 0, sp), "bn dgamma")
-
-                def write_dbeta(dst, accumulate):
-                    _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), None, dst.data_ptr(), C, 1 if accumulate else 0, sp), "bn dbeta")
-
-                dgamma = _deliver_grad(bn.weight, write_dgamma) if ctx.needs_input_grad[2] else None
-                dbeta = _deliver_grad(bn.bias, write_dbeta) if ctx.needs_input_grad[3] else None
-            else:
-                # eval-mode BN: y = x*scale + shift with constant statistics
-                g = dout.float()
-                if relu:
-                    g = torch.where(out > 0, g, torch.zeros_like(g))
-                if ctx.has_res:
-                    dres_t = g.to(torch.bfloat16)
-                sc = (gamma if gamma is not None else 1.0) * invstd
-                dy = (g * sc.view(1, -1, 1, 1)).to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-                xh = (y_raw.float() - mean.view(1, -1, 1, 1)) * invstd.view(1, -1, 1, 1)
-                dgamma = (g * xh).sum((0, 2, 3)) if ctx.needs_input_grad[2] else None
-                dbeta = g.sum((0, 2, 3)) if ctx.needs_input_grad[3] else None
-            dres = dres_t
+            dy, dres, dgamma, dbeta = _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu,
+                                                        ctx.needs_input_grad[2], ctx.needs_input_grad[3])
         dx, write_dw = _conv_bwd_cuda(dy, x, w, conv, kind, ctx.x_needs_grad)
         dw = _deliver_grad(conv.weight, write_dw) if ctx.needs_input_grad[1] else None
         return dx, dw, dgamma, dbeta, dres, None, None, None, None
+
+
+class _BNAct(torch.autograd.Function):
+    """BatchNorm (+residual, +ReLU) without a convolution in front (bare BN / SyncBatchNorm modules)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, bn, relu, sync):
+        x = _as_cl_bf16(x)
+        ctx.bn, ctx.relu, ctx.sync = bn, relu, sync
+        ctx.has_res = residual is not None
+        if residual is not None:
+            residual = _as_cl_bf16(residual)
+        out, mean, invstd, ctx.count, ctx.bn_train = _bn_forward_cuda(x, gamma, beta, residual, bn, relu, sync)
+        ctx.save_for_backward(out if relu else None, x, mean, invstd, gamma)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        out, x, mean, invstd, gamma = ctx.saved_tensors
+        dout = _as_cl_bf16(dout)
+        dy, dres, dgamma, dbeta = _bn_backward_cuda(ctx, dout, out, x, mean, invstd, gamma, ctx.bn, ctx.relu,
+                                                    ctx.needs_input_grad[1], ctx.needs_input_grad[2])
+        return dy, dgamma, dbeta, dres, None, None, None
 
 
 def _conv_bn_act_reference(x, conv, bn, relu, residual):
@@ -401,6 +439,25 @@ def conv_bn_act(x: torch.Tensor, conv: nn.Conv2d, bn: Optional[nn.Module] = None
     gamma = bn.weight if bn is not None else None
     beta = bn.bias if bn is not None else None
     return _ConvBNAct.apply(x, conv.weight, gamma, beta, residual, conv, bn, relu, sync)
+
+
+class _IdentityConv:
+    """Stand-in so a bare BatchNorm can reuse the fused op: y_raw = x."""
+    kernel_size, stride, padding, dilation, groups, bias, padding_mode = (1, 1), (1, 1), (0, 0), (1, 1), 1, None, "zeros"
+
+
+def batch_norm_act(x: torch.Tensor, bn: nn.Module, relu: bool = False, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``act(bn(x) + residual)`` on the kernel path (x channels-last bf16), reference path otherwise."""
+    if not _use_kernels(x) or x.dim() != 4 or x.shape[1] % 8 != 0:
+        y = F.batch_norm(x, bn.running_mean, bn.running_var, bn.weight, bn.bias, bn.training or bn.running_mean is None,
+                         bn.momentum if bn.momentum is not None else 0.1, bn.eps)
+        if residual is not None:
+            y = y + residual
+        return F.relu(y) if relu else y
+    sync = getattr(bn, "_dmp_sync", None)
+    if sync is not None and not (bn.training and sync.world_size > 1):
+        sync = None
+    return _BNAct.apply(x, bn.weight, bn.bias, residual, bn, relu, sync)
 
 
 # ----------------------------------------------------------------------------------------------------

@@ -129,6 +129,11 @@ def broadcast_coalesced(tensors: Sequence[torch.Tensor], devices: Sequence, buff
     outputs: List[List[torch.Tensor]] = [list(tensors)] + [[None] * len(tensors) for _ in devs[1:]]
     if len(devs) == 1:
         return outputs
+    with torch.no_grad():  # a raw data movement op: differentiability is added by replicate.Broadcast
+        return _broadcast_coalesced_impl(tensors, devs, outputs, buffer_size)
+
+
+def _broadcast_coalesced_impl(tensors, devs, outputs, buffer_size):
     src_dev = tensors[0].device
     chunks = list(take_tensors(tensors, buffer_size))
     pos = {id(t): i for i, t in enumerate(tensors)}

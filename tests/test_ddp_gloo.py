@@ -1,0 +1,121 @@
+"""DistributedDataParallel on CPU/gloo, world_size 2 (BASELINE.json config 1): parity with torch DDP."""
+import copy
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+from _dist_utils import run_gloo
+
+
+def _small_net():
+    from distributed_model_parallel_b200.models import ResNet18
+    return ResNet18()
+
+
+def _w_parity(rank, world):
+    from distributed_model_parallel_b200.parallel import DistributedDataParallel as DDP
+
+    torch.manual_seed(rank)  # different initial weights per rank: init sync must make them equal
+    base = _small_net()
+    ours = DDP(copy.deepcopy(base), bucket_cap_mb=5)
+    ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base), bucket_cap_mb=5)
+    o1 = torch.optim.SGD(ours.parameters(), lr=0.1, momentum=0.9)
+    o2 = torch.optim.SGD(ref.parameters(), lr=0.1, momentum=0.9)
+    for it in range(3):
+        torch.manual_seed(100 + 10 * rank + it)
+        x, y = torch.randn(4, 3, 32, 32), torch.randint(0, 10, (4,))
+        for m, o in ((ours, o1), (ref, o2)):
+            o.zero_grad()
+            F.cross_entropy(m(x), y).backward()
+            o.step()
+        for (n, p), q in zip(ours.module.named_parameters(), ref.module.parameters()):
+            assert torch.allclose(p.grad, q.grad, atol=1e-6, rtol=1e-5), (it, n)
+            assert torch.allclose(p, q, atol=1e-6, rtol=1e-5), (it, n)
+    assert ours.reducer.stats["rebuilds"] == 1
+    assert len(ours.reducer.buckets) > 1
+    assert all(k.startswith("module.") for k in ours.state_dict())
+    # buffers (BN running stats) are re-broadcast from rank 0 at every forward, exactly like torch's wrapper
+    for (n, b), c in zip(ours.module.named_buffers(), ref.module.buffers()):
+        assert torch.allclose(b.float(), c.float(), atol=1e-6), n
+
+
+def test_ddp_matches_torch_ddp_resnet18():
+    run_gloo(_w_parity, 2)
+
+
+class _Branchy(nn.Module):
+    def __init__(self):
+        super().__init__()
+        self.a, self.b, self.c = nn.Linear(8, 8), nn.Linear(8, 8), nn.Linear(8, 4)
+
+    def forward(self, x, use_b=True):
+        h = self.a(x)
+        if use_b:
+            h = self.b(h)
+        return self.c(h)
+
+
+def _w_features(rank, world):
+    from distributed_model_parallel_b200.parallel import DistributedDataParallel as DDP
+
+    torch.manual_seed(0)
+    base = _Branchy()
+    # --- no_sync accumulates locally, the next synced backward reduces the sum
+    ours = DDP(copy.deepcopy(base))
+    ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base))
+    torch.manual_seed(rank + 1)
+    xs = [torch.randn(3, 8) for _ in range(2)]
+    for m in (ours, ref):
+        with m.no_sync():
+            m(xs[0]).sum().backward()
+        m(xs[1]).sum().backward()
+    for p, q in zip(ours.module.parameters(), ref.module.parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-6)
+    # --- unused parameters: error without the flag, zeros-contributing with it
+    strict = DDP(copy.deepcopy(base))
+    with pytest.raises(RuntimeError, match="no gradient"):
+        strict(xs[0], use_b=False).sum().backward()
+    lax = DDP(copy.deepcopy(base), find_unused_parameters=True)
+    ref2 = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base), find_unused_parameters=True)
+    for m in (lax, ref2):
+        m(xs[0], use_b=False).sum().backward()
+    for (n, p), q in zip(lax.module.named_parameters(), ref2.module.parameters()):
+        if q.grad is None:
+            assert p.grad is None or float(p.grad.abs().max()) == 0.0, n
+        else:
+            assert torch.allclose(p.grad, q.grad, atol=1e-6), n
+    # --- communication hook replaces the built-in all-reduce
+    calls = []
+
+    def hook(state, bucket):
+        calls.append(bucket.index())
+        t = bucket.buffer().clone()
+        fut = dist.all_reduce(t, async_op=True).get_future()
+        return fut.then(lambda f: f.value()[0] / world)
+
+    hooked = DDP(copy.deepcopy(base))
+    hooked.register_comm_hook(None, hook)
+    hooked(xs[1]).sum().backward()
+    plain = DDP(copy.deepcopy(base))
+    plain(xs[1]).sum().backward()
+    assert calls
+    for p, q in zip(hooked.module.parameters(), plain.module.parameters()):
+        assert torch.allclose(p.grad, q.grad, atol=1e-6)
+    # --- constructor validation
+    frozen = copy.deepcopy(base)
+    for p in frozen.parameters():
+        p.requires_grad_(False)
+    with pytest.raises(RuntimeError, match="doesn't have any parameter"):
+        DDP(frozen)
+    # --- gradient_as_bucket_view: grads alias the flat bucket
+    view = DDP(copy.deepcopy(base), gradient_as_bucket_view=True)
+    view(xs[0]).sum().backward()
+    bk = view.reducer.buckets[0]
+    assert bk.params[0].grad.data_ptr() == bk.views[0].data_ptr()
+
+
+def test_ddp_no_sync_unused_hooks_validation():
+    run_gloo(_w_features, 2)
