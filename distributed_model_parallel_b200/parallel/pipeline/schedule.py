@@ -75,6 +75,30 @@ class PipelineStage:
         self._probe_key = None
         self._keepalive, self._send_works = [], []
         self.stats = {"steps": 0, "p2p_messages": 0}
+        if self.device.type == "cuda" and num_stages > 1:
+            self._warmup_p2p()
+
+    def _warmup_p2p(self):
+        """Establish the NCCL p2p connections of every neighbour pair with a SYMMETRIC grouped send+recv on both sides.
+        NCCL sets up a pair's send and receive connectors on first use and the two ranks must agree on what is being
+        connected; the schedules later issue asymmetric groups (one side send+recv, the other only recv), which fails
+        on a cold pair ("Message truncated" inside ncclGroupEnd)."""
+        def pair(peer):
+            a = torch.zeros(8, device=self.device)
+            b = torch.empty(8, device=self.device)
+            p2p.wait_all(p2p.batched([("send", a, peer), ("recv", b, peer)], self.group))
+
+        for parity in (0, 1):                      # even pairs first, then odd pairs: no rank is in two exchanges at once
+            if self.stage % 2 == parity and self.next is not None:
+                pair(self.next)
+            if self.stage % 2 != parity and self.prev is not None:
+                pair(self.prev)
+        if self.W > 2:                             # the logits ring / target hand-off pair (first <-> last)
+            if self.first:
+                pair(self.rank_last)
+            elif self.last:
+                pair(self.rank0)
+        torch.cuda.synchronize(self.device)
 
     # ------------------------------------------------------------------------------------------ control plane
     CTRL_LEN = 4 + p2p.HEADER_LEN
@@ -140,7 +164,7 @@ class PipelineStage:
             buf = recv_meta.empty(self.device)
             ops.append(("recv", p2p.wire_view(buf), recv_peer))
         if _DEBUG:
-            print("[pp stage %d] exchange %s" % (self.stage, [(k, tuple(t.shape), peer) for k, t, peer in ops]), flush=True)
+            print("[pp stage %d] exchange %s" % (self.stage, [(k, tuple(t.shape), str(t.dtype), t.is_contiguous(), peer) for k, t, peer in ops]), flush=True)
         works = p2p.batched(ops, self.group)
         self.stats["p2p_messages"] += len(ops)
         if recv_meta is not None and len(works) == len(ops):
