@@ -240,8 +240,8 @@ int bn_grid(long long nvec, int C, int vec) {
     long long a = C, b = per_block;
     while (b) { long long t = a % b; a = b; b = t; }
     int q = (int)(C / a);
-    long long want = (nvec + BN_THREADS * 4 - 1) / (BN_THREADS * 4);
-    long long cap = (long long)dmp_num_sms() * 4;
+    long long want = (nvec + BN_THREADS * 8 - 1) / (BN_THREADS * 8);
+    long long cap = (long long)dmp_num_sms() * 2;  // fewer, longer-lived blocks: each pays 2*C double atomics at its end
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     long long g = ((want + q - 1) / q) * q;

@@ -10,10 +10,27 @@ namespace {
 
 constexpr int DW_THREADS = 256;
 
+// 8 channels x 9 taps = 72 contiguous weights of the [C,1,3,3] tensor, fetched with 16-byte loads
+// (ch0 is a multiple of 8, so the 144-byte / 288-byte block is 16-byte aligned).
 template <typename WT>
-__device__ __forceinline__ void load_w72(const WT* __restrict__ w, int ch0, float* out /*[8][9]*/) {
+__device__ __forceinline__ void load_w72(const WT* __restrict__ w, int ch0, float* out /*[8][9]*/);
+template <>
+__device__ __forceinline__ void load_w72<bf16>(const bf16* __restrict__ w, int ch0, float* out) {
+    const int4* p = (const int4*)(w + ch0 * 9);
 #pragma unroll
-    for (int i = 0; i < 72; ++i) out[i] = to_f32<WT>(w[ch0 * 9 + i]);
+    for (int i = 0; i < 9; ++i) {
+        int4 raw = __ldg(p + i);
+        bf16x8_to_float(*(bf16x8*)&raw, out + i * 8);
+    }
+}
+template <>
+__device__ __forceinline__ void load_w72<float>(const float* __restrict__ w, int ch0, float* out) {
+    const float4* p = (const float4*)(w + ch0 * 9);
+#pragma unroll
+    for (int i = 0; i < 18; ++i) {
+        float4 v = __ldg(p + i);
+        out[i * 4] = v.x; out[i * 4 + 1] = v.y; out[i * 4 + 2] = v.z; out[i * 4 + 3] = v.w;
+    }
 }
 
 __device__ __forceinline__ void load8(const bf16* p, float* f) {
@@ -103,6 +120,150 @@ dw_dgrad_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __r
     store8(dx + (((long long)n * H + hi) * W + wi) * C + ch0, acc);
 }
 
+// Strip version of the forward stencil: one thread produces TW horizontally adjacent output pixels of its 8 channels,
+// so every input vector of a row is loaded once and reused by up to 3 outputs (4.5 instead of 9 loads per output at
+// stride 1).  FLIP=true mirrors the taps: with stride 1 the data gradient is the same stencil applied to dy.
+template <typename WT, int STRIDE, int TW, bool FLIP>
+__global__ void __launch_bounds__(DW_THREADS)
+dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
+                int Ho, int Wo) {
+    constexpr int NC = (TW - 1) * STRIDE + 3;  // input columns feeding the strip
+    const int P = C >> 3;
+    const int tiles_w = (Wo + TW - 1) / TW;
+    const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
+    const long long total = (long long)N * Ho * tiles_w * P;
+    if (idx >= total) return;
+    const int cv = (int)(idx % P);
+    long long t = idx / P;
+    const int wt_ = (int)(t % tiles_w); t /= tiles_w;
+    const int ho = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    const int ch0 = cv * 8;
+    const int wo0 = wt_ * TW;
+    float wt[72];
+    load_w72<WT>(w, ch0, wt);
+    float acc[TW][8];
+#pragma unroll
+    for (int i = 0; i < TW; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+    const int wi0 = wo0 * STRIDE - 1;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+        const int hi = ho * STRIDE + kh - 1;
+        if (hi < 0 || hi >= H) continue;
+        const bf16* row = x + (((long long)n * H + hi) * W) * C + ch0;
+        float col[NC][8];
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const int wi = wi0 + c;
+            if (wi >= 0 && wi < W) load8(row + (long long)wi * C, col[c]);
+            else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) col[c][j] = 0.f;
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < TW; ++i)
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int tap = FLIP ? ((2 - kh) * 3 + (2 - kw)) : (kh * 3 + kw);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) acc[i][j] += col[i * STRIDE + kw][j] * wt[j * 9 + tap];
+            }
+    }
+#pragma unroll
+    for (int i = 0; i < TW; ++i)
+        if (wo0 + i < Wo) store8(y + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0, acc[i]);
+}
+
+// Strip version of the weight gradient: per thread 8 channels x 9 taps of partial sums over a strided set of
+// (n, ho, strip) work items; dy and the three input rows of a strip are loaded once.  Partials of threads that share
+// a channel vector are pre-reduced with warp shuffles when the sharing pattern is a power of two, then combined in
+// shared memory and flushed with one atomic per (block, weight).
+template <int STRIDE, int TW>
+__global__ void __launch_bounds__(DW_THREADS)
+dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, float* __restrict__ dw, int N, int H, int W,
+                      int C, int Ho, int Wo) {
+    constexpr int NC = (TW - 1) * STRIDE + 3;
+    extern __shared__ float sm[];  // [groups_in_block][72]
+    const int P = C >> 3;
+    const int groups = P < DW_THREADS ? P : DW_THREADS;
+    for (int i = threadIdx.x; i < groups * 72; i += DW_THREADS) sm[i] = 0.f;
+    __syncthreads();
+    const long long tid = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
+    const long long nthreads = (long long)gridDim.x * DW_THREADS;  // multiple of P (host guarantees)
+    const int cv = (int)(tid % P);
+    const long long istride = nthreads / P;
+    const int tiles_w = (Wo + TW - 1) / TW;
+    const long long nitems = (long long)N * Ho * tiles_w;
+    const int ch0 = cv * 8;
+    float acc[72];
+#pragma unroll
+    for (int i = 0; i < 72; ++i) acc[i] = 0.f;
+    for (long long item = tid / P; item < nitems; item += istride) {
+        long long t = item;
+        const int wt_ = (int)(t % tiles_w); t /= tiles_w;
+        const int ho = (int)(t % Ho);
+        const int n = (int)(t / Ho);
+        const int wo0 = wt_ * TW;
+        // operands stay packed (8 bf16 = one int4) until the FMA that consumes them: halves the live registers
+        int4 g[TW];
+#pragma unroll
+        for (int i = 0; i < TW; ++i)
+            g[i] = (wo0 + i < Wo) ? *(const int4*)(dy + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0) : make_int4(0, 0, 0, 0);
+        const int wi0 = wo0 * STRIDE - 1;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int hi = ho * STRIDE + kh - 1;
+            if (hi < 0 || hi >= H) continue;
+            const bf16* row = x + (((long long)n * H + hi) * W) * C + ch0;
+            int4 col[NC];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                const int wi = wi0 + c;
+                col[c] = (wi >= 0 && wi < W) ? *(const int4*)(row + (long long)wi * C) : make_int4(0, 0, 0, 0);
+            }
+#pragma unroll
+            for (int i = 0; i < TW; ++i) {
+                float gf[8];
+                bf16x8_to_float(*(bf16x8*)&g[i], gf);
+#pragma unroll
+                for (int kw = 0; kw < 3; ++kw) {
+                    float cf[8];
+                    bf16x8_to_float(*(bf16x8*)&col[i * STRIDE + kw], cf);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[j * 9 + kh * 3 + kw] += gf[j] * cf[j];
+                }
+            }
+        }
+    }
+    // lanes l, l+P, l+2P, ... of a warp hold the same channel vector when P divides 32 (and the block base is a
+    // multiple of P): fold them with xor-shuffles so that only P lanes per warp touch shared memory
+    const bool pow2 = (P & (P - 1)) == 0 && P < 32;
+    if (pow2) {
+#pragma unroll
+        for (int i = 0; i < 72; ++i) {
+            float v = acc[i];
+            for (int o = 16; o >= P; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            acc[i] = v;
+        }
+    }
+    const int slot = (P < DW_THREADS) ? cv : threadIdx.x;
+    if (!pow2 || (threadIdx.x & 31) < P) {
+#pragma unroll
+        for (int i = 0; i < 72; ++i) atomicAdd(&sm[slot * 72 + i], acc[i]);
+    }
+    __shared__ int s_cv[DW_THREADS];
+    s_cv[slot] = cv;  // identical value from every writer of a slot
+    __syncthreads();
+    for (int i = threadIdx.x; i < groups * 72; i += DW_THREADS) {
+        const int sl = i / 72, k = i % 72;
+        const float v = sm[i];
+        if (v != 0.f) atomicAdd(&dw[(long long)s_cv[sl] * 72 + k], v);
+    }
+}
+
 // dw[c,kh,kw] = sum_{n,ho,wo} dy[n,ho,wo,c] * x[n,ho*s+kh-1,wo*s+kw-1,c]
 // Each thread keeps 8x9 partial sums for its channel vector over a strided subset of output pixels,
 // partials are combined per block in shared memory and flushed with one fp32 atomic per (block, weight).
@@ -174,14 +335,17 @@ DMP_API int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y
                               cudaStream_t stream) {
     if (int rc = dw_check("dmp_dwconv3x3_fwd", N, H, W, C, stride)) return rc;
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
-    const long long total = (long long)N * Ho * Wo * (C / 8);
-    const int grid = dmp_ceil_div(total, DW_THREADS);
-    if (w_dtype == 0)
-        dw_fwd_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo,
-                                                              stride);
-    else
-        dw_fwd_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo,
-                                                             stride);
+    if (stride == 1) {
+        const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo);
+        else dw_strip_kernel<bf16, 1, 4, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo);
+    } else {
+        const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo);
+        else dw_strip_kernel<bf16, 2, 2, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo);
+    }
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
@@ -191,14 +355,19 @@ DMP_API int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void
                                 int stride, cudaStream_t stream) {
     if (int rc = dw_check("dmp_dwconv3x3_dgrad", N, H, W, C, stride)) return rc;
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
-    const long long total = (long long)N * H * W * (C / 8);
-    const int grid = dmp_ceil_div(total, DW_THREADS);
-    if (w_dtype == 0)
-        dw_dgrad_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, Ho,
-                                                                Wo, stride);
-    else
-        dw_dgrad_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, Ho,
-                                                               Wo, stride);
+    if (stride == 1) {  // dx = dy (*) flipped taps: the forward strip stencil applied to dy (Ho == H, Wo == W)
+        const long long total = (long long)N * H * ((W + 3) / 4) * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W);
+        else dw_strip_kernel<bf16, 1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, H, W);
+    } else {
+        const long long total = (long long)N * H * W * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0)
+            dw_dgrad_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, Ho, Wo, stride);
+        else
+            dw_dgrad_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, Ho, Wo, stride);
+    }
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
@@ -215,9 +384,10 @@ DMP_API int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N,
     int a = P, b = DW_THREADS;
     while (b) { int t = a % b; a = b; b = t; }
     const int q = P / a;
-    const long long npix = (long long)N * Ho * Wo;
-    long long want = (npix * P + (long long)DW_THREADS * 16 - 1) / ((long long)DW_THREADS * 16);  // ~16 pixels per thread
-    const long long cap = (long long)dmp_num_sms() * 4;
+    const int TWs = stride == 1 ? 4 : 2;
+    const long long nitems = (long long)N * Ho * ((Wo + TWs - 1) / TWs);
+    long long want = (nitems * P + (long long)DW_THREADS * 8 - 1) / ((long long)DW_THREADS * 8);  // ~8 strips per thread
+    const long long cap = (long long)dmp_num_sms() * 2;
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     const int grid = (int)(((want + q - 1) / q) * q);
@@ -228,11 +398,13 @@ DMP_API int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N,
         int dev = 0;
         cudaGetDevice(&dev);
         if (!(configured_mask & (1 << dev))) {
-            DMP_CHECK_CUDA(cudaFuncSetAttribute(dw_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
+            DMP_CHECK_CUDA(cudaFuncSetAttribute(dw_wgrad_strip_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
+            DMP_CHECK_CUDA(cudaFuncSetAttribute(dw_wgrad_strip_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
             configured_mask |= 1 << dev;
         }
     }
-    dw_wgrad_kernel<<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo, stride);
+    if (stride == 1) dw_wgrad_strip_kernel<1, 4><<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
+    else dw_wgrad_strip_kernel<2, 2><<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;

@@ -49,9 +49,13 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     if (mbar_try_wait(bar, parity)) return;
-    unsigned long long t0 = globaltimer_ns();
+    unsigned long long t0 = 0;
+    unsigned spins = 0;
     while (!mbar_try_wait(bar, parity)) {
-        if (globaltimer_ns() - t0 > WAIT_TIMEOUT_NS) {
+        if ((++spins & 0xFFF) != 0) continue;  // read the (slow) global timer only every 4096 failed probes
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > WAIT_TIMEOUT_NS) {
             printf("dmp gemm_tcgen05: mbarrier wait timed out (block %d,%d,%d thread %d)\n", blockIdx.x, blockIdx.y,
                    blockIdx.z, threadIdx.x);
             __trap();
@@ -134,13 +138,32 @@ __host__ __device__ constexpr uint32_t make_idesc(int n, int a_mn_major, int b_m
 
 struct GemmParams {
     int M, N, K;
-    int k_blocks_per_split;  // split-K: each blockIdx.z handles this many BK blocks
+    int k_blocks_per_split;  // split-K: each split handles this many BK blocks
+    int splits;
+    int m_tiles, n_tiles;
     void* D;
     long long ldd;
     const float* bias;  // per-column (N) fp32 bias, nullable
     int epi;            // 0: store bf16, 1: store fp32, 2: atomic add fp32
 };
 
+__device__ __forceinline__ void tmem_ld_32(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]),
+          "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]),
+          "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// Persistent kernel: CTA b processes work items b, b+gridDim.x, ...  A work item is one 128 x BN output tile of one
+// K split.  Two TMEM accumulator buffers let the epilogue of item i overlap the TMA/MMA of item i+1.
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -149,24 +172,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int B_BYTES = B_ROWS * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    constexpr uint32_t TMEM_COLS = BN < 32 ? 32 : BN;
+    constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;
+    constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;  // double-buffered accumulator (power of two: 64/128/256)
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint64_t* full_bar = (uint64_t*)(smem + STAGES * STAGE_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
-    uint64_t* tmem_full_bar = empty_bar + STAGES;
-    uint32_t* tmem_ptr_smem = (uint32_t*)(tmem_full_bar + 1);
+    uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
+    uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
+    uint32_t* tmem_ptr_smem = (uint32_t*)(tmem_empty_bar + 2);
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
-    const int m0 = blockIdx.x * BM;
-    const int n0 = blockIdx.y * BN;
     const int total_kb = (p.K + BK - 1) / BK;
-    const int kb_begin = blockIdx.z * p.k_blocks_per_split;
-    int kb_end = kb_begin + p.k_blocks_per_split;
-    if (kb_end > total_kb) kb_end = total_kb;
-    const int num_kb = kb_end - kb_begin;  // host guarantees >= 1
+    const int tiles_mn = p.m_tiles * p.n_tiles;
+    const int num_items = tiles_mn * p.splits;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -175,7 +196,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(tmem_full_bar, 1);
+        for (int b = 0; b < 2; ++b) {
+            mbar_init(&tmem_full_bar[b], 1);
+            mbar_init(&tmem_empty_bar[b], 4);  // one arrive per epilogue warp
+        }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr_smem, TMEM_COLS);
@@ -187,27 +211,34 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0) {
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
-            for (int i = 0; i < num_kb; ++i) {
-                const int s = i % STAGES;
-                const uint32_t ph = (i / STAGES) & 1;
-                mbar_wait(&empty_bar[s], ph ^ 1);
-                uint8_t* sa = smem + s * STAGE_BYTES;
-                uint8_t* sb = sa + A_BYTES;
-                const int k0 = (kb_begin + i) * BK;
-                mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                if (A_MN) {
-                    // global A^T stored [K, M] (M contiguous): two boxes of {64 m, 64 k}
-                    tma_load_2d(sa, &tmA, &full_bar[s], m0, k0);
-                    tma_load_2d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0);
-                } else {
-                    tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);  // box {64 k, 128 m}
-                }
-                if (B_MN) {
+            int it = 0;  // global k-block counter -> smem ring position
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
+                const int split = item / tiles_mn, tile = item % tiles_mn;
+                const int m0 = (tile / p.n_tiles) * BM, n0 = (tile % p.n_tiles) * BN;
+                const int kb_begin = split * p.k_blocks_per_split;
+                int kb_end = kb_begin + p.k_blocks_per_split;
+                if (kb_end > total_kb) kb_end = total_kb;
+                for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&empty_bar[s], ph ^ 1);
+                    uint8_t* sa = smem + s * STAGE_BYTES;
+                    uint8_t* sb = sa + A_BYTES;
+                    const int k0 = kb * BK;
+                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    if (A_MN) {
+                        tma_load_2d(sa, &tmA, &full_bar[s], m0, k0);  // global A^T [K, M]: two boxes of {64 m, 64 k}
+                        tma_load_2d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0);
+                    } else {
+                        tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);  // box {64 k, 128 m}
+                    }
+                    if (B_MN) {
 #pragma unroll
-                    for (int c = 0; c < B_ROWS / 64; ++c)
-                        tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0);
-                } else {
-                    tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);  // box {64 k, BN n}
+                        for (int c = 0; c < B_ROWS / 64; ++c)
+                            tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0);
+                    } else {
+                        tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);  // box {64 k, BN n}
+                    }
                 }
             }
         }
@@ -215,81 +246,110 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // ------------------------------------------------------------------ MMA issuer
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc(BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
-            for (int i = 0; i < num_kb; ++i) {
-                const int s = i % STAGES;
-                const uint32_t ph = (i / STAGES) & 1;
-                mbar_wait(&full_bar[s], ph);
+            int it = 0, local = 0;
+            for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
+                const int split = item / tiles_mn;
+                const int kb_begin = split * p.k_blocks_per_split;
+                int kb_end = kb_begin + p.k_blocks_per_split;
+                if (kb_end > total_kb) kb_end = total_kb;
+                const int buf = local & 1;
+                const uint32_t acc_ph = (local >> 1) & 1;
+                mbar_wait(&tmem_empty_bar[buf], acc_ph ^ 1);  // epilogue has drained this accumulator
                 tcgen05_fence_after();
-                const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
-                const uint32_t sb = sa + A_BYTES;
-                const int k0 = (kb_begin + i) * BK;
-                int ksteps = (p.K - k0 + 15) / 16;  // skip the zero-filled K tail
-                if (ksteps > BK / 16) ksteps = BK / 16;
-                for (int k = 0; k < ksteps; ++k) {
-                    // K-major: 16 bf16 = 32 B inside the 128 B swizzle row.  MN-major: 16 k-rows = 2 KB.
-                    const uint64_t adesc = A_MN ? make_smem_desc(sa + k * 2048, A_BYTES / 2, 1024)
-                                                : make_smem_desc(sa + k * 32, 16, 1024);
-                    const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024)
-                                                : make_smem_desc(sb + k * 32, 16, 1024);
-                    umma_bf16(tmem_base, adesc, bdesc, idesc, (i > 0 || k > 0) ? 1u : 0u);
+                const uint32_t tmem_d = tmem_base + buf * ACC_COLS;
+                for (int kb = kb_begin; kb < kb_end; ++kb, ++it) {
+                    const int s = it % STAGES;
+                    const uint32_t ph = (it / STAGES) & 1;
+                    mbar_wait(&full_bar[s], ph);
+                    tcgen05_fence_after();
+                    const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
+                    const uint32_t sb = sa + A_BYTES;
+                    const int k0 = kb * BK;
+                    int ksteps = (p.K - k0 + 15) / 16;  // skip the zero-filled K tail
+                    if (ksteps > BK / 16) ksteps = BK / 16;
+                    for (int k = 0; k < ksteps; ++k) {
+                        // K-major: 16 bf16 = 32 B inside the 128 B swizzle row.  MN-major: 16 k-rows = 2 KB.
+                        const uint64_t adesc = A_MN ? make_smem_desc(sa + k * 2048, A_BYTES / 2, 1024)
+                                                    : make_smem_desc(sa + k * 32, 16, 1024);
+                        const uint64_t bdesc = B_MN ? make_smem_desc(sb + k * 2048, 64 * BK * 2, 1024)
+                                                    : make_smem_desc(sb + k * 32, 16, 1024);
+                        umma_bf16(tmem_d, adesc, bdesc, idesc, (kb > kb_begin || k > 0) ? 1u : 0u);
+                    }
+                    umma_commit(&empty_bar[s]);  // frees the smem slot once the MMAs above have read it
                 }
-                umma_commit(&empty_bar[s]);  // frees the smem slot once the MMAs above have read it
+                umma_commit(&tmem_full_bar[buf]);  // accumulator complete -> epilogue
             }
-            umma_commit(tmem_full_bar);  // accumulator complete -> epilogue
         }
     } else {
         // ------------------------------------------------------------------ epilogue (warps 2..5)
         const int lane_grp = warp & 3;  // TMEM lane quarter this warp may access
-        const int row = m0 + lane_grp * 32 + lane;
-        mbar_wait(tmem_full_bar, 0);
-        tcgen05_fence_after();
-        const uint32_t taddr_row = tmem_base + ((uint32_t)(lane_grp * 32) << 16);
+        int local = 0;
+        for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
+            const int tile = item % tiles_mn;
+            const int m0 = (tile / p.n_tiles) * BM, n0 = (tile % p.n_tiles) * BN;
+            const int buf = local & 1;
+            const uint32_t acc_ph = (local >> 1) & 1;
+            const int row = m0 + lane_grp * 32 + lane;
+            mbar_wait(&tmem_full_bar[buf], acc_ph);
+            tcgen05_fence_after();
+            const uint32_t taddr_row = tmem_base + buf * ACC_COLS + ((uint32_t)(lane_grp * 32) << 16);
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 16) {
-            if (n0 + c0 >= p.N) break;  // warp-uniform
-            uint32_t r[16];
-            tmem_ld_16(taddr_row + c0, r);
-            tmem_ld_wait();
-            if (row < p.M) {
-                float v[16];
+            for (int c0 = 0; c0 < BN; c0 += 32) {
+                if (n0 + c0 >= p.N) break;  // warp-uniform
+                uint32_t r[32];
+                if (BN >= 32) tmem_ld_32(taddr_row + c0, r);
+                else tmem_ld_16(taddr_row + c0, r);
+                tmem_ld_wait();
+                if (row < p.M) {
+                    const int n = n0 + c0;
+                    float v[32];
 #pragma unroll
-                for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-                const int n = n0 + c0;
-                if (p.bias != nullptr) {
+                    for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
+                    if (p.bias != nullptr) {
 #pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        if (n + j < p.N) v[j] += p.bias[n + j];
-                }
-                if (p.epi == 0) {
-                    bf16* d = (bf16*)p.D + (long long)row * p.ldd + n;
-                    if (n + 16 <= p.N && ((p.ldd & 7) == 0)) {
-                        bf16x8 o0 = float_to_bf16x8(v), o1 = float_to_bf16x8(v + 8);
-                        *(bf16x8*)d = o0;
-                        *(bf16x8*)(d + 8) = o1;
-                    } else {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (n + j < p.N) d[j] = __float2bfloat16_rn(v[j]);
+                        for (int j = 0; j < 32; ++j)
+                            if (n + j < p.N) v[j] += p.bias[n + j];
                     }
-                } else if (p.epi == 1) {
-                    float* d = (float*)p.D + (long long)row * p.ldd + n;
-                    if (n + 16 <= p.N && ((p.ldd & 3) == 0)) {
+                    if (p.epi == 0) {
+                        bf16* d = (bf16*)p.D + (long long)row * p.ldd + n;
+                        if (n + 32 <= p.N && ((p.ldd & 7) == 0)) {
 #pragma unroll
-                        for (int j = 0; j < 16; j += 4) *(float4*)(d + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                            for (int j = 0; j < 32; j += 8) {
+                                bf16x8 o = float_to_bf16x8(v + j);
+                                *(int4*)(d + j) = *(int4*)&o;  // one 16-byte store (a struct copy would be split into 4)
+                            }
+                        } else {
+#pragma unroll
+                            for (int j = 0; j < 32; j += 8) {
+                                if (n + j + 8 <= p.N && ((p.ldd & 7) == 0)) {
+                                    bf16x8 o = float_to_bf16x8(v + j);
+                                    *(int4*)(d + j) = *(int4*)&o;
+                                } else
+                                    for (int q = 0; q < 8; ++q)
+                                        if (n + j + q < p.N) d[j + q] = __float2bfloat16_rn(v[j + q]);
+                            }
+                        }
+                    } else if (p.epi == 1) {
+                        float* d = (float*)p.D + (long long)row * p.ldd + n;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            if (n + j + 4 <= p.N && ((p.ldd & 3) == 0)) *(float4*)(d + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+                            else
+                                for (int q = 0; q < 4; ++q)
+                                    if (n + j + q < p.N) d[j + q] = v[j + q];
+                        }
                     } else {
+                        float* d = (float*)p.D + (long long)row * p.ldd + n;
 #pragma unroll
-                        for (int j = 0; j < 16; ++j)
-                            if (n + j < p.N) d[j] = v[j];
+                        for (int j = 0; j < 32; ++j)
+                            if (n + j < p.N) atomicAdd(d + j, v[j]);
                     }
-                } else {
-                    float* d = (float*)p.D + (long long)row * p.ldd + n;
-#pragma unroll
-                    for (int j = 0; j < 16; ++j)
-                        if (n + j < p.N) atomicAdd(d + j, v[j]);
                 }
             }
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);  // this warp is done reading the accumulator
         }
-        tcgen05_fence_before();
     }
     __syncthreads();
     if (warp == 1) {
@@ -337,7 +397,7 @@ int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t out
 template <int BN, bool A_MN, bool B_MN>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
-    constexpr int smem_bytes = STAGES * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ + 128 /*barriers*/;
+    constexpr int smem_bytes = STAGES * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
     static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
     static int configured_dev_mask = 0;
@@ -348,8 +408,15 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
         configured = true;
         configured_dev_mask |= (1 << dev);
     }
-    dim3 grid(dmp_ceil_div(p.M, BM), dmp_ceil_div(p.N, BN), splits);
-    kern<<<grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, p);
+    GemmParams q = p;
+    q.m_tiles = dmp_ceil_div(p.M, BM);
+    q.n_tiles = dmp_ceil_div(p.N, BN);
+    q.splits = splits;
+    const long long items = (long long)q.m_tiles * q.n_tiles * splits;
+    const int ctas_per_sm = smem_bytes <= 110 * 1024 ? 2 : 1;
+    long long grid = (long long)dmp_num_sms() * ctas_per_sm;
+    if (grid > items) grid = items;
+    kern<<<(int)grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, q);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
