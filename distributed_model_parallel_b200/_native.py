@@ -46,6 +46,9 @@ _KERNEL_SIGS = {
     "dmp_bn_bwd_reduce": (i32, [vp, vp, vp, i32, vp, vp, i64, i32, i32, vp, vp]),
     "dmp_bn_bwd_dx": (i32, [vp, vp, vp, i32, vp, vp, vp, vp, f64, vp, vp, i64, i32, i32, vp]),
     "dmp_bn_bwd_params": (i32, [vp, vp, vp, i32, i32, vp]),
+    "dmp_bn_fused_ws_bytes": (i64, [i32]),
+    "dmp_bn_fwd_fused": (i32, [vp, i32, vp, vp, i64, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, i32, vp]),
+    "dmp_bn_bwd_fused": (i32, [vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, vp, vp]),
     "dmp_bn_stats_finalize_noalloc": (i32, [vp, i32, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),
     "dmp_bn_noalloc_max_channels": (i32, []),
     # depthwise conv

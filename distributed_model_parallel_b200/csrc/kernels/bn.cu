@@ -23,6 +23,8 @@ struct Vec;
 template <>
 struct Vec<bf16> {
     static constexpr int N = 8;
+    __device__ static int4 load_raw(const bf16* p, long long v) { return *(const int4*)(p + v * 8); }
+    __device__ static void unpack(const int4& raw, float* out) { bf16x8_to_float(*(const bf16x8*)&raw, out); }
     __device__ static void load(const bf16* p, long long v, float* out) {
         int4 raw = *(const int4*)(p + v * 8);
         bf16x8 b = *(bf16x8*)&raw;
@@ -36,6 +38,10 @@ struct Vec<bf16> {
 template <>
 struct Vec<float> {
     static constexpr int N = 4;
+    __device__ static int4 load_raw(const float* p, long long v) { return *(const int4*)(p + v * 4); }
+    __device__ static void unpack(const int4& raw, float* out) {
+        out[0] = __int_as_float(raw.x); out[1] = __int_as_float(raw.y); out[2] = __int_as_float(raw.z); out[3] = __int_as_float(raw.w);
+    }
     __device__ static void load(const float* p, long long v, float* out) {
         float4 r = *(const float4*)(p + v * 4);
         out[0] = r.x; out[1] = r.y; out[2] = r.z; out[3] = r.w;
@@ -234,6 +240,256 @@ __global__ void bn_bwd_params_kernel(const double* __restrict__ accum_local, flo
     if (dbeta) dbeta[c] = accumulate ? dbeta[c] + db : db;
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Fused single-launch BatchNorm (cooperative grid): statistics -> grid barrier -> normalise, and for backward
+// reductions -> grid barrier -> dx.  The second pass re-reads the activation from L2 (the largest MobileNetV2 tensor
+// is 38 MB, L2 is 126 MB).  `ws` is a per-layer workspace {double accum[2][2C]; int parity}: call k accumulates into
+// accum[parity] and clears accum[parity^1] for call k+1, then flips the parity -- all on the device, so a captured
+// CUDA graph can be replayed without host-side bookkeeping.  Replaces 5 launches (memset, stats, finalize, counter
+// increment, apply) by one, and 4 (memset, reduce, dx, params) by one.
+// ---------------------------------------------------------------------------------------------------------
+}  // namespace
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+namespace {
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ residual, T* __restrict__ y, long long nvec, int C,
+                    double count, const float* __restrict__ gamma, const float* __restrict__ beta, float* __restrict__ running_mean,
+                    float* __restrict__ running_var, long long* __restrict__ num_batches_tracked, float momentum, float eps,
+                    float* __restrict__ mean_out, float* __restrict__ invstd_out, double* __restrict__ ws, int relu) {
+    constexpr int VEC = Vec<T>::N;
+    extern __shared__ float sm[];
+    cg::grid_group grid = cg::this_grid();
+    int* parity_p = (int*)(ws + 4 * (long long)C);
+    const int parity = *parity_p;
+    double* accum = ws + (long long)parity * 2 * C;
+    double* other = ws + (long long)(parity ^ 1) * 2 * C;
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    float acc[2 * VEC];
+#pragma unroll
+    for (int i = 0; i < 2 * VEC; ++i) acc[i] = 0.f;
+    constexpr int U = 4;  // independent 16-byte loads in flight per thread (HBM latency x bandwidth needs MBs in flight)
+    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+        int4 raw[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) raw[u] = Vec<T>::load_raw(x, v0 + u * stride);
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                float f[VEC];
+                Vec<T>::unpack(raw[u], f);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    acc[j] += f[j];
+                    acc[VEC + j] += f[j] * f[j];
+                }
+            }
+    }
+    block_channel_reduce<VEC, 2>(acc, ch0, C, accum, sm);
+    grid.sync();
+    float sc[VEC], sh[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const int c = ch0 + j;
+        const double m = accum[c] / count;
+        double var = accum[C + c] / count - m * m;
+        if (var < 0.0) var = 0.0;
+        const float is = (float)(1.0 / sqrt(var + (double)eps));
+        const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+        sc[j] = g * is;
+        sh[j] = b - (float)m * g * is;
+    }
+    if (blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+            const double m = accum[c] / count;
+            double var = accum[C + c] / count - m * m;
+            if (var < 0.0) var = 0.0;
+            mean_out[c] = (float)m;
+            invstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
+            if (running_mean != nullptr) {
+                const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+            }
+        }
+        if (threadIdx.x == 0) {
+            if (num_batches_tracked != nullptr) *num_batches_tracked += 1;
+            *parity_p = parity ^ 1;
+        }
+    }
+    for (long long i = tid; i < 2 * (long long)C; i += stride) other[i] = 0.0;  // ready for the next call
+    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+        int4 raw[U], rres[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                raw[u] = Vec<T>::load_raw(x, v0 + u * stride);
+                if (residual != nullptr) rres[u] = Vec<T>::load_raw(residual, v0 + u * stride);
+            }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                float f[VEC];
+                Vec<T>::unpack(raw[u], f);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) f[j] = f[j] * sc[j] + sh[j];
+                if (residual != nullptr) {
+                    float r[VEC];
+                    Vec<T>::unpack(rres[u], r);
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) f[j] += r[j];
+                }
+                if (relu) {
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) f[j] = fmaxf(f[j], 0.f);
+                }
+                Vec<T>::store(y, v0 + u * stride, f);
+            }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, const float* __restrict__ mean,
+                    const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta, double count,
+                    T* __restrict__ dx, T* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                    int accumulate_params, long long nvec, int C, int relu, double* __restrict__ ws) {
+    constexpr int VEC = Vec<T>::N;
+    constexpr int U = 4;
+    extern __shared__ float sm[];
+    cg::grid_group grid = cg::this_grid();
+    int* parity_p = (int*)(ws + 4 * (long long)C);
+    const int parity = *parity_p;
+    double* accum = ws + (long long)parity * 2 * C;
+    double* other = ws + (long long)(parity ^ 1) * 2 * C;
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    // ReLU mask: from the saved output when given, otherwise recomputed from x (y = relu(xhat*gamma + beta) without a
+    // residual), which saves reading a third tensor in both passes
+    const bool mask_from_x = relu && (y == nullptr);
+    float mu[VEC], is[VEC], gs[VEC], bs[VEC], acc[2 * VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        mu[j] = mean[ch0 + j];
+        is[j] = invstd[ch0 + j];
+        gs[j] = (gamma ? gamma[ch0 + j] : 1.f);
+        bs[j] = (beta ? beta[ch0 + j] : 0.f);
+        acc[j] = 0.f;
+        acc[VEC + j] = 0.f;
+    }
+    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+        int4 rg[U], rx[U], ry[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                rg[u] = Vec<T>::load_raw(dy, v0 + u * stride);
+                rx[u] = Vec<T>::load_raw(x, v0 + u * stride);
+                if (relu && !mask_from_x) ry[u] = Vec<T>::load_raw(y, v0 + u * stride);
+            }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                float g[VEC], xv[VEC];
+                Vec<T>::unpack(rg[u], g);
+                Vec<T>::unpack(rx[u], xv);
+                if (relu) {
+                    if (mask_from_x) {
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) g[j] = ((xv[j] - mu[j]) * is[j] * gs[j] + bs[j]) > 0.f ? g[j] : 0.f;
+                    } else {
+                        float yv[VEC];
+                        Vec<T>::unpack(ry[u], yv);
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+                    }
+                }
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    acc[j] += g[j];
+                    acc[VEC + j] += g[j] * (xv[j] - mu[j]) * is[j];
+                }
+            }
+    }
+    block_channel_reduce<VEC, 2>(acc, ch0, C, accum, sm);
+    grid.sync();
+    float a[VEC], b[VEC], c[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        a[j] = gs[j] * is[j];
+        b[j] = (float)(accum[ch0 + j] / count);
+        c[j] = (float)(accum[C + ch0 + j] / count);
+    }
+    if (blockIdx.x == 0) {
+        for (int ch = threadIdx.x; ch < C; ch += BN_THREADS) {
+            const float db = (float)accum[ch], dg = (float)accum[C + ch];
+            if (dgamma) dgamma[ch] = accumulate_params ? dgamma[ch] + dg : dg;
+            if (dbeta) dbeta[ch] = accumulate_params ? dbeta[ch] + db : db;
+        }
+        if (threadIdx.x == 0) *parity_p = parity ^ 1;
+    }
+    for (long long i = tid; i < 2 * (long long)C; i += stride) other[i] = 0.0;
+    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+        int4 rg[U], rx[U], ry[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                rg[u] = Vec<T>::load_raw(dy, v0 + u * stride);
+                rx[u] = Vec<T>::load_raw(x, v0 + u * stride);
+                if (relu && !mask_from_x) ry[u] = Vec<T>::load_raw(y, v0 + u * stride);
+            }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                float g[VEC], xv[VEC];
+                Vec<T>::unpack(rg[u], g);
+                Vec<T>::unpack(rx[u], xv);
+                if (relu) {
+                    if (mask_from_x) {
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) g[j] = ((xv[j] - mu[j]) * is[j] * gs[j] + bs[j]) > 0.f ? g[j] : 0.f;
+                    } else {
+                        float yv[VEC];
+                        Vec<T>::unpack(ry[u], yv);
+#pragma unroll
+                        for (int j = 0; j < VEC; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+                    }
+                }
+                if (dres != nullptr) Vec<T>::store(dres, v0 + u * stride, g);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    const float xh = (xv[j] - mu[j]) * is[j];
+                    g[j] = a[j] * (g[j] - b[j] - xh * c[j]);
+                }
+                Vec<T>::store(dx, v0 + u * stride, g);
+            }
+    }
+}
+
+// grid for a cooperative launch: a multiple of q (channel alignment) that fits co-resident on the device
+template <typename K>
+int bn_coop_grid(K kernel, long long nvec, int C, int vec, size_t smem) {
+    long long per_block = (long long)BN_THREADS * vec;
+    long long a = C, b = per_block;
+    while (b) { long long t = a % b; a = b; b = t; }
+    const int q = (int)(C / a);
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BN_THREADS, smem) != cudaSuccess || per_sm < 1) return -1;
+    if (per_sm > 2) per_sm = 2;
+    long long cap = (long long)dmp_num_sms() * per_sm;
+    long long want = (nvec + BN_THREADS * 8 - 1) / (BN_THREADS * 8);
+    if (want > cap) want = cap;
+    long long g = (want / q) * q;
+    if (g < q) g = q;
+    if (g > cap) return -1;  // cannot satisfy alignment and co-residency together: caller falls back to the split path
+    return (int)g;
+}
+
 int bn_grid(long long nvec, int C, int vec) {
     // smallest multiple q of blocks such that (blocks * BN_THREADS * vec) % C == 0
     long long per_block = (long long)BN_THREADS * vec;
@@ -347,6 +603,63 @@ DMP_API int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* d
                               cudaStream_t stream) {
     bn_bwd_params_kernel<<<dmp_ceil_div(C, 128), 128, 0, stream>>>(accum_local, dgamma, dbeta, C, accumulate);
     DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+
+// Workspace size (bytes) of the fused BatchNorm kernels for C channels; must be zero-initialised once.
+DMP_API long long dmp_bn_fused_ws_bytes(int C) { return (long long)(4 * (long long)C + 2) * 8; }
+
+// One-launch train-mode BatchNorm forward: y = act((x-mean)*invstd*gamma + beta (+ residual)); also writes mean/invstd
+// (saved for backward), updates running statistics and the batch counter.  Returns 1 if the shape cannot be launched
+// cooperatively (caller uses dmp_bn_stats/finalize/apply), 0 on success.
+DMP_API int dmp_bn_fwd_fused(const void* x, int dtype, const void* residual, void* y, long long M, int C, const float* gamma,
+                             const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+                             float momentum, float eps, float* mean, float* invstd, double* ws, int relu, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_fwd_fused", M, C, dtype)) return rc;
+    const int vec = dtype == 1 ? 8 : 4;
+    long long nvec = M * C / vec;
+    size_t smem = (size_t)BN_THREADS * 2 * vec * sizeof(float);
+    double count = (double)M;
+    void* args[] = {(void*)&x, (void*)&residual, (void*)&y, (void*)&nvec, (void*)&C, (void*)&count, (void*)&gamma, (void*)&beta,
+                    (void*)&running_mean, (void*)&running_var, (void*)&num_batches_tracked, (void*)&momentum, (void*)&eps,
+                    (void*)&mean, (void*)&invstd, (void*)&ws, (void*)&relu};
+    if (dtype == 1) {
+        const int grid = bn_coop_grid(bn_fwd_fused_kernel<bf16>, nvec, C, vec, smem);
+        if (grid < 0) return 1;
+        DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_fwd_fused_kernel<bf16>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
+    } else {
+        const int grid = bn_coop_grid(bn_fwd_fused_kernel<float>, nvec, C, vec, smem);
+        if (grid < 0) return 1;
+        DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_fwd_fused_kernel<float>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
+    }
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// One-launch BatchNorm backward: dx (and optional d(residual)), dgamma/dbeta (written or accumulated).
+// y == null with relu != 0: the mask is recomputed from x, gamma, beta (only valid when the forward had no residual).
+DMP_API int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int dtype, const float* mean, const float* invstd,
+                             const float* gamma, const float* beta, void* dx, void* dres, float* dgamma, float* dbeta,
+                             int accumulate_params, long long M, int C, int relu, double* ws, cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_bwd_fused", M, C, dtype)) return rc;
+    const int vec = dtype == 1 ? 8 : 4;
+    long long nvec = M * C / vec;
+    size_t smem = (size_t)BN_THREADS * 2 * vec * sizeof(float);
+    double count = (double)M;
+    void* args[] = {(void*)&dy, (void*)&y, (void*)&x, (void*)&mean, (void*)&invstd, (void*)&gamma, (void*)&beta, (void*)&count, (void*)&dx,
+                    (void*)&dres, (void*)&dgamma, (void*)&dbeta, (void*)&accumulate_params, (void*)&nvec, (void*)&C, (void*)&relu,
+                    (void*)&ws};
+    if (dtype == 1) {
+        const int grid = bn_coop_grid(bn_bwd_fused_kernel<bf16>, nvec, C, vec, smem);
+        if (grid < 0) return 1;
+        DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_fused_kernel<bf16>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
+    } else {
+        const int grid = bn_coop_grid(bn_bwd_fused_kernel<float>, nvec, C, vec, smem);
+        if (grid < 0) return 1;
+        DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_fused_kernel<float>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
+    }
     DMP_COUNT_LAUNCH(1);
     return 0;
 }

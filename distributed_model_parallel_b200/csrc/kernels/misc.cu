@@ -76,18 +76,34 @@ __global__ void stem_wgrad_kernel(const bf16* __restrict__ dy, const void* __res
     float acc[8];
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[j] = 0.f;
-    for (long long pix = blockIdx.x; pix < npix; pix += gridDim.x) {
-        long long t = pix;
-        const int wo = (int)(t % Wo); t /= Wo;
-        const int ho = (int)(t % Ho);
-        const int n = (int)(t / Ho);
-        const int hi = ho * stride + kh - pad, wi = wo * stride + kw - pad;
-        if (hi < 0 || hi >= H || wi < 0 || wi >= W) continue;
-        const float xv = stem_x(x, layout, n, ci, hi, wi, Cin, H, W);
-        float g[8];
-        load8(dy + pix * Cout + cg * 8, g);
+    constexpr int U = 8;  // pixels in flight per thread: the loop body is two dependent-free global loads per pixel
+    for (long long pix0 = blockIdx.x; pix0 < npix; pix0 += (long long)U * gridDim.x) {
+        float xv[U];
+        int4 gr[U];
 #pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += g[j] * xv;
+        for (int u = 0; u < U; ++u) {
+            const long long pix = pix0 + (long long)u * gridDim.x;
+            xv[u] = 0.f;
+            gr[u] = make_int4(0, 0, 0, 0);
+            if (pix < npix) {
+                long long t = pix;
+                const int wo = (int)(t % Wo); t /= Wo;
+                const int ho = (int)(t % Ho);
+                const int n = (int)(t / Ho);
+                const int hi = ho * stride + kh - pad, wi = wo * stride + kw - pad;
+                if (hi >= 0 && hi < H && wi >= 0 && wi < W) {
+                    xv[u] = stem_x(x, layout, n, ci, hi, wi, Cin, H, W);
+                    gr[u] = *(const int4*)(dy + pix * Cout + cg * 8);
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            float g[8];
+            bf16x8_to_float(*(bf16x8*)&gr[u], g);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[j] += g[j] * xv[u];
+        }
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j) atomicAdd(&dw[(long long)(cg * 8 + j) * T + tap], acc[j]);
@@ -242,7 +258,7 @@ DMP_API int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, flo
     const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
     if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)T * Cout, stream));
     const int block = ((threads + 31) / 32) * 32;
-    const int grid = dmp_num_sms() * 2;
+    const int grid = dmp_num_sms() * 4;
     stem_wgrad_kernel<<<grid, block, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, Cin, H, W, Cout, KH, KW, stride, pad,
                                                   Ho, Wo);
     DMP_LAUNCH_CHECK();

@@ -252,6 +252,17 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
 # ----------------------------------------------------------------------------------------------------
 # fused conv -> (BatchNorm) -> (+residual) -> (ReLU)
 # ----------------------------------------------------------------------------------------------------
+def _bn_workspace(bn, which: str, C: int, dev):
+    """Per-layer, per-device zero-initialised workspace of the fused BatchNorm kernels (double accum[2][2C] + parity)."""
+    store = bn.__dict__.setdefault("_dmp_ws", {})
+    key = (dev.index, which)
+    ws = store.get(key)
+    if ws is None or ws.numel() < 4 * C + 2:
+        ws = torch.zeros(4 * C + 2, dtype=torch.float64, device=dev)
+        store[key] = ws
+    return ws
+
+
 def _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync):
     """Train/eval BatchNorm (+residual, +ReLU) of a channels-last bf16 tensor. Returns (out, mean, invstd, count, training)."""
     lib = _k()
@@ -260,6 +271,21 @@ def _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync):
     M = N * Ho * Wo
     dev = y_raw.device
     training = bn.training or (bn.running_mean is None)
+    if training and sync is None and (bn.momentum is not None or not bn.track_running_stats):
+        # single cooperative launch: statistics -> grid barrier -> normalise (+residual, +ReLU), running stats, counter
+        mean = torch.empty(C, device=dev, dtype=torch.float32)
+        invstd = torch.empty(C, device=dev, dtype=torch.float32)
+        out = torch.empty_like(y_raw)
+        track = bn.track_running_stats
+        rc = lib.dmp_bn_fwd_fused(y_raw.data_ptr(), 1, _native.ptr(residual), out.data_ptr(), M, C, _native.ptr(gamma), _native.ptr(beta),
+                                  _native.ptr(bn.running_mean if track else None), _native.ptr(bn.running_var if track else None),
+                                  _native.ptr(bn.num_batches_tracked if track else None), float(bn.momentum or 0.1), float(bn.eps),
+                                  mean.data_ptr(), invstd.data_ptr(), _bn_workspace(bn, "f", C, dev).data_ptr(), 1 if relu else 0, sp)
+        if rc == 0:
+            _note("bn:fused1")
+            return out, mean, invstd, float(M), True
+        if rc != 1:
+            _ck(rc, "bn fwd fused")
     if training:
         accum = torch.empty(2 * C, device=dev, dtype=torch.float64)
         mean = torch.empty(C, device=dev, dtype=torch.float32)
@@ -301,6 +327,35 @@ def _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu, need
     N, C, Ho, Wo = y_raw.shape
     M = N * Ho * Wo
     dres_t = None
+    if ctx.bn_train and ctx.sync is None:
+        # single cooperative launch: reductions -> grid barrier -> dx (+dres), dgamma/dbeta accumulated in place
+        gw, gb = (bn.weight if needs_gamma else None), (bn.bias if needs_beta else None)
+        direct = all(p is None or (p.grad is not None and getattr(p, "_dmp_direct", False) and p.grad.dtype == torch.float32
+                                   and p.grad.is_contiguous()) for p in (gw, gb))
+        dy = torch.empty_like(y_raw)
+        dres_t = torch.empty_like(y_raw) if ctx.has_res else None
+        if direct:
+            dg_t, db_t, acc_flag = (gw.grad if gw is not None else None), (gb.grad if gb is not None else None), 1
+        else:
+            dg_t = torch.empty(C, device=y_raw.device, dtype=torch.float32) if gw is not None else None
+            db_t = torch.empty(C, device=y_raw.device, dtype=torch.float32) if gb is not None else None
+            acc_flag = 0
+        # without a residual the ReLU mask is recomputed from the BN input: one tensor less to read in both passes
+        y_mask = out if (relu and ctx.has_res) else None
+        rc = lib.dmp_bn_bwd_fused(dout.data_ptr(), _native.ptr(y_mask), y_raw.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(),
+                                  _native.ptr(gamma), _native.ptr(bn.bias), dy.data_ptr(), _native.ptr(dres_t), _native.ptr(dg_t),
+                                  _native.ptr(db_t), acc_flag,
+                                  M, C, 1 if relu else 0, _bn_workspace(bn, "b", C, y_raw.device).data_ptr(), sp)
+        if rc == 0:
+            if direct:
+                for p in (gw, gb):
+                    if p is not None:
+                        for cb in grad_ready_callbacks:
+                            cb(p)
+                return dy, dres_t, None, None
+            return dy, dres_t, dg_t, db_t
+        if rc != 1:
+            _ck(rc, "bn bwd fused")
     if ctx.bn_train:
         dy = torch.empty_like(y_raw)
         dres_t = torch.empty_like(y_raw) if ctx.has_res else None

@@ -60,6 +60,17 @@ int dmp_bn_bwd_dx(const void* dy, const void* y, const void* x, int dtype, const
                   const float* gamma, const double* accum_global, double count, void* dx, void* dres, long long M, int C,
                   int relu, dmp_stream_t stream);
 int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* dbeta, int C, int accumulate, dmp_stream_t stream);
+/* Single-launch (cooperative grid) train-mode BatchNorm: statistics -> grid barrier -> normalise(+residual,+ReLU) with running
+ * statistics / batch counter update, and reductions -> grid barrier -> dx(+dres) with dgamma/dbeta.  ws: per-layer workspace of
+ * dmp_bn_fused_ws_bytes(C) bytes, zeroed once (double-buffered accumulators + device-side parity, graph-replay safe).
+ * Return 1 = shape not launchable cooperatively, use the split entry points above.  (T/nn/functional.py batch_norm semantics) */
+long long dmp_bn_fused_ws_bytes(int C);
+int dmp_bn_fwd_fused(const void* x, int dtype, const void* residual, void* y, long long M, int C, const float* gamma,
+                     const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked, float momentum,
+                     float eps, float* mean, float* invstd, double* ws, int relu, dmp_stream_t stream);
+int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int dtype, const float* mean, const float* invstd,
+                     const float* gamma, const float* beta, void* dx, void* dres, float* dgamma, float* dbeta,
+                     int accumulate_params, long long M, int C, int relu, double* ws, dmp_stream_t stream);
 /* Statistics + finalize for callers that may not allocate device memory (their process gave all of HBM to its own arena, or
  * bans allocator calls in its steady-state loop): same results as dmp_bn_stats + dmp_bn_finalize, but the double[2*C]
  * accumulator is a fixed 64 KiB array inside the library instead of a caller buffer.  No counterpart in the reference (it has

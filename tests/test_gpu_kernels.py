@@ -20,13 +20,15 @@ def _sp():
     return torch.cuda.current_stream().cuda_stream
 
 
-def _close(a, b, rtol, atol, what=""):
+def _close(a, b, rtol, atol, what="", max_bad_frac=0.0):
+    """max_bad_frac > 0 tolerates isolated outliers: a ReLU mask taken from a bf16 activation can flip for elements
+    whose pre-activation is within rounding distance of zero, which changes that one gradient by the whole dy."""
     a = a.float()
     b = b.float()
     err = (a - b).abs()
     tol = atol + rtol * b.abs()
     bad = (err > tol).sum().item()
-    assert bad == 0, "%s: %d/%d mismatches, max abs err %.4g (ref max %.4g)" % (
+    assert bad <= max_bad_frac * a.numel(), "%s: %d/%d mismatches, max abs err %.4g (ref max %.4g)" % (
         what, bad, a.numel(), err.max().item(), b.abs().max().item())
 
 
@@ -199,9 +201,9 @@ def test_batchnorm_train(M, C, relu, res):
     scale_g = max(1.0, (M ** 0.5) * 0.02)
     _close(dbeta, b_r.grad, 2e-2, 0.05 * scale_g, "bn dbeta")
     _close(dgamma, g_r.grad, 2e-2, 0.05 * scale_g, "bn dgamma")
-    _close(dx, xr.grad, 3e-2, 3e-2, "bn dx")
+    _close(dx, xr.grad, 3e-2, 3e-2, "bn dx", 1e-5 if relu else 0.0)
     if res:
-        _close(dres, rr.grad, 1e-2, 1e-2, "bn dres")
+        _close(dres, rr.grad, 1e-2, 1e-2, "bn dres", 1e-5 if relu else 0.0)
 
 
 @pytest.mark.parametrize("N,H,C,stride", [(8, 32, 32, 1), (4, 16, 144, 2), (2, 8, 960, 1), (3, 9, 24, 2), (128, 32, 96, 1)])
@@ -312,3 +314,57 @@ def test_pool_linear_elementwise():
     torch.cuda.synchronize()
     _close(o, F.relu(a.float() + b.float()), 1e-2, 1e-2, "add_act")
     _close(g, torch.where(o.float() > 0, b.float(), torch.zeros_like(b.float())), 0, 0, "relu_bwd")
+
+
+@pytest.mark.parametrize("M,C", [(128 * 32 * 32, 96), (128 * 16 * 16, 144), (2048, 1280), (1000, 24)])
+@pytest.mark.parametrize("relu,res", [(1, 1), (0, 0), (1, 0)])
+def test_batchnorm_fused_single_launch(M, C, relu, res):
+    """The cooperative one-launch BN kernels against torch, three calls in a row (exercises the parity workspace)."""
+    nat = _lib()
+    lib = nat.kernels()
+    sp = _sp()
+    ws_f = torch.zeros(lib.dmp_bn_fused_ws_bytes(C) // 8, device="cuda", dtype=torch.float64)
+    ws_b = torch.zeros_like(ws_f)
+    gamma = torch.rand(C, device="cuda") + 0.5
+    beta = torch.randn(C, device="cuda") * 0.1
+    rm, rv = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    rm_r, rv_r = torch.zeros(C, device="cuda"), torch.ones(C, device="cuda")
+    nbt = torch.zeros((), device="cuda", dtype=torch.int64)
+    for it in range(3):
+        torch.manual_seed(M + C + it)
+        x = (torch.randn(M, C, device="cuda") * 2 + 0.5).bfloat16()
+        resid = torch.randn(M, C, device="cuda").bfloat16() if res else None
+        y = torch.empty_like(x)
+        mean = torch.empty(C, device="cuda"); invstd = torch.empty_like(mean)
+        rc = lib.dmp_bn_fwd_fused(x.data_ptr(), 1, nat.ptr(resid), y.data_ptr(), M, C, gamma.data_ptr(), beta.data_ptr(), rm.data_ptr(),
+                                  rv.data_ptr(), nbt.data_ptr(), 0.1, 1e-5, mean.data_ptr(), invstd.data_ptr(), ws_f.data_ptr(), relu, sp)
+        assert rc == 0, nat.kernels().dmp_last_error()
+        xr = x.float().clone().requires_grad_()
+        g_r, b_r = gamma.clone().requires_grad_(), beta.clone().requires_grad_()
+        rr = resid.float().clone().requires_grad_() if res else None
+        z = F.batch_norm(xr, rm_r, rv_r, g_r, b_r, True, 0.1, 1e-5)
+        if res:
+            z = z + rr
+        yr = F.relu(z) if relu else z
+        torch.cuda.synchronize()
+        _close(y, yr, 2e-2, 2e-2, "fused bn y (call %d)" % it)
+        _close(rm, rm_r, 1e-4, 1e-5, "fused bn running_mean")
+        _close(rv, rv_r, 1e-3, 1e-4, "fused bn running_var")
+        dy = torch.randn(M, C, device="cuda").bfloat16()
+        yr.backward(dy.float())
+        dx = torch.empty_like(x); dres = torch.empty_like(x) if res else None
+        dgamma = torch.full((C,), 1.0, device="cuda"); dbeta = torch.full((C,), -2.0, device="cuda")
+        # with a residual the mask comes from the saved output, without one it is recomputed from x (y = NULL)
+        rc = lib.dmp_bn_bwd_fused(dy.data_ptr(), y.data_ptr() if res else None, x.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(),
+                                  gamma.data_ptr(), beta.data_ptr(), dx.data_ptr(), nat.ptr(dres), dgamma.data_ptr(), dbeta.data_ptr(), 1,
+                                  M, C, relu, ws_b.data_ptr(), sp)
+        assert rc == 0
+        torch.cuda.synchronize()
+        scale_g = max(1.0, (M ** 0.5) * 0.02)
+        # per-channel sums over M elements; a handful of ReLU-mask flips move a sum by O(1) each
+        _close(dbeta + 2.0, b_r.grad, 2e-2, 0.05 * scale_g + 0.01 * b_r.grad.abs().max().item(), "fused bn dbeta (accumulated)")
+        _close(dgamma - 1.0, g_r.grad, 2e-2, 0.05 * scale_g + 0.01 * g_r.grad.abs().max().item(), "fused bn dgamma (accumulated)")
+        _close(dx, xr.grad, 3e-2, 3e-2, "fused bn dx", 1e-5 if relu else 0.0)
+        if res:
+            _close(dres, rr.grad, 1e-2, 1e-2, "fused bn dres", 1e-5 if relu else 0.0)
+    assert int(nbt.item()) == 3
