@@ -177,37 +177,35 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
         if (wo0 + i < Wo) store8(y + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0, acc[i]);
 }
 
-// Strip version of the weight gradient: per thread 8 channels x 9 taps of partial sums over a strided set of
-// (n, ho, strip) work items; dy and the three input rows of a strip are loaded once.  Partials of threads that share
-// a channel vector are pre-reduced with warp shuffles when the sharing pattern is a power of two, then combined in
-// shared memory and flushed with one atomic per (block, weight).
+// Strip version of the weight gradient.  A warp owns TWO adjacent channel vectors (lane & 1) and its 16 lane pairs walk
+// 16 different (n, ho, strip) work items at a time, so a lane pair reads 32 contiguous bytes (one full sector) and all
+// partial sums that must be combined live in the same warp: 4 xor-shuffle rounds fold the 16 items, then lanes 0/1 issue
+// the 72 fp32 atomics of their channel vector.  (An earlier version combined threads through shared-memory atomics and
+// spent most of its time serialised on bank conflicts.)
 template <int STRIDE, int TW>
 __global__ void __launch_bounds__(DW_THREADS)
 dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, float* __restrict__ dw, int N, int H, int W,
                       int C, int Ho, int Wo) {
     constexpr int NC = (TW - 1) * STRIDE + 3;
-    extern __shared__ float sm[];  // [groups_in_block][72]
-    const int P = C >> 3;
-    const int groups = P < DW_THREADS ? P : DW_THREADS;
-    for (int i = threadIdx.x; i < groups * 72; i += DW_THREADS) sm[i] = 0.f;
-    __syncthreads();
-    const long long tid = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
-    const long long nthreads = (long long)gridDim.x * DW_THREADS;  // multiple of P (host guarantees)
-    const int cv = (int)(tid % P);
-    const long long istride = nthreads / P;
+    const int P2 = C >> 4;                       // pairs of channel vectors (host guarantees C % 16 == 0)
+    const int lane = threadIdx.x & 31, sub = lane & 1, li = lane >> 1;
+    const long long gw = (blockIdx.x * (long long)DW_THREADS + threadIdx.x) >> 5;
+    const long long nw = ((long long)gridDim.x * DW_THREADS) >> 5;   // multiple of P2 (host guarantees)
+    const int pw = (int)(gw % P2);
+    const int ch0 = (pw * 2 + sub) * 8;
     const int tiles_w = (Wo + TW - 1) / TW;
     const long long nitems = (long long)N * Ho * tiles_w;
-    const int ch0 = cv * 8;
+    const long long istride = (nw / P2) * 16;
     float acc[72];
 #pragma unroll
     for (int i = 0; i < 72; ++i) acc[i] = 0.f;
-    for (long long item = tid / P; item < nitems; item += istride) {
+    for (long long item = (gw / P2) * 16 + li; item < nitems; item += istride) {
         long long t = item;
         const int wt_ = (int)(t % tiles_w); t /= tiles_w;
         const int ho = (int)(t % Ho);
         const int n = (int)(t / Ho);
         const int wo0 = wt_ * TW;
-        // operands stay packed (8 bf16 = one int4) until the FMA that consumes them: halves the live registers
+        // operands stay packed (8 bf16 = one int4) until the FMA that consumes them
         int4 g[TW];
 #pragma unroll
         for (int i = 0; i < TW; ++i)
@@ -238,29 +236,19 @@ dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, f
             }
         }
     }
-    // lanes l, l+P, l+2P, ... of a warp hold the same channel vector when P divides 32 (and the block base is a
-    // multiple of P): fold them with xor-shuffles so that only P lanes per warp touch shared memory
-    const bool pow2 = (P & (P - 1)) == 0 && P < 32;
-    if (pow2) {
 #pragma unroll
-        for (int i = 0; i < 72; ++i) {
-            float v = acc[i];
-            for (int o = 16; o >= P; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            acc[i] = v;
-        }
+    for (int i = 0; i < 72; ++i) {
+        float v = acc[i];
+        v += __shfl_xor_sync(0xffffffffu, v, 2);
+        v += __shfl_xor_sync(0xffffffffu, v, 4);
+        v += __shfl_xor_sync(0xffffffffu, v, 8);
+        v += __shfl_xor_sync(0xffffffffu, v, 16);
+        acc[i] = v;
     }
-    const int slot = (P < DW_THREADS) ? cv : threadIdx.x;
-    if (!pow2 || (threadIdx.x & 31) < P) {
+    if (li == 0) {
+        float* d = dw + (long long)ch0 * 9;
 #pragma unroll
-        for (int i = 0; i < 72; ++i) atomicAdd(&sm[slot * 72 + i], acc[i]);
-    }
-    __shared__ int s_cv[DW_THREADS];
-    s_cv[slot] = cv;  // identical value from every writer of a slot
-    __syncthreads();
-    for (int i = threadIdx.x; i < groups * 72; i += DW_THREADS) {
-        const int sl = i / 72, k = i % 72;
-        const float v = sm[i];
-        if (v != 0.f) atomicAdd(&dw[(long long)s_cv[sl] * 72 + k], v);
+        for (int i = 0; i < 72; ++i) atomicAdd(d + i, acc[i]);
     }
 }
 
@@ -379,32 +367,38 @@ DMP_API int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N,
     if (int rc = dw_check("dmp_dwconv3x3_wgrad", N, H, W, C, stride)) return rc;
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
     if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)C, stream));
-    const int P = C / 8;
-    // grid * threads must be a multiple of P
-    int a = P, b = DW_THREADS;
-    while (b) { int t = a % b; a = b; b = t; }
-    const int q = P / a;
-    const int TWs = stride == 1 ? 4 : 2;
-    const long long nitems = (long long)N * Ho * ((Wo + TWs - 1) / TWs);
-    long long want = (nitems * P + (long long)DW_THREADS * 8 - 1) / ((long long)DW_THREADS * 8);  // ~8 strips per thread
-    const long long cap = (long long)dmp_num_sms() * 2;
-    if (want > cap) want = cap;
-    if (want < 1) want = 1;
-    const int grid = (int)(((want + q - 1) / q) * q);
-    const int groups = P < DW_THREADS ? P : DW_THREADS;
-    const size_t smem = (size_t)groups * 72 * sizeof(float);
-    if (smem > 48 * 1024) {
-        static int configured_mask = 0;
-        int dev = 0;
-        cudaGetDevice(&dev);
-        if (!(configured_mask & (1 << dev))) {
-            DMP_CHECK_CUDA(cudaFuncSetAttribute(dw_wgrad_strip_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
-            DMP_CHECK_CUDA(cudaFuncSetAttribute(dw_wgrad_strip_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
-            configured_mask |= 1 << dev;
-        }
+    if (C % 16 == 0) {
+        const int P2 = C / 16;
+        const int warps_per_block = DW_THREADS / 32;
+        // total warps must be a multiple of P2
+        int a = P2, b = warps_per_block;
+        while (b) { int t = a % b; a = b; b = t; }
+        const int q = P2 / a;
+        const int TWs = stride == 1 ? 4 : 2;
+        const long long nitems = (long long)N * Ho * ((Wo + TWs - 1) / TWs);
+        long long want = (nitems * P2 / 16 + (long long)warps_per_block * 4 - 1) / ((long long)warps_per_block * 4);  // ~4 items per lane pair
+        const long long cap = (long long)dmp_num_sms();
+        if (want > cap) want = cap;
+        if (want < 1) want = 1;
+        const int grid = (int)(((want + q - 1) / q) * q);
+        if (stride == 1) dw_wgrad_strip_kernel<1, 4><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
+        else dw_wgrad_strip_kernel<2, 2><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
+    } else {
+        const int P = C / 8;
+        int a = P, b = DW_THREADS;
+        while (b) { int t = a % b; a = b; b = t; }
+        const int q = P / a;
+        const long long npix = (long long)N * Ho * Wo;
+        long long want = (npix * P + (long long)DW_THREADS * 16 - 1) / ((long long)DW_THREADS * 16);
+        const long long cap = (long long)dmp_num_sms() * 2;
+        if (want > cap) want = cap;
+        if (want < 1) want = 1;
+        const int grid = (int)(((want + q - 1) / q) * q);
+        const int groups = P < DW_THREADS ? P : DW_THREADS;
+        const size_t smem = (size_t)groups * 72 * sizeof(float);
+        DMP_REQUIRE(smem <= 48 * 1024, "dmp_dwconv3x3_wgrad: C=%d (not a multiple of 16) is too wide for the fallback kernel", C);
+        dw_wgrad_kernel<<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo, stride);
     }
-    if (stride == 1) dw_wgrad_strip_kernel<1, 4><<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
-    else dw_wgrad_strip_kernel<2, 2><<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
