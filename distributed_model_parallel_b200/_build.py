@@ -82,7 +82,10 @@ def build_kernels(force: bool = False, verbose: bool = False) -> Path:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
             list(ex.map(lambda j: _run(*j), jobs))
     if force or jobs or _newer(objs, KERNEL_LIB):
-        _run([nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", str(KERNEL_LIB), *map(str, objs)])
+        # shared CUDA runtime: inside a PyTorch process the library then uses the very libcudart torch has loaded (one runtime
+        # instance, one view of current device / peer access); standalone users get it from the toolkit via the rpath
+        _run([nvcc, "-shared", "-cudart", "shared", "-gencode", "arch=compute_100a,code=sm_100a", "-Xlinker", "-rpath,/usr/local/cuda/lib64",
+              "-o", str(KERNEL_LIB), *map(str, objs)])
     return KERNEL_LIB
 
 

@@ -64,6 +64,27 @@ _KERNEL_SIGS = {
     "dmp_linear_small_bwd": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, vp]),
     "dmp_add_act": (i32, [vp, vp, vp, i64, i32, vp]),
     "dmp_relu_bwd": (i32, [vp, vp, vp, i64, vp]),
+    # peer-memory collectives and plumbing (csrc/comm/collectives.cu)
+    "dmp_comm_state_bytes": (C.c_longlong, []),
+    "dmp_comm_max_ranks": (C.c_int, []),
+    "dmp_comm_max_blocks": (C.c_int, []),
+    "dmp_allreduce_fused": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_float,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
+                                      C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_broadcast": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int,
+                                C.c_int, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_gather_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "dmp_copy_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
+    "dmp_reduce_add_peer": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_symm_malloc": (C.c_int, [C.c_longlong, C.POINTER(C.c_void_p)]),
+    "dmp_symm_free": (C.c_int, [C.c_void_p]),
+    "dmp_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "dmp_ipc_import": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "dmp_ipc_close": (C.c_int, [C.c_void_p]),
+    "dmp_ipc_handle_bytes": (C.c_int, []),
+    "dmp_enable_peer_access": (C.c_int, [C.c_int]),
+    "dmp_comm_status": (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 
 _RUNTIME_SIGS = {
@@ -104,6 +125,7 @@ def kernels():
                 path = _build.KERNEL_LIB
                 if os.environ.get("DMP_B200_NO_BUILD") != "1":
                     path = _build.build_kernels(verbose=False)
+                import torch  # noqa: F401  (loads the CUDA runtime this library shares with torch before dlopen)
                 lib = C.CDLL(str(path), mode=C.RTLD_GLOBAL)
                 _apply(lib, _KERNEL_SIGS)
                 _klib = lib

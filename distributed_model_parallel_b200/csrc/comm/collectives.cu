@@ -17,6 +17,7 @@
 // the kernel records an error in `status` and returns instead of hanging the GPU.
 #include "../common.cuh"
 #include <type_traits>
+#include <stdlib.h>
 
 #define DMP_MAX_RANKS 16
 #define DMP_COMM_THREADS 512
@@ -466,6 +467,16 @@ DMP_API int dmp_gather_peer(void* const* src, const long long* bytes, int n_src,
 DMP_API int dmp_copy_peer(const void* src, void* dst, long long bytes, int max_blocks, cudaStream_t stream) {
     DMP_REQUIRE(bytes % 16 == 0, "dmp_copy_peer: size must be a multiple of 16 bytes");
     if (bytes == 0) return 0;
+    if (getenv("DMP_DEBUG_PEER")) {
+        int dev = -1, can = -1;
+        cudaGetDevice(&dev);
+        cudaPointerAttributes a, b;
+        cudaPointerGetAttributes(&a, src);
+        cudaPointerGetAttributes(&b, dst);
+        if (a.device != dev) cudaDeviceCanAccessPeer(&can, dev, a.device);
+        fprintf(stderr, "[dmp_copy_peer] current device %d, src on %d (type %d), dst on %d (type %d), canAccess(src)=%d stream=%p\n", dev,
+                a.device, (int)a.type, b.device, (int)b.type, can, (void*)stream);
+    }
     copy16_kernel<<<comm_grid(bytes / 16, max_blocks), DMP_COMM_THREADS, 0, stream>>>(src, dst, bytes / 16);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);

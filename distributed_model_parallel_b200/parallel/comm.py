@@ -115,7 +115,12 @@ def _ensure_peer_access(devs: Sequence[torch.device]):
         with torch.cuda.device(d):
             for e in devs:
                 if e != d:
-                    _native.check(lib.dmp_enable_peer_access(e.index), "enable_peer_access")
+                    # peer access is switched on through torch (a tiny device-to-device copy in each direction) so that
+                    # torch's allocator and our kernels share one consistent view of which pairs are enabled
+                    torch.zeros(4, device=d).to(e)
+                    torch.zeros(4, device=e).to(d)
+    for d in devs:
+        torch.cuda.synchronize(d)
     _peer_enabled.add(key)
 
 

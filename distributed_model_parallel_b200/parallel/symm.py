@@ -22,28 +22,7 @@ import torch.distributed as dist
 
 from .. import _native
 
-_native.register_kernel_sigs({
-    "dmp_comm_state_bytes": (C.c_longlong, []),
-    "dmp_comm_max_ranks": (C.c_int, []),
-    "dmp_comm_max_blocks": (C.c_int, []),
-    "dmp_allreduce_fused": (C.c_int, [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_longlong, C.c_float,
-                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p,
-                                      C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
-    "dmp_broadcast": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_longlong, C.c_void_p, C.c_int,
-                                C.c_int, C.c_int, C.c_int, C.c_void_p]),
-    "dmp_gather_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
-    "dmp_copy_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
-    "dmp_reduce_add_peer": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p,
-                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
-    "dmp_symm_malloc": (C.c_int, [C.c_longlong, C.POINTER(C.c_void_p)]),
-    "dmp_symm_free": (C.c_int, [C.c_void_p]),
-    "dmp_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),
-    "dmp_ipc_import": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
-    "dmp_ipc_close": (C.c_int, [C.c_void_p]),
-    "dmp_ipc_handle_bytes": (C.c_int, []),
-    "dmp_enable_peer_access": (C.c_int, [C.c_int]),
-    "dmp_comm_status": (C.c_int, [C.c_void_p, C.c_void_p]),
-})
+# (the C signatures of the communication entry points are declared centrally in _native.py)
 
 DTYPE_CODE = {torch.float32: 0, torch.bfloat16: 1, torch.float64: 2}
 
@@ -158,7 +137,8 @@ class DeviceSymmGroup:
             with torch.cuda.device(d):
                 for e in self.devices:
                     if e != d:
-                        _native.check(self.lib.dmp_enable_peer_access(e), "enable_peer_access")
+                        torch.zeros(4, device=torch.device("cuda", d)).to(torch.device("cuda", e))  # torch enables the pair
+                        torch.zeros(4, device=torch.device("cuda", e)).to(torch.device("cuda", d))
 
     def alloc(self, nbytes: int) -> List[torch.Tensor]:
         nbytes = max(256, (int(nbytes) + 255) // 256 * 256)
