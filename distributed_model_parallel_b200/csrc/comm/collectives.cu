@@ -48,8 +48,11 @@ __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
 
 // Block-level barrier across all ranks.  `flags.p[r]` is rank r's flag pad, `epoch` the value to publish.
 // Every thread's prior global writes are made visible system-wide first.
-__device__ __forceinline__ bool barrier_ranks(const PeerPtrs& flags, int rank, int W, uint32_t epoch, uint32_t* status) {
-    __threadfence_system();
+// fence_sys: the caller's threads wrote data that PEERS will read after this barrier (stores into peer memory or into local
+// memory that peers load next); a barrier that only announces "I have finished reading" needs no system-wide fence.
+__device__ __forceinline__ bool barrier_ranks(const PeerPtrs& flags, int rank, int W, uint32_t epoch, uint32_t* status,
+                                              bool fence_sys = true) {
+    if (fence_sys) __threadfence_system();
     __syncthreads();
     int ok = 1;
     if (threadIdx.x < W) {
@@ -186,7 +189,8 @@ allreduce_oneshot_kernel(PeerPtrs bufs, PeerPtrs flags, uint32_t* epoch_mem, uin
     typedef typename VecIO<T>::acc_t acc_t;
     uint32_t epoch = epoch_mem[blockIdx.x];
     __syncthreads();
-    if (!barrier_ranks(flags, rank, W, epoch + 1, status)) return;
+    // inputs were written by earlier kernels of this stream: the kernel boundary already published them
+    if (!barrier_ranks(flags, rank, W, epoch + 1, status, false)) return;
     const long long stride = (long long)gridDim.x * blockDim.x;
     const long long first = blockIdx.x * (long long)blockDim.x + threadIdx.x;
     for (long long v = first; v < nvec; v += stride) {
@@ -203,7 +207,7 @@ allreduce_oneshot_kernel(PeerPtrs bufs, PeerPtrs flags, uint32_t* epoch_mem, uin
         }
         VecIO<T>::store(out, v, acc);
     }
-    if (!barrier_ranks(flags, rank, W, epoch + 2, status)) return;
+    if (!barrier_ranks(flags, rank, W, epoch + 2, status, false)) return;  // "done reading": nothing to publish
     // every peer finished reading my buffer: now it may be overwritten
     void* mine = bufs.p[rank];
     if (sgd.master == nullptr) {
@@ -230,7 +234,7 @@ allreduce_twoshot_kernel(PeerPtrs bufs, PeerPtrs flags, uint32_t* epoch_mem, uin
     constexpr int N = VecIO<T>::N;
     uint32_t epoch = epoch_mem[blockIdx.x];
     __syncthreads();
-    if (!barrier_ranks(flags, rank, W, epoch + 1, status)) return;
+    if (!barrier_ranks(flags, rank, W, epoch + 1, status, false)) return;
     const long long per = (nvec + W - 1) / W;
     const long long lo = per * rank;
     long long hi = lo + per;

@@ -124,7 +124,7 @@ dw_dgrad_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __r
 // so every input vector of a row is loaded once and reused by up to 3 outputs (4.5 instead of 9 loads per output at
 // stride 1).  FLIP=true mirrors the taps: with stride 1 the data gradient is the same stencil applied to dy.
 template <typename WT, int STRIDE, int TW, bool FLIP>
-__global__ void __launch_bounds__(DW_THREADS)
+__global__ void __launch_bounds__(DW_THREADS, 2)  // 2 blocks/SM: the few spilled registers cost less than half occupancy
 dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
                 int Ho, int Wo) {
     constexpr int NC = (TW - 1) * STRIDE + 3;  // input columns feeding the strip

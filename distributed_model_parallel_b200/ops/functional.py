@@ -257,8 +257,9 @@ def _bn_workspace(bn, which: str, C: int, dev):
     store = bn.__dict__.setdefault("_dmp_ws", {})
     key = (dev.index, which)
     ws = store.get(key)
-    if ws is None or ws.numel() < 4 * C + 2:
-        ws = torch.zeros(4 * C + 2, dtype=torch.float64, device=dev)
+    need = int(_k().dmp_bn_fused_ws_bytes(C)) // 8
+    if ws is None or ws.numel() < need:
+        ws = torch.zeros(need, dtype=torch.float64, device=dev)
         store[key] = ws
     return ws
 
