@@ -34,6 +34,8 @@ _KERNEL_SIGS = {
     # gemm
     "dmp_gemm_bf16": (i32, [i32, vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i32, i32, vp]),
     "dmp_gemm_ref_f32out": (i32, [i32, vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i32, vp]),
+    "dmp_conv_igemm_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_conv_igemm_wgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     # optimizer
     "dmp_sgd_flat": (i32, [vp, vp, vp, i32, vp, i64, vp, i32, i32, vp]),
     "dmp_cast_flat": (i32, [vp, vp, i64, i32, vp]),

@@ -126,6 +126,9 @@ def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
     if (kh, kw) == (3, 3) and g == cin == cout and conv.padding == (1, 1) and conv.stride in ((1, 1), (2, 2)) \
             and cin % 8 == 0:
         return "dw"
+    if g == 1 and kh == kw and kh % 2 == 1 and kh > 1 and conv.stride == (1, 1) and conv.padding == (kh // 2, kh // 2) \
+            and cin % 64 == 0 and cout % 8 == 0:
+        return "igemm"
     if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
             and cin * kh * kw * cout * 4 <= 48 * 1024 and cin * kh * kw * (cout // 8) <= 1024:
         return "stem"
@@ -171,7 +174,17 @@ def _conv_fwd_cuda(x, w, conv, kind):
                                   s, p, sp), "stem conv fwd")
         _note("conv_stem:direct")
         return y, x
-    # generic: library convolution (dense 3x3 / 7x7 until the implicit-GEMM kernel covers them)
+    if kind == "igemm":
+        _, cin, H, W = x.shape
+        kh, kw = conv.kernel_size
+        cout = conv.out_channels
+        wp = weight_bf16(w).permute(0, 2, 3, 1).reshape(cout, kh * kw * cin).contiguous()  # [Cout][kh][kw][Cin]
+        y = _cl_empty(N, cout, H, W, x.device)
+        _ck(lib.dmp_conv_igemm_fwd(x.data_ptr(), wp.data_ptr(), None, y.data_ptr(), N, H, W, cin, cout, kh, kw, conv.padding[0], sp),
+            "conv igemm fwd")
+        _note("conv_dense:tcgen05_igemm")
+        return y, x
+    # generic: library convolution (strided dense convolutions, 7x7 stem of ResNet-50)
     x = _as_cl_bf16(x)
     y = F.conv2d(x, weight_bf16(w), None, conv.stride, conv.padding, conv.dilation, conv.groups)
     _note("conv_generic:cudnn")
@@ -235,6 +248,32 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
                                         kh, kw, s, p, 1 if accumulate else 0, sp), "stem conv wgrad")
 
         return None, write_dw
+    if kind == "igemm":
+        _, cin, H, W = x.shape
+        kh, kw = conv.kernel_size
+        cout = conv.out_channels
+        if need_dx:
+            if cout % 64 == 0:
+                # dx = conv(dy, flipped filter with in/out channels swapped): the same implicit-GEMM kernel
+                wd = weight_bf16(w).permute(1, 2, 3, 0).flip(1, 2).reshape(cin, kh * kw * cout).contiguous()
+                dx = _cl_empty(N, cin, H, W, x.device)
+                _ck(lib.dmp_conv_igemm_fwd(dy.data_ptr(), wd.data_ptr(), None, dx.data_ptr(), N, H, W, cout, cin, kh, kw,
+                                           conv.padding[0], sp), "conv igemm dgrad")
+            else:
+                dx = torch.ops.aten.convolution_backward(dy, x, weight_bf16(w), None, conv.stride, conv.padding, conv.dilation, False,
+                                                         (0, 0), conv.groups, (True, False, False))[0]
+
+        def write_dw(dst, accumulate):
+            dwp = torch.zeros((cout, kh * kw * cin), device=x.device, dtype=torch.float32)
+            _ck(lib.dmp_conv_igemm_wgrad(dy.data_ptr(), x.data_ptr(), dwp.data_ptr(), N, H, W, cin, cout, kh, kw, conv.padding[0], sp),
+                "conv igemm wgrad")
+            g = dwp.view(cout, kh, kw, cin).permute(0, 3, 1, 2)
+            if accumulate:
+                dst.add_(g)
+            else:
+                dst.copy_(g)
+
+        return dx, write_dw
     # generic
     wb = weight_bf16(w)
     gi, gw, _ = torch.ops.aten.convolution_backward(dy, x, wb, None, conv.stride, conv.padding, conv.dilation, False, (0, 0),

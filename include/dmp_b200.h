@@ -35,6 +35,16 @@ int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* B, long 
 int dmp_gemm_ref_f32out(int layout, const void* A, long long lda, const void* B, long long ldb, float* D, long long ldd,
                         int M, int N, int K, const float* bias, int accumulate, dmp_stream_t stream); /* CUDA-core oracle */
 
+/* ------------------------------------------------------------------ implicit-GEMM dense convolution (csrc/kernels/conv_igemm_tcgen05.cu)
+ * 'same' stride-1 KxK convolution on channels-last bf16: 4-D TMA boxes with zero-filled halo feed tcgen05.mma, no im2col buffer.
+ * NOT IN REFERENCE beyond its Cin=3 stem (R/model/mobilenetv2.py:52); serves the ResNet/VGG configs.  wp = weight permuted to
+ * [Cout][kh][kw][Cin] (bf16).  The stride-1 data gradient is dmp_conv_igemm_fwd on dy with the flipped, transposed filter.
+ * dmp_conv_igemm_wgrad accumulates into dwp (fp32, [Cout][kh][kw][Cin]) with split-K atomics. */
+int dmp_conv_igemm_fwd(const void* x, const void* wp, const float* bias, void* y, int N, int H, int W, int Cin, int Cout, int KH,
+                       int KW, int pad, dmp_stream_t stream);
+int dmp_conv_igemm_wgrad(const void* dy, const void* x, float* dwp, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
+                         dmp_stream_t stream);
+
 /* ------------------------------------------------------------------ optimizer (csrc/kernels/sgd.cu; R/data_parallel.py:90-91,111)
  * hp_dev = device {lr, momentum, weight_decay, grad_scale}. */
 int dmp_sgd_flat(float* master, void* shadow_bf16, void* grad, int grad_dtype, float* momentum, long long n,

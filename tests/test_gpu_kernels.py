@@ -368,3 +368,37 @@ def test_batchnorm_fused_single_launch(M, C, relu, res):
         if res:
             _close(dres, rr.grad, 1e-2, 1e-2, "fused bn dres", 1e-5 if relu else 0.0)
     assert int(nbt.item()) == 3
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,k", [(4, 32, 64, 128, 3), (8, 8, 128, 64, 3), (16, 4, 256, 256, 3), (2, 14, 64, 64, 3), (3, 7, 128, 192, 3),
+                                             (1, 56, 64, 64, 3), (2, 16, 64, 32, 5)])
+def test_conv_igemm_tcgen05(N, H, Cin, Cout, k):
+    """Implicit-GEMM dense convolution (fwd, dgrad via the flipped filter, wgrad) vs F.conv2d in fp32."""
+    nat = _lib()
+    lib = nat.kernels()
+    sp = _sp()
+    torch.manual_seed(N * H + Cin + Cout)
+    pad = k // 2
+    x = torch.randn(N, H, H, Cin, device="cuda").bfloat16()
+    w = (torch.randn(Cout, Cin, k, k, device="cuda") * (1.0 / (Cin * k * k) ** 0.5)).bfloat16()
+    wp = w.permute(0, 2, 3, 1).reshape(Cout, k * k * Cin).contiguous()
+    y = torch.empty(N, H, H, Cout, device="cuda", dtype=torch.bfloat16)
+    nat.check(lib.dmp_conv_igemm_fwd(x.data_ptr(), wp.data_ptr(), None, y.data_ptr(), N, H, H, Cin, Cout, k, k, pad, sp), "igemm fwd")
+    xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_()
+    wr = w.float().clone().requires_grad_()
+    yr = F.conv2d(xr, wr, None, 1, pad)
+    torch.cuda.synchronize()
+    _close(y, yr.permute(0, 2, 3, 1), 2e-2, 2e-2, "igemm fwd")
+    dy = torch.randn(N, H, H, Cout, device="cuda").bfloat16()
+    yr.backward(dy.float().permute(0, 3, 1, 2))
+    if Cout % 64 == 0:
+        wd = w.permute(1, 2, 3, 0).flip(1, 2).reshape(Cin, k * k * Cout).contiguous()
+        dx = torch.empty(N, H, H, Cin, device="cuda", dtype=torch.bfloat16)
+        nat.check(lib.dmp_conv_igemm_fwd(dy.data_ptr(), wd.data_ptr(), None, dx.data_ptr(), N, H, H, Cout, Cin, k, k, pad, sp), "igemm dgrad")
+        torch.cuda.synchronize()
+        _close(dx, xr.grad.permute(0, 2, 3, 1), 2e-2, 2e-2 * xr.grad.abs().max().item(), "igemm dgrad")
+    dwp = torch.zeros(Cout, k * k * Cin, device="cuda")
+    nat.check(lib.dmp_conv_igemm_wgrad(dy.data_ptr(), x.data_ptr(), dwp.data_ptr(), N, H, H, Cin, Cout, k, k, pad, sp), "igemm wgrad")
+    torch.cuda.synchronize()
+    dw = dwp.view(Cout, k, k, Cin).permute(0, 3, 1, 2)
+    _close(dw, wr.grad, 1e-2, 1e-2 * wr.grad.abs().max().item(), "igemm wgrad")
