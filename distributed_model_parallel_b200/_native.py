@@ -66,6 +66,10 @@ _KERNEL_SIGS = {
     "dmp_linear_small_bwd": (i32, [vp, vp, vp, i32, vp, vp, vp, i32, i32, i32, i32, vp]),
     "dmp_add_act": (i32, [vp, vp, vp, i64, i32, vp]),
     "dmp_relu_bwd": (i32, [vp, vp, vp, i64, vp]),
+    # NVLS multicast objects (csrc/comm/multicast.cu)
+    "dmp_mc_supported": (i32, [vp, i32]),
+    "dmp_mc_create": (i32, [vp, i32, i64, vp, vp, vp, vp]),
+    "dmp_mc_destroy": (i32, [vp]),
     # peer-memory collectives and plumbing (csrc/comm/collectives.cu)
     "dmp_comm_state_bytes": (C.c_longlong, []),
     "dmp_comm_max_ranks": (C.c_int, []),

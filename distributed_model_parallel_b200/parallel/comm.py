@@ -24,6 +24,7 @@ import torch.distributed as dist
 from .. import _native
 
 DEFAULT_BUFFER_BYTES = 10 * 1024 * 1024  # torch default: 10 MiB coalescing buffer
+stats: Dict[str, int] = {}               # which transport served broadcast chunks (multicast vs peer stores)
 
 
 def _dev(d) -> torch.device:
@@ -104,6 +105,28 @@ def _all_cuda(devs) -> bool:
 
 
 _peer_enabled = set()
+_active_arena = None  # MulticastArena used by broadcast_coalesced while a DataParallel forward is replicating
+
+
+class use_multicast_arena:
+    """Route ``broadcast_coalesced`` destination buffers into an NVLS multicast arena (one multimem.st pass per chunk)."""
+
+    def __init__(self, arena):
+        self.arena = arena
+
+    def __enter__(self):
+        global _active_arena
+        self._old = _active_arena
+        _active_arena = self.arena
+        if self.arena is not None:
+            self.arena.reset()
+        return self
+
+    def __exit__(self, *exc):
+        global _active_arena
+        _active_arena = self._old
+        return False
+
 
 
 def _ensure_peer_access(devs: Sequence[torch.device]):
@@ -154,12 +177,25 @@ def _broadcast_coalesced_impl(tensors, devs, outputs, buffer_size):
             ev.record(torch.cuda.current_stream(d))
             src_stream.wait_event(ev)
         with torch.cuda.device(src_dev):
+            arena = _active_arena
+            if arena is not None and [d.index for d in devs] != arena.devices[: len(devs)]:
+                arena = None
             for chunk in chunks:
                 flat = flatten_dense(chunk, _pad_elems(chunk[0].dtype))
-                dsts = [torch.empty(flat.numel(), dtype=flat.dtype, device=d) for d in devs[1:]]
-                arr = ptr_array([t.data_ptr() for t in dsts])
-                _native.check(lib.dmp_broadcast(flat.data_ptr(), arr, len(dsts), None, None, flat.numel() * flat.element_size(),
-                                                None, 0, len(devs), 1, 0, src_stream.cuda_stream), "broadcast")
+                nbytes = flat.numel() * flat.element_size()
+                off = arena.take(nbytes) if (arena is not None and len(devs) == len(arena.devices)) else None
+                if off is not None:
+                    # NVLS: one multimem.st pass lands in every replica's copy of the arena
+                    dsts = [arena.views[k + 1][off: off + nbytes].view(flat.dtype) for k in range(len(devs) - 1)]
+                    _native.check(lib.dmp_broadcast(flat.data_ptr(), None, 0, arena.mc_ptr + off, None, nbytes, None, 0, len(devs), 1,
+                                                    0, src_stream.cuda_stream), "broadcast (multicast)")
+                    stats["multicast_chunks"] = stats.get("multicast_chunks", 0) + 1
+                else:
+                    dsts = [torch.empty(flat.numel(), dtype=flat.dtype, device=d) for d in devs[1:]]
+                    arr = ptr_array([t.data_ptr() for t in dsts])
+                    _native.check(lib.dmp_broadcast(flat.data_ptr(), arr, len(dsts), None, None, nbytes, None, 0, len(devs), 1, 0,
+                                                    src_stream.cuda_stream), "broadcast")
+                    stats["peer_store_chunks"] = stats.get("peer_store_chunks", 0) + 1
                 for k, dflat in enumerate(dsts):
                     for t, v in zip(chunk, unflatten_dense(dflat, chunk)):
                         outputs[k + 1][pos[id(t)]] = v

@@ -57,6 +57,8 @@ class DataParallel(nn.Module):
             _check_balance(self.devices)
         if len(self.devices) == 1:
             self.module.to(self.devices[0])
+        self._mc_arena = None
+        self._mc_tried = False
 
     def forward(self, *inputs: Any, **kwargs: Any) -> Any:
         with torch.autograd.profiler.record_function("DataParallel.forward"):
@@ -75,8 +77,29 @@ class DataParallel(nn.Module):
             outputs = self.parallel_apply(replicas, inputs, module_kwargs)
             return self.gather(outputs, self.output_device)
 
+    def _multicast_arena(self):
+        """NVLS multicast arena for the per-forward parameter/buffer broadcast (created once; None if unsupported or
+        disabled with DMP_DP_MULTICAST=0)."""
+        import os
+        if self._mc_tried:
+            return self._mc_arena
+        self._mc_tried = True
+        if os.environ.get("DMP_DP_MULTICAST", "1") == "0" or not all(d.type == "cuda" for d in self.devices) or len(self.devices) < 2:
+            return None
+        try:
+            from .symm import MulticastArena
+            total = sum(t.numel() * t.element_size() + 512 for t in chain(self.module.parameters(), self.module.buffers()))
+            self._mc_arena = MulticastArena([d.index for d in self.devices], total + (1 << 20))
+        except Exception as e:  # noqa: BLE001  (no NVSwitch multicast on this platform: keep peer stores)
+            warnings.warn("DataParallel: NVLS multicast unavailable (%s); broadcasting with peer stores" % str(e)[:120])
+            self._mc_arena = None
+        return self._mc_arena
+
     def replicate(self, module, devices):
-        return replicate(module, devices, not torch.is_grad_enabled())
+        from . import comm
+        arena = self._multicast_arena() if len(devices) == len(self.devices) else None
+        with comm.use_multicast_arena(arena):
+            return replicate(module, devices, not torch.is_grad_enabled())
 
     def scatter(self, inputs, kwargs, devices):
         return scatter_kwargs(inputs, kwargs, devices, dim=self.dim)

@@ -125,9 +125,6 @@ class DistributedDataParallel(nn.Module):
                  static_graph: bool = False, *, comm_backend: Optional[str] = None, fused_sgd: Optional[dict] = None,
                  first_bucket_bytes: int = DEFAULT_FIRST_BUCKET_BYTES):
         super().__init__()
-        if not (dist.is_available() and dist.is_initialized()) and process_group is None:
-            if comm_backend != "peer" or (torch.cuda.is_available() and False):
-                pass
         params_all = [p for p in module.parameters()]
         if not any(p.requires_grad for p in params_all):
             raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any parameter that "
@@ -257,8 +254,7 @@ class DistributedDataParallel(nn.Module):
             will_sync = torch.is_grad_enabled() and self.require_backward_grad_sync
             if will_sync and not self._rebuild_checked and self.reducer.stats["iterations"] >= 1:
                 self._rebuild_checked = True
-                if not self.static_graph or True:
-                    self.reducer.maybe_rebuild_buckets()
+                self.reducer.maybe_rebuild_buckets()
             if self.require_forward_param_sync and self.broadcast_buffers and self.training:
                 self._sync_buffers()
             if self.device_ids and self.device_type == "cuda":

@@ -143,3 +143,45 @@ class DeviceSymmGroup:
     def alloc(self, nbytes: int) -> List[torch.Tensor]:
         nbytes = max(256, (int(nbytes) + 255) // 256 * 256)
         return [torch.zeros(nbytes, dtype=torch.uint8, device=torch.device("cuda", d)) for d in self.devices]
+
+
+class MulticastArena:
+    """NVLS multicast-backed replica storage for one process driving several GPUs.
+
+    ``views[d]`` is a uint8 tensor over device d's copy, ``mc_ptr`` the multicast address: a ``multimem.st`` issued by ONE GPU
+    to ``mc_ptr + off`` lands at offset ``off`` of every device's copy.  ``take(nbytes)`` hands out offsets bump-pointer style;
+    ``reset()`` rewinds (DataParallel rewinds at the start of every forward, when the previous replicas are dead)."""
+
+    def __init__(self, devices: Sequence[int], nbytes: int):
+        self.lib = _native.kernels()
+        self.devices = [int(d) for d in devices]
+        n = len(self.devices)
+        devs = (C.c_int * n)(*self.devices)
+        if not self.lib.dmp_mc_supported(devs, n):
+            raise RuntimeError("NVLS multicast is not supported on these devices")
+        handle, mc, size = C.c_void_p(), C.c_void_p(), C.c_longlong()
+        uc = (C.c_void_p * n)()
+        _native.check(self.lib.dmp_mc_create(devs, n, int(nbytes), C.byref(handle), uc, C.byref(mc), C.byref(size)), "mc_create")
+        self._handle, self.mc_ptr, self.size = handle, mc.value, int(size.value)
+        self.views = [torch.as_tensor(_RawCuda(uc[i], self.size, self), device=torch.device("cuda", d))
+                      for i, d in enumerate(self.devices)]
+        self._off = 0
+
+    def reset(self):
+        self._off = 0
+
+    def take(self, nbytes: int) -> Optional[int]:
+        nbytes = (int(nbytes) + 255) // 256 * 256
+        if self._off + nbytes > self.size:
+            return None
+        off = self._off
+        self._off += nbytes
+        return off
+
+    def __del__(self):
+        try:
+            if self._handle:
+                self.lib.dmp_mc_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass

@@ -136,6 +136,13 @@ int dmp_reduce_add_peer(int dtype, void* const* src, int W, long long n, float s
                         dmp_stream_t stream);
 int dmp_comm_status(void* state_local, dmp_stream_t stream); /* 0 healthy, 1+peer: barrier with that peer timed out */
 
+/* NVLS multicast objects for one process driving several GPUs (csrc/comm/multicast.cu): per-device allocations bound to one
+ * multicast address; a multimem.st to out_mc (dmp_broadcast's mc_dst) lands in every device's copy (out_unicast[i]). */
+int dmp_mc_supported(const int* devs, int ndev);
+int dmp_mc_create(const int* devs, int ndev, long long bytes, void** out_handle, void** out_unicast, void** out_mc,
+                  long long* out_size);
+int dmp_mc_destroy(void* handle);
+
 /* peer-memory plumbing */
 int dmp_symm_malloc(long long bytes, void** out);
 int dmp_symm_free(void* p);

@@ -344,3 +344,34 @@ def _w_pipeline(rank, world, port, sched):
 @pytest.mark.parametrize("sched", ["naive", "gpipe", "1f1b"])
 def test_pipeline_nccl_p2p_matches_single_gpu(sched):
     _spawn(_w_pipeline, 2, sched)
+
+
+def test_multicast_broadcast_matches_source():
+    """NVLS path of broadcast_coalesced: one multimem.st pass must land bit-exact in every replica (skipped without NVLS)."""
+    import ctypes as C
+    from distributed_model_parallel_b200 import _native
+    from distributed_model_parallel_b200.parallel import comm
+    from distributed_model_parallel_b200.parallel.symm import MulticastArena
+
+    lib = _native.kernels()
+    n = min(torch.cuda.device_count(), 4)
+    devs = (C.c_int * n)(*range(n))
+    if not lib.dmp_mc_supported(devs, n):
+        pytest.skip("no NVLS multicast support on this box")
+    try:
+        arena = MulticastArena(list(range(n)), 8 << 20)
+    except RuntimeError as e:
+        pytest.skip("multicast object could not be created: %s" % str(e)[:100])
+    torch.manual_seed(0)
+    d0 = torch.device("cuda:0")
+    ts = [torch.randn(1000, 33, device=d0), torch.randn(7, device=d0), torch.arange(5, device=d0), torch.randn(300000, device=d0)]
+    for rep in range(2):
+        comm.stats.clear()
+        with comm.use_multicast_arena(arena):
+            outs = comm.broadcast_coalesced(ts, list(range(n)), buffer_size=1 << 20)
+        torch.cuda.synchronize()
+        assert comm.stats.get("multicast_chunks", 0) >= 2 and comm.stats.get("peer_store_chunks", 0) == 0
+        for k in range(1, n):
+            for a, b in zip(ts, outs[k]):
+                assert b.device.index == k and torch.equal(a.cpu(), b.cpu())
+        ts = [t + 1 for t in ts]
