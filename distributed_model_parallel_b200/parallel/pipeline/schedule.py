@@ -11,6 +11,7 @@ feed where the schedule allows, and every stage owns a private optimizer like th
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Callable, Dict, List, Optional
 
 import torch
@@ -50,7 +51,8 @@ class PipelineStage:
     (logits are shipped back to stage 0 and dlogits return, the reference's ring, utils.py:56-58)."""
 
     def __init__(self, module: nn.Module, stage: int, num_stages: int, group=None, optimizer=None,
-                 loss_fn: Optional[Callable] = None, schedule: str = "1f1b", loss_on: str = "last", device=None):
+                 loss_fn: Optional[Callable] = None, schedule: str = "1f1b", loss_on: str = "last", device=None,
+                 use_graphs: Optional[bool] = None):
         self.module, self.stage, self.W = module, stage, num_stages
         self.group = group
         self.optimizer = optimizer
@@ -74,7 +76,13 @@ class PipelineStage:
         self._logits_meta: Optional[p2p.TensorMeta] = None
         self._probe_key = None
         self._keepalive, self._send_works = [], []
-        self.stats = {"steps": 0, "p2p_messages": 0}
+        # CUDA-graph every micro-batch's stage forward and backward (static shapes): a micro-batch step is then two graph
+        # launches instead of hundreds of eager kernel launches, which is what makes GPipe/1F1B pay off on small models
+        if use_graphs is None:
+            use_graphs = os.environ.get("DMP_PIPELINE_GRAPHS", "1") != "0"
+        self.use_graphs = bool(use_graphs) and self.device.type == "cuda" and loss_on == "last"
+        self._slots, self._slots_key, self._gstream = None, None, None
+        self.stats = {"steps": 0, "p2p_messages": 0, "graph_replays": 0}
         if self.device.type == "cuda" and num_stages > 1:
             self._warmup_p2p()
 
@@ -151,7 +159,7 @@ class PipelineStage:
         return [base + (1 if i < rem else 0) for i in range(m) if base + (1 if i < rem else 0) > 0]
 
     # ------------------------------------------------------------------------------------------ data plane
-    def _exchange(self, send, recv_meta, recv_peer):
+    def _exchange(self, send, recv_meta, recv_peer, into: Optional[torch.Tensor] = None):
         """One grouped p2p round: optionally send ``send = (tensor, peer)`` and receive a tensor of ``recv_meta`` from
         ``recv_peer``.  Grouping (batch_isend_irecv) lets opposite-direction transfers between two stages proceed
         together; the received tensor is returned once it has landed, the send is reaped at the end of the step."""
@@ -161,7 +169,7 @@ class PipelineStage:
             self._keepalive.append(wire)
             ops.append(("send", wire, send[1]))
         if recv_meta is not None:
-            buf = recv_meta.empty(self.device)
+            buf = into if into is not None else recv_meta.empty(self.device)  # `into`: a static CUDA-graph input buffer
             ops.append(("recv", p2p.wire_view(buf), recv_peer))
         if _DEBUG:
             print("[pp stage %d] exchange %s" % (self.stage, [(k, tuple(t.shape), str(t.dtype), t.is_contiguous(), peer) for k, t, peer in ops]), flush=True)
@@ -176,6 +184,80 @@ class PipelineStage:
         else:
             self._send_works.extend(works)
         return buf
+
+    # ------------------------------------------------------------------------------------------ graphed micro-batch slots
+    def _zero_param_grads(self):
+        for p in self.module.parameters():
+            if p.grad is not None:
+                p.grad.zero_()
+
+    def _build_slots(self, mb: int, M: int, B: int, n_slots: int):
+        """Captures, for each of the ``n_slots`` micro-batches that can be in flight on this stage at once (M for GPipe,
+        at most W - stage for 1F1B), one CUDA graph of this stage's forward (plus the loss on the last stage) and one of its
+        backward, on static input / target / incoming-gradient buffers.  Micro-batch m uses slot m % n_slots."""
+        dev = self.device
+        in_meta = self._in_meta.with_batch(mb)
+        scale = float(mb) / float(B)
+        # ONE stream for the warm-up and every capture: autograd runs a parameter's AccumulateGrad node on the stream that was
+        # current when the node was created (the warm-up) and, at the end of backward, joins that stream into the caller's.
+        # With gradients delivered straight into the optimizer arena those nodes receive nothing, so a different stream would
+        # never have entered the capture and the join would be an illegal dependency on uncaptured work.
+        if self._gstream is None:
+            self._gstream = torch.cuda.Stream(device=dev)
+        side = self._gstream
+        side.wait_stream(torch.cuda.current_stream(dev))
+
+        def make_x():
+            x = in_meta.empty(dev)
+            x.zero_()
+            if not self.first and x.is_floating_point():
+                x.requires_grad_(True)
+            return x
+
+        with torch.cuda.stream(side):  # eager warm-up so that lazy initialisation does not end up inside a capture
+            for _ in range(2):
+                x = make_x()
+                y = self.module(x)
+                if self.last:
+                    y = self.loss_fn(y, torch.zeros(mb, dtype=torch.int64, device=dev)) * scale
+                    y.backward()
+                else:
+                    torch.autograd.backward(y, torch.zeros_like(y))
+            self._zero_param_grads()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        # One private memory pool per slot.  A backward capture returns the slot's saved activations to its pool, so with a
+        # shared pool the temporaries of another slot's graphs would be laid over them -- and under 1F1B a slot is re-filled
+        # (forward of micro-batch m + n_slots) while its neighbour's backward is still to run.  Inside a slot the forward is
+        # captured before the backward, and they replay in that order, so sharing there is safe.
+        slots = []
+        for m in range(n_slots):
+            pool = torch.cuda.graph_pool_handle()
+            sl = {"x": make_x(), "t": torch.zeros(mb, dtype=torch.int64, device=dev) if self.last else None}
+            sl["gf"] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(sl["gf"], pool=pool, stream=side):
+                y = self.module(sl["x"])
+                if self.last:
+                    y = self.loss_fn(y, sl["t"]) * scale
+            sl["y"] = y
+            sl["g"] = None if self.last else p2p.TensorMeta.of(y).empty(dev).zero_()
+            sl["gb"] = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(sl["gb"], pool=pool, stream=side):
+                if self.last:
+                    y.backward()
+                else:
+                    torch.autograd.backward(y, sl["g"])
+            sl["dx"] = sl["x"].grad if not self.first else None
+            slots.append(sl)
+        self._zero_param_grads()
+        self._slots, self._slots_key = slots, self._graph_key(mb, n_slots, B)
+
+    def _graph_key(self, mb: int, n_slots: int, B: int):
+        """Everything a captured micro-batch graph has baked in: shapes, the loss scale mb/B, and the addresses of the gradient
+        tensors it accumulates into (an optimizer that re-homes .grad, or zero_grad(set_to_none=True), forces a re-capture)."""
+        meta = self._in_meta.with_batch(mb)
+        grads = tuple(p.grad.data_ptr() if p.grad is not None else 0 for p in self.module.parameters())
+        return (mb, n_slots, B, tuple(meta.shape), meta.dtype, self.module.training, hash(grads))
 
     # ------------------------------------------------------------------------------------------ one training step
     def train_step(self, inputs: Optional[torch.Tensor] = None, targets: Optional[torch.Tensor] = None,
@@ -213,8 +295,58 @@ class PipelineStage:
         saved_out: Dict[int, torch.Tensor] = {}
         total_loss = None
         pending = None  # (tensor, peer) produced by the previous step, sent together with the next receive
+        graphed = self.use_graphs and len(set(sizes)) == 1
+        if graphed:
+            live = n_slots = 0  # micro-batches retire in FIFO order, so the deepest in-flight count is the number of slots
+            for o in order:
+                live += 1 if o > 0 else -1
+                n_slots = max(n_slots, live)
+            if self._slots_key != self._graph_key(sizes[0], n_slots, B):
+                self._slots = None  # releases the previous graphs and their pool
+                try:
+                    self._build_slots(sizes[0], M, B, n_slots)
+                except Exception as e:  # e.g. the module cannot be captured: keep training, eagerly (every stage decides alone;
+                    import warnings     # graphs change nothing on the wire)
+                    warnings.warn("pipeline stage %d: CUDA-graph capture failed (%s); running micro-batches eagerly" % (self.stage, e))
+                    torch.cuda.synchronize(self.device)
+                    self._slots, self._slots_key, self.use_graphs, graphed = None, None, False, False
+                    self._zero_param_grads()
         for op in order:
             m = abs(op) - 1
+            if graphed:  # ---------------------------------------------------------------- two graph launches per micro-batch
+                sl = self._slots[m % n_slots]
+                if op > 0:
+                    if m >= n_slots:
+                        p2p.wait_all(self._send_works)  # the slot's previous occupant: its sends must have left the buffers
+                        self._send_works = []
+                    if self.first:
+                        if pending is not None:
+                            self._exchange(pending, None, None)
+                            pending = None
+                        sl["x"].detach().copy_(in_chunks[m])
+                    else:
+                        self._exchange(pending, self._in_meta.with_batch(sizes[m]), self.prev, into=sl["x"].detach())
+                        pending = None
+                    if self.last:
+                        sl["t"].copy_(tgt_chunks[m])
+                    sl["gf"].replay()
+                    if self.last:
+                        total_loss = sl["y"].detach().clone() if total_loss is None else total_loss + sl["y"].detach()
+                    else:
+                        pending = (sl["y"], self.next)
+                else:
+                    if self.last:
+                        if pending is not None:
+                            self._exchange(pending, None, None)
+                            pending = None
+                    else:
+                        self._exchange(pending, p2p.TensorMeta.of(sl["g"]), self.next, into=sl["g"])
+                        pending = None
+                    sl["gb"].replay()
+                    if not self.first:
+                        pending = (sl["dx"], self.prev)
+                self.stats["graph_replays"] += 1
+                continue
             if op > 0:  # ---------------------------------------------------------------- forward of micro-batch m
                 if self.first:
                     if pending is not None:
@@ -268,7 +400,10 @@ class PipelineStage:
         self._keepalive, self._send_works = [], []
         if self.optimizer is not None:
             self.optimizer.step()
-            self.optimizer.zero_grad()
+            if graphed:
+                self.optimizer.zero_grad(set_to_none=False)  # captured graphs accumulate into these very tensors
+            else:
+                self.optimizer.zero_grad()
         self.stats["steps"] += 1
         return total_loss if loss_here else None
 
