@@ -20,6 +20,8 @@ from typing import Any, Optional, Sequence
 import torch
 import torch.nn as nn
 
+from ..utils.tracing import nvtx_range
+
 from .comm import _dev
 from .parallel_apply import parallel_apply
 from .replicate import replicate
@@ -68,14 +70,18 @@ class DataParallel(nn.Module):
                 if t.device != self.src_device_obj:
                     raise RuntimeError("module must have its parameters and buffers on device %s (device_ids[0]) but found "
                                        "one of them on device: %s" % (self.src_device_obj, t.device))
-            inputs, module_kwargs = self.scatter(inputs, kwargs, self.devices)
+            with nvtx_range("dp.scatter"):
+                inputs, module_kwargs = self.scatter(inputs, kwargs, self.devices)
             if not inputs and not module_kwargs:  # forward without arguments
                 inputs, module_kwargs = ((),), ({},)
             if len(self.devices) == 1:
                 return self.module(*inputs[0], **module_kwargs[0])
-            replicas = self.replicate(self.module, self.devices[: len(inputs)])
-            outputs = self.parallel_apply(replicas, inputs, module_kwargs)
-            return self.gather(outputs, self.output_device)
+            with nvtx_range("dp.replicate"):
+                replicas = self.replicate(self.module, self.devices[: len(inputs)])
+            with nvtx_range("dp.parallel_apply"):
+                outputs = self.parallel_apply(replicas, inputs, module_kwargs)
+            with nvtx_range("dp.gather"):
+                return self.gather(outputs, self.output_device)
 
     def _multicast_arena(self):
         """NVLS multicast arena for the per-forward parameter/buffer broadcast (created once; None if unsupported or

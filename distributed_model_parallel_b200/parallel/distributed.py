@@ -199,6 +199,7 @@ class DistributedDataParallel(nn.Module):
         if isinstance(self.backend, PeerBackend) and self.backend.symm is not None and self.modules_buffers and broadcast_buffers:
             self._build_buffer_arena()
         self._rebuild_checked = False
+        self._join_active, self._join_iters = False, 0
         self.logger_data = {"backend": self.backend.name, "world_size": self.world_size,
                             "bucket_cap_bytes": self.bucket_bytes_cap}
 
@@ -211,9 +212,9 @@ class DistributedDataParallel(nn.Module):
             if s != shapes:
                 raise RuntimeError("DDP parameter shapes differ between rank %d and rank %d" % (self.rank, r))
 
-    def _sync_module_states(self):
+    def _sync_module_states(self, src: int = 0):
         tensors = [p.detach() for p in self._params] + list(self.modules_buffers)
-        broadcast_coalesced_group(self.process_group, tensors, BROADCAST_BUCKET_BYTES, src=0)
+        broadcast_coalesced_group(self.process_group, tensors, BROADCAST_BUCKET_BYTES, src=src)
 
     def _build_buffer_arena(self):
         """Moves every buffer (BN running statistics, counters) into one peer-visible byte arena so that the per-forward
@@ -252,6 +253,9 @@ class DistributedDataParallel(nn.Module):
     def forward(self, *inputs, **kwargs):
         with torch.autograd.profiler.record_function("DistributedDataParallel.forward"):
             will_sync = torch.is_grad_enabled() and self.require_backward_grad_sync
+            if self._join_active:
+                self._join_count(1)  # tells the ranks that already ran out of data that one more iteration is coming
+                self._join_iters += 1
             if will_sync and not self._rebuild_checked and self.reducer.stats["iterations"] >= 1:
                 self._rebuild_checked = True
                 self.reducer.maybe_rebuild_buckets()
@@ -284,6 +288,47 @@ class DistributedDataParallel(nn.Module):
             yield
         finally:
             self.require_backward_grad_sync = old
+
+    # ------------------------------------------------------------------------------------------ uneven inputs
+    def _join_count(self, mine: int) -> int:
+        dev = self._params[0].device if dist.get_backend(self.process_group) == "nccl" else "cpu"
+        t = torch.tensor([mine], dtype=torch.int32, device=dev)
+        dist.all_reduce(t, group=self.process_group)
+        return int(t.item())
+
+    @contextlib.contextmanager
+    def join(self, divide_by_initial_world_size: bool = True, enable: bool = True):
+        """Training with a different number of batches per rank (torch distributed.py ``join``, the Join hook
+        ``_DDPJoinHook``).  Inside the context every forward first all-reduces a one ("I am still training"); a rank that
+        leaves the context keeps answering with a zero and, while the sum is positive, *shadows* the iteration of the others:
+        the per-forward buffer broadcast and one all-reduce per gradient bucket with a zero contribution, in bucket order,
+        so that nobody blocks in a collective.  Gradients are divided by the initial world size (the only mode offered).
+        With the fused all-reduce + SGD kernel a shadowing rank applies the same update as everyone else and stays in
+        sync; otherwise the parameters of the rank that trained longest are broadcast to all when the last rank leaves.
+        The reference never has to deal with this: its loaders give every rank the same number of batches
+        (model_parallel.py:92-97)."""
+        if not divide_by_initial_world_size:
+            raise ValueError("join(divide_by_initial_world_size=False) is not supported: the 1/W scale is compiled into the "
+                             "bucket kernels' launch arguments")
+        if not enable or self.world_size == 1:
+            yield
+            return
+        self._join_active, self._join_iters = True, 0
+        try:
+            yield
+        finally:
+            self._join_active = False
+            while self._join_count(0) > 0:
+                if self.require_forward_param_sync and self.broadcast_buffers and self.training:
+                    self._sync_buffers()
+                self.reducer.shadow_iteration()
+            # whoever trained longest owns the final model (ties: highest rank), unless the fused optimizer kept all in sync
+            best = self._join_iters * self.world_size + self.rank
+            dev = self._params[0].device if dist.get_backend(self.process_group) == "nccl" else "cpu"
+            t = torch.tensor([best], dtype=torch.int64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.process_group)
+            if self.optimizer is None:
+                self._sync_module_states(src=int(t.item()) % self.world_size)
 
     # ------------------------------------------------------------------------------------------ hooks / misc API
     def register_comm_hook(self, state: Any, hook: Callable):

@@ -19,6 +19,7 @@ import torch.distributed as dist
 import torch.nn as nn
 
 from ... import _native
+from ...utils.tracing import nvtx_range
 from . import p2p
 from .partition import partition_balanced  # noqa: F401  (registers the runtime signatures)
 
@@ -329,7 +330,8 @@ class PipelineStage:
                         pending = None
                     if self.last:
                         sl["t"].copy_(tgt_chunks[m])
-                    sl["gf"].replay()
+                    with nvtx_range("pp.s%d.F%d" % (self.stage, m)):
+                        sl["gf"].replay()
                     if self.last:
                         total_loss = sl["y"].detach().clone() if total_loss is None else total_loss + sl["y"].detach()
                     else:
@@ -342,7 +344,8 @@ class PipelineStage:
                     else:
                         self._exchange(pending, p2p.TensorMeta.of(sl["g"]), self.next, into=sl["g"])
                         pending = None
-                    sl["gb"].replay()
+                    with nvtx_range("pp.s%d.B%d" % (self.stage, m)):
+                        sl["gb"].replay()
                     if not self.first:
                         pending = (sl["dx"], self.prev)
                 self.stats["graph_replays"] += 1
@@ -358,7 +361,8 @@ class PipelineStage:
                     pending = None
                     if x.is_floating_point():
                         x.requires_grad_(True)
-                y = self.module(x)
+                with nvtx_range("pp.s%d.F%d" % (self.stage, m)):
+                    y = self.module(x)
                 saved_in[m] = x
                 if not self.last:
                     saved_out[m] = y

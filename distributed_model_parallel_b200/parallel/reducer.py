@@ -28,6 +28,7 @@ import torch.distributed as dist
 
 from .. import _native
 from ..ops import functional as OF
+from ..utils.tracing import nvtx_range
 
 _native.register_runtime_sigs({
     "dmp_bucket_assign": (C.c_int, [C.c_int, C.POINTER(C.c_int64), C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.c_int,
@@ -444,6 +445,19 @@ class Reducer:
         self._unused_local = list(unused_indices)
         self._direct_marked = set()
 
+    def shadow_iteration(self):
+        """One backward's worth of collectives with a zero contribution from this rank (DistributedDataParallel.join): every
+        bucket is launched, in bucket order, exactly as the ranks that are still training launch theirs."""
+        self.require_sync = True
+        self.prepare_for_backward(())
+        for bk in self.buckets:
+            if bk.fused is None:
+                bk.flat.zero_()
+        self._unused_local = list(range(len(self.params)))
+        for i in self._unused_local:
+            self._mark(i, unused=True)
+        self.finalize_backward()
+
     def _grad_ready(self, i: int, param, direct: bool = False):
         if not self.require_sync or not self._in_backward:
             return
@@ -480,7 +494,8 @@ class Reducer:
         if self.comm_hook is not None:
             bk.future = self.comm_hook(self.comm_hook_state, GradBucket(bk, bk.index == len(self.buckets) - 1))
         else:
-            self.backend.launch(bk)
+            with nvtx_range("ddp.bucket%d" % bk.index):
+                self.backend.launch(bk)
 
     def finalize_backward(self):
         if not self._in_backward:
@@ -503,14 +518,40 @@ class Reducer:
             else:
                 self.backend.wait(bk)
         self.backend.end_iteration()
+        globally_unused = self._globally_unused()
         if not self.grad_as_view:
             for bk in self.buckets:
                 for p, v in zip(bk.params, bk.views):
+                    if id(p) in globally_unused:
+                        continue
                     if p.grad is not None:
                         p.grad.copy_(v)
                     else:
                         p.grad = v.clone()
+        elif globally_unused:
+            for p in self.params:
+                if id(p) in globally_unused:
+                    p.grad = None
         self.stats["iterations"] += 1
+
+    def _globally_unused(self) -> set:
+        """Parameters no rank used in this iteration keep their ``.grad`` untouched (None with the usual set-to-none
+        zero_grad), as in torch's reducer (its all-reduced ``local_used_map``): an optimizer with weight decay or momentum must
+        not move a parameter that took no part.  One extra small all-reduce, only with find_unused_parameters=True; not
+        offered with the fused optimizer, whose update has already run inside the bucket kernels."""
+        W = getattr(self.backend, "world_size", 1)
+        if not self.find_unused or self.fused_cfg is not None or W <= 1 or not (dist.is_available() and dist.is_initialized()):
+            return set()
+        group = self.backend.group
+        dev = self.params[0].device if dist.get_backend(group) == "nccl" else "cpu"
+        used = torch.ones(len(self.params), dtype=torch.int32)
+        if self._unused_local:
+            used[torch.tensor(self._unused_local, dtype=torch.long)] = 0
+        used = used.to(dev)
+        dist.all_reduce(used, group=group)
+        idx = (used == 0).nonzero().flatten().tolist()
+        self.stats["globally_unused"] = len(idx)
+        return {id(self.params[i]) for i in idx}
 
     # -------------------------------------------------------------------------------- rebuild
     def maybe_rebuild_buckets(self) -> bool:

@@ -126,6 +126,24 @@ class ProcessSymmGroup:
         return self.alloc(int(self.lib.dmp_comm_state_bytes()))
 
 
+def comm_status_words(state: SymmBuffer) -> torch.Tensor:
+    """The four trailing uint32 words of a communicator state: [0] status (0 healthy, 1 + peer = that peer never arrived),
+    [1] spin timeout in milliseconds (0 = built-in default), [2..3] reserved."""
+    words = int(_native.kernels().dmp_comm_state_bytes()) // 4
+    return state.local.view(torch.int32)[words - 4: words]
+
+
+def set_comm_timeout_ms(state: SymmBuffer, ms: int) -> None:
+    """Bounds every cross-GPU spin-wait of the collectives that use ``state`` (fault detection: a dead or diverged peer
+    turns into a status code within ``ms`` instead of a hung kernel).  The reference has no timeout anywhere
+    (model_parallel.py:57-58 passes none to init_process_group)."""
+    comm_status_words(state)[1] = int(ms)
+
+
+def reset_comm_status(state: SymmBuffer) -> None:
+    comm_status_words(state)[0] = 0
+
+
 class DeviceSymmGroup:
     """Peer-addressable buffers across several devices of one process (DataParallel)."""
 

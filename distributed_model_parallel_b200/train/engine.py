@@ -16,6 +16,7 @@ import torch.nn as nn
 
 from .. import _native
 from ..ops import functional as OF
+from ..utils.tracing import nvtx_range
 
 
 class TrainStep:
@@ -85,7 +86,8 @@ class TrainStep:
         if self.graph is not None:
             if hasattr(self.optimizer, "push_hyperparameters"):
                 self.optimizer.push_hyperparameters()
-            self.graph.replay()
+            with nvtx_range("train_step.graph"):
+                self.graph.replay()
         else:
             c0 = _native.launch_count()
             self._iteration()

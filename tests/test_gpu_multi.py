@@ -74,6 +74,80 @@ def test_allreduce_oneshot_twoshot():
     _spawn(_w_allreduce)
 
 
+# ------------------------------------------------------------------------------------------------ fault injection / races
+def _w_dead_peer(rank, world, port):
+    """A rank that never joins the collective (a dead peer) must turn into a status code, not a hung kernel."""
+    _init(rank, world, port)
+    from distributed_model_parallel_b200 import _native
+    from distributed_model_parallel_b200.parallel.symm import DTYPE_CODE, ProcessSymmGroup, set_comm_timeout_ms
+
+    lib = _native.kernels()
+    g = ProcessSymmGroup()
+    state = g.new_state()
+    set_comm_timeout_ms(state, 200)
+    sp = torch.cuda.current_stream().cuda_stream
+    n = 1 << 16
+    buf = g.alloc(n * 4)
+    buf.view(torch.float32, n).fill_(1.0)
+    torch.cuda.synchronize()
+    dist.barrier()
+    if rank == 0:  # rank 1 "died": it never launches its half
+        import time
+
+        t0 = time.time()
+        _native.check(lib.dmp_allreduce_fused(1, DTYPE_CODE[torch.float32], buf.ptrs, state.ptrs, rank, world, n, 0.5, None, None,
+                                              None, None, None, 0, None, None, 0, 0, sp), "allreduce")
+        torch.cuda.synchronize()
+        dt = time.time() - t0
+        code = lib.dmp_comm_status(state.local.data_ptr(), sp)
+        assert code == 1 + 1, code          # 1 + the rank that never arrived
+        assert dt < 5.0, dt                  # bounded by the 200 ms timeout per barrier, not by a watchdog
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_dead_peer_times_out_with_status():
+    _spawn(_w_dead_peer)
+
+
+def _w_flag_stress(rank, world, port):
+    """Flag-protocol stress: thousands of back-to-back collectives with randomised launch skew between the ranks."""
+    _init(rank, world, port)
+    from distributed_model_parallel_b200 import _native
+    from distributed_model_parallel_b200.parallel.symm import DTYPE_CODE, ProcessSymmGroup
+
+    lib = _native.kernels()
+    g = ProcessSymmGroup()
+    state = g.new_state()
+    sp = torch.cuda.current_stream().cuda_stream
+    n = 4096
+    buf = g.alloc(n * 4)
+    t = buf.view(torch.float32, n)
+    out = torch.empty(n, device="cuda")
+    acc = torch.zeros((), device="cuda", dtype=torch.float64)
+    gen = torch.Generator().manual_seed(1234 + rank)
+    iters = int(os.environ.get("DMP_STRESS_ITERS", "3000"))
+    skews = torch.randint(0, 40000, (iters,), generator=gen).tolist()
+    for it in range(iters):
+        if skews[it] > 20000:
+            torch.cuda._sleep(skews[it])                       # device-side skew: this rank's kernel starts late
+        t.fill_(float(it % 7 + rank))                          # written before the collective, read by the peers inside it
+        algo = it & 1
+        _native.check(lib.dmp_allreduce_fused(algo, 0, buf.ptrs, state.ptrs, rank, world, n, 1.0, _native.ptr(out) if algo == 0 else None,
+                                              None, None, None, None, 0, None, None, 0, 0, sp), "allreduce")
+        want = float(world * (it % 7) + sum(range(world)))
+        acc += ((out if algo == 0 else t) - want).abs().max().double()
+    torch.cuda.synchronize()
+    assert float(acc) == 0.0, float(acc)
+    assert lib.dmp_comm_status(state.local.data_ptr(), sp) == 0
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_flag_protocol_stress_random_skew():
+    _spawn(_w_flag_stress)
+
+
 def _w_fused_sgd(rank, world, port):
     _init(rank, world, port)
     from distributed_model_parallel_b200 import _native

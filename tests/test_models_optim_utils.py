@@ -170,4 +170,24 @@ def test_ops_reference_path_and_cross_entropy_stats():
     assert OF.conv_kind(nn.Conv2d(16, 32, 1, bias=False), x) == "pw"
     assert OF.conv_kind(nn.Conv2d(16, 16, 3, padding=1, groups=16, bias=False), x) == "dw"
     assert OF.conv_kind(nn.Conv2d(3, 32, 3, padding=1, bias=False), x) == "stem"
-    assert OF.conv_kind(nn.Conv2d(64, 64, 3, padding=1, bias=False), x) == "generic"
+    assert OF.conv_kind(nn.Conv2d(64, 64, 3, padding=1, bias=False), x) == "igemm"
+    assert OF.conv_kind(nn.Conv2d(48, 64, 3, padding=1, bias=False), x) == "generic"
+
+
+def test_tracing_ranges_record_framework_phases():
+    """NVTX ranges are off by default and, once enabled, bracket the framework phases."""
+    from distributed_model_parallel_b200.utils import tracing
+
+    tracing.events.clear()
+    with tracing.nvtx_range("off"):
+        pass
+    assert not tracing.enabled() and len(tracing.events) == 0
+    tracing.enable(True)
+    try:
+        with tracing.nvtx_range("phase.a"):
+            tracing.mark("inside")
+        names = [n for n, _ in tracing.events]
+        assert names == ["inside", "phase.a"]
+    finally:
+        tracing.enable(False)
+        tracing.events.clear()
