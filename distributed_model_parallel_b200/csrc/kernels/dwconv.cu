@@ -120,6 +120,69 @@ dw_dgrad_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __r
     store8(dx + (((long long)n * H + hi) * W + wi) * C + ch0, acc);
 }
 
+// Stride-2 data gradient by output parity.  With pad 1 and even H, W the 2x2 block of dx at rows 2a..2a+1, columns 2b..2b+1
+// reads exactly dy[a..a+1][b..b+1] and uses each of the nine taps once:
+//   dx[2a  ][2b  ] = dy[a][b] w11                       dx[2a  ][2b+1] = dy[a][b+1] w10 + dy[a][b] w12
+//   dx[2a+1][2b  ] = dy[a+1][b] w01 + dy[a][b] w21      dx[2a+1][2b+1] = dy[a+1][b+1] w00 + dy[a+1][b] w02 + dy[a][b+1] w20 + dy[a][b] w22
+// One thread writes two such blocks (2 x 4 pixels of its 8 channels) from six 16-byte loads -- no divisibility tests, 0.75
+// loads per output instead of 2.25, and the 72 weights are fetched once per eight outputs instead of once per output.
+template <typename WT>
+__global__ void __launch_bounds__(DW_THREADS, 2)
+dw_dgrad_s2_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __restrict__ dx, int N, int H, int W, int C,
+                   int Ho, int Wo) {
+    constexpr int TQ = 2;
+    const int P = C >> 3;
+    const int tiles_w = (Wo + TQ - 1) / TQ;
+    const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
+    const long long total = (long long)N * Ho * tiles_w * P;
+    if (idx >= total) return;
+    const int cv = (int)(idx % P);
+    long long t = idx / P;
+    const int tw = (int)(t % tiles_w); t /= tiles_w;
+    const int a = (int)(t % Ho);
+    const int n = (int)(t / Ho);
+    const int ch0 = cv * 8;
+    const int b0 = tw * TQ;
+    float wt[72];
+    load_w72<WT>(w, ch0, wt);
+    float d0[TQ + 1][8], d1[TQ + 1][8];
+#pragma unroll
+    for (int c = 0; c <= TQ; ++c) {
+        const int col = b0 + c;
+        const bool okc = col < Wo;
+        if (okc) load8(dy + (((long long)n * Ho + a) * Wo + col) * C + ch0, d0[c]);
+        else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) d0[c][j] = 0.f;
+        }
+        if (okc && a + 1 < Ho) load8(dy + (((long long)n * Ho + a + 1) * Wo + col) * C + ch0, d1[c]);
+        else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) d1[c][j] = 0.f;
+        }
+    }
+#pragma unroll
+    for (int q = 0; q < TQ; ++q) {
+        const int b = b0 + q;
+        if (b >= Wo) break;
+        float o00[8], o01[8], o10[8], o11[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float* k = wt + j * 9;
+            o00[j] = d0[q][j] * k[4];
+            o01[j] = d0[q + 1][j] * k[3] + d0[q][j] * k[5];
+            o10[j] = d1[q][j] * k[1] + d0[q][j] * k[7];
+            o11[j] = d1[q + 1][j] * k[0] + d1[q][j] * k[2] + d0[q + 1][j] * k[6] + d0[q][j] * k[8];
+        }
+        bf16* r0 = dx + (((long long)n * H + 2 * a) * W + 2 * b) * C + ch0;
+        bf16* r1 = r0 + (long long)W * C;
+        store8(r0, o00);
+        store8(r0 + C, o01);
+        store8(r1, o10);
+        store8(r1 + C, o11);
+    }
+}
+
 // Strip version of the forward stencil: one thread produces TW horizontally adjacent output pixels of its 8 channels,
 // so every input vector of a row is loaded once and reused by up to 3 outputs (4.5 instead of 9 loads per output at
 // stride 1).  FLIP=true mirrors the taps: with stride 1 the data gradient is the same stencil applied to dy.
@@ -348,6 +411,11 @@ DMP_API int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void
         const int grid = dmp_ceil_div(total, DW_THREADS);
         if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W);
         else dw_strip_kernel<bf16, 1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, H, W);
+    } else if (stride == 2 && H % 2 == 0 && W % 2 == 0) {
+        const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0) dw_dgrad_s2_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, Ho, Wo);
+        else dw_dgrad_s2_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, Ho, Wo);
     } else {
         const long long total = (long long)N * H * W * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);

@@ -32,6 +32,16 @@ struct GemmParams {
 
 // Persistent kernel: CTA b processes work items b, b+gridDim.x, ...  A work item is one 128 x BN output tile of one
 // K split.  Two TMEM accumulator buffers let the epilogue of item i overlap the TMA/MMA of item i+1.
+// Depth of the TMA -> MMA shared-memory ring.  These GEMMs are memory-bound (K is a handful of 64-wide blocks forward, or a
+// very long split pixel axis for the weight gradient), so what matters is bytes in flight per SM: HBM needs roughly
+// 7.7 TB/s x ~1 us / 148 SMs = 50 KB outstanding per SM to stay busy, and a 3-stage ring holds at most two stages of loads
+// (32-64 KB) in the air.  One CTA per SM owns the whole 227 KB, so the ring takes ~200 KB of it: 6 stages at BN=128, 8 below.
+constexpr int gemm_stages(int b_rows) {
+    const int per = BM * BK * 2 + b_rows * BK * 2;
+    const int s = (200 * 1024) / per;
+    return s > 8 ? 8 : s;
+}
+
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -40,6 +50,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int B_BYTES = B_ROWS * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    constexpr int STAGES = gemm_stages(B_ROWS);  // shadows the common 3-stage default: see gemm_stages()
     constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;  // double-buffered accumulator (power of two: 64/128/256)
 
@@ -250,7 +261,7 @@ int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t out
 template <int BN, bool A_MN, bool B_MN>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
-    constexpr int smem_bytes = STAGES * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
+    constexpr int smem_bytes = gemm_stages(B_ROWS) * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
     static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
     static int configured_dev_mask = 0;

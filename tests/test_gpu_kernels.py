@@ -206,7 +206,7 @@ def test_batchnorm_train(M, C, relu, res):
         _close(dres, rr.grad, 1e-2, 1e-2, "bn dres", 1e-5 if relu else 0.0)
 
 
-@pytest.mark.parametrize("N,H,C,stride", [(8, 32, 32, 1), (4, 16, 144, 2), (2, 8, 960, 1), (3, 9, 24, 2), (128, 32, 96, 1)])
+@pytest.mark.parametrize("N,H,C,stride", [(8, 32, 32, 1), (4, 16, 144, 2), (2, 8, 960, 1), (3, 9, 24, 2), (128, 32, 96, 1), (16, 32, 144, 2), (5, 6, 576, 2)])
 @pytest.mark.parametrize("wdt", [torch.float32, torch.bfloat16])
 def test_dwconv3x3(N, H, C, stride, wdt):
     nat = _lib()
