@@ -49,6 +49,10 @@ _KERNEL_SIGS = {
     "dmp_bn_bwd_dx": (i32, [vp, vp, vp, i32, vp, vp, vp, vp, f64, vp, vp, i64, i32, i32, vp]),
     "dmp_bn_bwd_params": (i32, [vp, vp, vp, i32, i32, vp]),
     "dmp_bn_fused_ws_bytes": (i64, [i32]),
+    "dmp_gemm_bf16_colstats": (i32, [vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, vp]),
+    "dmp_dwconv3x3_fwd_colstats": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp, vp]),
+    "dmp_bn_sums_bytes": (i64, [i32]),
+    "dmp_bn_apply_sums": (i32, [vp, i32, vp, vp, i64, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, i32, vp]),
     "dmp_bn_fwd_fused": (i32, [vp, i32, vp, vp, i64, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, i32, vp]),
     "dmp_bn_bwd_fused": (i32, [vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, vp, vp]),
     "dmp_bn_stats_finalize_noalloc": (i32, [vp, i32, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),

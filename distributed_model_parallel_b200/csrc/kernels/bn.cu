@@ -203,13 +203,14 @@ bn_bwd_dx_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __r
     const long long stride = (long long)gridDim.x * BN_THREADS;
     const int ch0 = (int)((tid * VEC) % C);
     float mu[VEC], is[VEC], a[VEC], b[VEC], c[VEC];
+    const double inv_count = 1.0 / count;  // one fp64 division per thread; per-channel divisions cost more than the data pass
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
         mu[j] = mean[ch0 + j];
         is[j] = invstd[ch0 + j];
         a[j] = (gamma ? gamma[ch0 + j] : 1.f) * is[j];
-        b[j] = (float)(accum[ch0 + j] / count);
-        c[j] = (float)(accum[C + ch0 + j] / count);
+        b[j] = (float)(accum[ch0 + j] * inv_count);
+        c[j] = (float)(accum[C + ch0 + j] * inv_count);
     }
     for (long long v = tid; v < nvec; v += stride) {
         float g[VEC], xv[VEC];
@@ -298,6 +299,7 @@ bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ residual, T* 
     }
     block_channel_reduce<VEC, 2>(acc, ch0, C, accum + (long long)(blockIdx.x % NSETS) * 2 * C, sm);
     grid.sync();
+    const double inv_count = 1.0 / count;
     float sc[VEC], sh[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
@@ -308,10 +310,13 @@ bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ residual, T* 
             s1 += accum[(long long)k * 2 * C + c];
             s2 += accum[(long long)k * 2 * C + C + c];
         }
-        const double m = s1 / count;
-        double var = s2 / count - m * m;
+        // per-thread path: fp64 only for the cancellation-prone s2/n - m^2 (multiplies), the root and reciprocal in fp32 --
+        // fp64 divisions and square roots are long instruction sequences and, at 8 channels x 3 per thread, used to cost
+        // more than the data pass of a small layer.  Block 0 below still publishes mean / invstd with full fp64 math.
+        const double m = s1 * inv_count;
+        double var = s2 * inv_count - m * m;
         if (var < 0.0) var = 0.0;
-        const float is = (float)(1.0 / sqrt(var + (double)eps));
+        const float is = 1.0f / sqrtf((float)var + eps);
         const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
         sc[j] = g * is;
         sh[j] = b - (float)m * g * is;
@@ -340,6 +345,94 @@ bn_fwd_fused_kernel(const T* __restrict__ x, const T* __restrict__ residual, T* 
         }
     }
     for (long long i = tid; i < 2 * (long long)NSETS * C; i += stride) other[i] = 0.0;  // ready for the next call
+    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+        int4 raw[U], rres[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                raw[u] = Vec<T>::load_raw(x, v0 + u * stride);
+                if (residual != nullptr) rres[u] = Vec<T>::load_raw(residual, v0 + u * stride);
+            }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                float f[VEC];
+                Vec<T>::unpack(raw[u], f);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) f[j] = f[j] * sc[j] + sh[j];
+                if (residual != nullptr) {
+                    float r[VEC];
+                    Vec<T>::unpack(rres[u], r);
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) f[j] += r[j];
+                }
+                if (relu) {
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) f[j] = fmaxf(f[j], 0.f);
+                }
+                Vec<T>::store(y, v0 + u * stride, f);
+            }
+    }
+}
+
+// BatchNorm forward when the batch sums already exist (written by the producing convolution's epilogue, see
+// dmp_gemm_bf16_colstats / dmp_dwconv3x3_fwd_colstats): one plain elementwise pass, no second read of x for statistics and no
+// grid-wide barrier.  sums = double[2C] {sum, sum of squares} followed by one int ticket.  Every block derives scale/shift for
+// its own channels; block 0 also publishes mean / invstd / running statistics; the last block to have read the sums (ticket)
+// zeroes them again, so the buffer is ready for the producer's next accumulation (CUDA-graph replay included).
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T* __restrict__ y, long long nvec, int C,
+                     double count, const float* __restrict__ gamma, const float* __restrict__ beta,
+                     float* __restrict__ running_mean, float* __restrict__ running_var,
+                     long long* __restrict__ num_batches_tracked, float momentum, float eps, float* __restrict__ mean_out,
+                     float* __restrict__ invstd_out, double* __restrict__ sums, int relu) {
+    constexpr int VEC = Vec<T>::N;
+    constexpr int U = 4;
+    __shared__ int s_last;
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    const double inv_count = 1.0 / count;
+    float sc[VEC], sh[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        const int c = ch0 + j;
+        const double m = sums[c] * inv_count;
+        double var = sums[C + c] * inv_count - m * m;
+        if (var < 0.0) var = 0.0;
+        const float is = 1.0f / sqrtf((float)var + eps);
+        const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+        sc[j] = g * is;
+        sh[j] = b - (float)m * g * is;
+    }
+    if (blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+            const double m = sums[c] / count;
+            double var = sums[C + c] / count - m * m;
+            if (var < 0.0) var = 0.0;
+            mean_out[c] = (float)m;
+            invstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
+            if (running_mean != nullptr) {
+                const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
+                running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
+            }
+        }
+        if (threadIdx.x == 0 && num_batches_tracked != nullptr) *num_batches_tracked += 1;
+    }
+    // everything this block needed from `sums` is in registers: take a ticket; the last block clears the buffer
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int* ticket = (int*)(sums + 2 * (long long)C);
+        s_last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last) {
+        for (int i = threadIdx.x; i < 2 * C; i += BN_THREADS) sums[i] = 0.0;
+        if (threadIdx.x == 0) *(int*)(sums + 2 * (long long)C) = 0;
+    }
     for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
         int4 raw[U], rres[U];
 #pragma unroll
@@ -435,6 +528,7 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
     }
     block_channel_reduce<VEC, 2>(acc, ch0, C, accum + (long long)(blockIdx.x % NSETS) * 2 * C, sm);
     grid.sync();
+    const double inv_count = 1.0 / count;
     float a[VEC], b[VEC], c[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
@@ -445,8 +539,8 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
             s2 += accum[(long long)k * 2 * C + C + ch0 + j];
         }
         a[j] = gs[j] * is[j];
-        b[j] = (float)(s1 / count);
-        c[j] = (float)(s2 / count);
+        b[j] = (float)(s1 * inv_count);
+        c[j] = (float)(s2 * inv_count);
     }
     if (blockIdx.x == 0) {
         for (int ch = threadIdx.x; ch < C; ch += BN_THREADS) {
@@ -662,6 +756,32 @@ DMP_API int dmp_bn_fwd_fused(const void* x, int dtype, const void* residual, voi
         if (grid < 0) return 1;
         DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_fwd_fused_kernel<float>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
     }
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// Bytes of the {double sums[2C]; int ticket} buffer dmp_bn_apply_sums and the *_colstats producers share (zero it once).
+DMP_API long long dmp_bn_sums_bytes(int C) { return (long long)(2 * (long long)C + 1) * 8; }
+
+// Train-mode BatchNorm forward from sums produced by the convolution epilogue; see bn_apply_sums_kernel.
+DMP_API int dmp_bn_apply_sums(const void* x, int dtype, const void* residual, void* y, long long M, int C, const float* gamma,
+                              const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+                              float momentum, float eps, float* mean, float* invstd, double* sums, int relu,
+                              cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_apply_sums", M, C, dtype)) return rc;
+    DMP_REQUIRE(sums && mean && invstd, "dmp_bn_apply_sums: null sums/mean/invstd");
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    if (dtype == 1)
+        bn_apply_sums_kernel<bf16><<<grid, BN_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)residual, (bf16*)y, nvec, C, (double)M,
+                                                                    gamma, beta, running_mean, running_var, num_batches_tracked,
+                                                                    momentum, eps, mean, invstd, sums, relu);
+    else
+        bn_apply_sums_kernel<float><<<grid, BN_THREADS, 0, stream>>>((const float*)x, (const float*)residual, (float*)y, nvec, C, (double)M,
+                                                                     gamma, beta, running_mean, running_var, num_batches_tracked,
+                                                                     momentum, eps, mean, invstd, sums, relu);
+    DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
 }

@@ -183,19 +183,42 @@ dw_dgrad_s2_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* 
     }
 }
 
+// Block-level combine of per-thread {sum[8], sumsq[8]} partials of channels ch0..ch0+7 into global double accumulators.
+// Channel vectors repeat over the block's threads with period P = C/8, so thread g < min(P, 256) folds threads g, g+P, ...
+// out of shared memory and issues the 16 atomics of its channel vector.  Must be reached by every thread of the block.
+__device__ __forceinline__ void dw_block_channel_reduce(const float* vals, int ch0, int C, double* __restrict__ accum) {
+    __shared__ float s_part[DW_THREADS * 17];  // padded rows: 17 floats per thread
+    __shared__ int s_ch0[DW_THREADS];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s_part[threadIdx.x * 17 + i] = vals[i];
+    s_ch0[threadIdx.x] = ch0;
+    __syncthreads();
+    const int P = C >> 3;
+    const int ngroups = P < DW_THREADS ? P : DW_THREADS;
+    for (int item = threadIdx.x; item < ngroups * 16; item += DW_THREADS) {
+        const int g = item >> 4, i = item & 15;
+        float sacc = 0.f;
+        for (int t = g; t < DW_THREADS; t += P) sacc += s_part[t * 17 + i];
+        atomicAdd(&accum[(long long)(i >> 3) * C + s_ch0[g] + (i & 7)], (double)sacc);
+    }
+}
+
 // Strip version of the forward stencil: one thread produces TW horizontally adjacent output pixels of its 8 channels,
 // so every input vector of a row is loaded once and reused by up to 3 outputs (4.5 instead of 9 loads per output at
 // stride 1).  FLIP=true mirrors the taps: with stride 1 the data gradient is the same stencil applied to dy.
-template <typename WT, int STRIDE, int TW, bool FLIP>
+// STATS=true additionally accumulates, per channel, the sum and sum of squares of the bf16-rounded outputs into
+// stats[0..C) / stats[C..2C) (double): the BatchNorm batch statistics come out of the convolution itself.
+template <typename WT, int STRIDE, int TW, bool FLIP, bool STATS>
 __global__ void __launch_bounds__(DW_THREADS, 2)  // 2 blocks/SM: the few spilled registers cost less than half occupancy
 dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
-                int Ho, int Wo) {
+                int Ho, int Wo, double* __restrict__ stats) {
     constexpr int NC = (TW - 1) * STRIDE + 3;  // input columns feeding the strip
     const int P = C >> 3;
     const int tiles_w = (Wo + TW - 1) / TW;
     const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
     const long long total = (long long)N * Ho * tiles_w * P;
-    if (idx >= total) return;
+    const bool active = idx < total;
+    if (!STATS && !active) return;
     const int cv = (int)(idx % P);
     long long t = idx / P;
     const int wt_ = (int)(t % tiles_w); t /= tiles_w;
@@ -203,41 +226,59 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
     const int n = (int)(t / Ho);
     const int ch0 = cv * 8;
     const int wo0 = wt_ * TW;
-    float wt[72];
-    load_w72<WT>(w, ch0, wt);
-    float acc[TW][8];
+    float st[STATS ? 16 : 1];
+    if (STATS) {
 #pragma unroll
-    for (int i = 0; i < TW; ++i)
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-    const int wi0 = wo0 * STRIDE - 1;
-#pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-        const int hi = ho * STRIDE + kh - 1;
-        if (hi < 0 || hi >= H) continue;
-        const bf16* row = x + (((long long)n * H + hi) * W) * C + ch0;
-        float col[NC][8];
-#pragma unroll
-        for (int c = 0; c < NC; ++c) {
-            const int wi = wi0 + c;
-            if (wi >= 0 && wi < W) load8(row + (long long)wi * C, col[c]);
-            else {
-#pragma unroll
-                for (int j = 0; j < 8; ++j) col[c][j] = 0.f;
-            }
-        }
+        for (int i = 0; i < 16; ++i) st[i] = 0.f;
+    }
+    if (active) {
+        float wt[72];
+        load_w72<WT>(w, ch0, wt);
+        float acc[TW][8];
 #pragma unroll
         for (int i = 0; i < TW; ++i)
 #pragma unroll
-            for (int kw = 0; kw < 3; ++kw) {
-                const int tap = FLIP ? ((2 - kh) * 3 + (2 - kw)) : (kh * 3 + kw);
+            for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+        const int wi0 = wo0 * STRIDE - 1;
 #pragma unroll
-                for (int j = 0; j < 8; ++j) acc[i][j] += col[i * STRIDE + kw][j] * wt[j * 9 + tap];
+        for (int kh = 0; kh < 3; ++kh) {
+            const int hi = ho * STRIDE + kh - 1;
+            if (hi < 0 || hi >= H) continue;
+            const bf16* row = x + (((long long)n * H + hi) * W) * C + ch0;
+            float col[NC][8];
+#pragma unroll
+            for (int c = 0; c < NC; ++c) {
+                const int wi = wi0 + c;
+                if (wi >= 0 && wi < W) load8(row + (long long)wi * C, col[c]);
+                else {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) col[c][j] = 0.f;
+                }
+            }
+#pragma unroll
+            for (int i = 0; i < TW; ++i)
+#pragma unroll
+                for (int kw = 0; kw < 3; ++kw) {
+                    const int tap = FLIP ? ((2 - kh) * 3 + (2 - kw)) : (kh * 3 + kw);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[i][j] += col[i * STRIDE + kw][j] * wt[j * 9 + tap];
+                }
+        }
+#pragma unroll
+        for (int i = 0; i < TW; ++i)
+            if (wo0 + i < Wo) {
+                store8(y + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0, acc[i]);
+                if (STATS) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float q = __bfloat162float(__float2bfloat16_rn(acc[i][j]));
+                        st[j] += q;
+                        st[8 + j] += q * q;
+                    }
+                }
             }
     }
-#pragma unroll
-    for (int i = 0; i < TW; ++i)
-        if (wo0 + i < Wo) store8(y + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0, acc[i]);
+    if (STATS) dw_block_channel_reduce(st, ch0, C, stats);  // reached by every thread of the block (idle tail threads add zeros)
 }
 
 // Strip version of the weight gradient.  A warp owns TWO adjacent channel vectors (lane & 1) and its 16 lane pairs walk
@@ -389,13 +430,36 @@ DMP_API int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y
     if (stride == 1) {
         const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo);
-        else dw_strip_kernel<bf16, 1, 4, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
+        else dw_strip_kernel<bf16, 1, 4, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
     } else {
         const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo);
-        else dw_strip_kernel<bf16, 2, 2, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo);
+        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
+        else dw_strip_kernel<bf16, 2, 2, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
+    }
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// Depthwise forward that also accumulates the BatchNorm batch sums of its (bf16-rounded) output: stats = double[2C]
+// {sum, sum of squares}, accumulated (the consumer dmp_bn_apply_sums re-zeroes them).
+DMP_API int dmp_dwconv3x3_fwd_colstats(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int stride,
+                                       double* stats, cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_fwd_colstats", N, H, W, C, stride)) return rc;
+    DMP_REQUIRE(stats != nullptr, "dmp_dwconv3x3_fwd_colstats: null stats");
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    if (stride == 1) {
+        const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
+        else dw_strip_kernel<bf16, 1, 4, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
+    } else {
+        const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
+        const int grid = dmp_ceil_div(total, DW_THREADS);
+        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
+        else dw_strip_kernel<bf16, 2, 2, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
     }
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
@@ -409,8 +473,8 @@ DMP_API int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void
     if (stride == 1) {  // dx = dy (*) flipped taps: the forward strip stencil applied to dy (Ho == H, Wo == W)
         const long long total = (long long)N * H * ((W + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W);
-        else dw_strip_kernel<bf16, 1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, H, W);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W, nullptr);
+        else dw_strip_kernel<bf16, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, H, W, nullptr);
     } else if (stride == 2 && H % 2 == 0 && W % 2 == 0) {
         const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);

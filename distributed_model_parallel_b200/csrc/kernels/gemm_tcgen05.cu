@@ -28,6 +28,7 @@ struct GemmParams {
     long long ldd;
     const float* bias;  // per-column (N) fp32 bias, nullable
     int epi;            // 0: store bf16, 1: store fp32, 2: atomic add fp32
+    double* stats;      // STATS kernels: [2N] per-column sum and sum of squares of the bf16-rounded outputs, accumulated
 };
 
 // Persistent kernel: CTA b processes work items b, b+gridDim.x, ...  A work item is one 128 x BN output tile of one
@@ -36,13 +37,17 @@ struct GemmParams {
 // very long split pixel axis for the weight gradient), so what matters is bytes in flight per SM: HBM needs roughly
 // 7.7 TB/s x ~1 us / 148 SMs = 50 KB outstanding per SM to stay busy, and a 3-stage ring holds at most two stages of loads
 // (32-64 KB) in the air.  One CTA per SM owns the whole 227 KB, so the ring takes ~200 KB of it: 6 stages at BN=128, 8 below.
-constexpr int gemm_stages(int b_rows) {
+// Narrow tiles (BN <= 64, 20-24 KB per stage) keep two CTAs per SM instead -- their kernels are bound by the epilogue, and two
+// epilogues in flight beat a deeper ring -- so they take 4 stages (3 when the statistics scratch is also resident).
+constexpr int STAT_SMEM_BYTES = 4 * 32 * 33 * 4;  // per epilogue warp: a padded 32 x 32 fp32 transpose tile
+constexpr int gemm_stages(int b_rows, bool stats) {
     const int per = BM * BK * 2 + b_rows * BK * 2;
-    const int s = (200 * 1024) / per;
+    if (per <= 24 * 1024) return stats ? 3 : 4;
+    const int s = (200 * 1024 - (stats ? STAT_SMEM_BYTES : 0)) / per;
     return s > 8 ? 8 : s;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool STATS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const GemmParams p) {
@@ -50,7 +55,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int B_BYTES = B_ROWS * BK * 2;
     constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    constexpr int STAGES = gemm_stages(B_ROWS);  // shadows the common 3-stage default: see gemm_stages()
+    constexpr int STAGES = gemm_stages(B_ROWS, STATS);  // shadows the common 3-stage default: see gemm_stages()
     constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;  // double-buffered accumulator (power of two: 64/128/256)
 
@@ -61,6 +66,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
     uint32_t* tmem_ptr_smem = (uint32_t*)(tmem_empty_bar + 2);
+    float* stat_smem = (float*)(smem + STAGES * STAGE_BYTES + 256);  // STATS only (the launch adds STAT_SMEM_BYTES)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -162,6 +168,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else {
         // ------------------------------------------------------------------ epilogue (warps 2..5)
         const int lane_grp = warp & 3;  // TMEM lane quarter this warp may access
+        // STATS: this CTA's tiles all share one n0 (the host makes gridDim.x a multiple of n_tiles), so lane l keeps the running
+        // column sums of columns n0 + 32 c + l in registers across all of its tiles and issues its atomics once, at the end.
+        constexpr int NCHUNK = BN >= 32 ? BN / 32 : 1;
+        float st1[NCHUNK], st2[NCHUNK];
+#pragma unroll
+        for (int c = 0; c < NCHUNK; ++c) st1[c] = st2[c] = 0.f;
         int local = 0;
         for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
             const int tile = item % tiles_mn;
@@ -172,13 +184,35 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_wait(&tmem_full_bar[buf], acc_ph);
             tcgen05_fence_after();
             const uint32_t taddr_row = tmem_base + buf * ACC_COLS + ((uint32_t)(lane_grp * 32) << 16);
-#pragma unroll 1
+#pragma unroll(STATS ? NCHUNK : 1)
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.N) break;  // warp-uniform
                 uint32_t r[32];
                 if (BN >= 32) tmem_ld_32(taddr_row + c0, r);
                 else tmem_ld_16(taddr_row + c0, r);
                 tmem_ld_wait();
+                if (STATS) {
+                    // column sums over this warp's 32 rows: transpose through a padded shared tile (conflict-free both ways)
+                    float* tr = stat_smem + lane_grp * (32 * 33);
+                    const bool rowok = row < p.M;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        float q = __uint_as_float(r[j]);
+                        q = (rowok && n0 + c0 + j < p.N) ? __bfloat162float(__float2bfloat16_rn(q)) : 0.f;
+                        tr[lane * 33 + j] = q;
+                    }
+                    __syncwarp();
+                    float a = 0.f, b = 0.f;
+#pragma unroll
+                    for (int rr = 0; rr < 32; ++rr) {
+                        const float q = tr[rr * 33 + lane];
+                        a += q;
+                        b += q * q;
+                    }
+                    __syncwarp();
+                    st1[c0 / 32] += a;
+                    st2[c0 / 32] += b;
+                }
                 if (row < p.M) {
                     const int n = n0 + c0;
                     float v[32];
@@ -229,6 +263,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);  // this warp is done reading the accumulator
         }
+        if (STATS && blockIdx.x < num_items) {
+            const int n0 = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;
+#pragma unroll
+            for (int c = 0; c < NCHUNK; ++c) {
+                const int col = n0 + c * 32 + lane;
+                if (col < p.N) {
+                    atomicAdd(p.stats + col, (double)st1[c]);
+                    atomicAdd(p.stats + p.N + col, (double)st2[c]);
+                }
+            }
+        }
     }
     __syncthreads();
     if (warp == 1) {
@@ -258,11 +303,12 @@ int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t out
     return 0;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool STATS = false>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
-    constexpr int smem_bytes = gemm_stages(B_ROWS) * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ + 256 /*barriers*/;
-    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN>;
+    constexpr int smem_bytes = gemm_stages(B_ROWS, STATS) * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ +
+                               256 /*barriers*/ + (STATS ? STAT_SMEM_BYTES : 0);
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, STATS>;
     static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
     static int configured_dev_mask = 0;
     int dev = 0;
@@ -280,6 +326,10 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     const int ctas_per_sm = smem_bytes <= 110 * 1024 ? 2 : 1;
     long long grid = (long long)dmp_num_sms() * ctas_per_sm;
     if (grid > items) grid = items;
+    if (STATS) {  // every tile of a CTA must have the same n0: the item stride has to be a multiple of n_tiles
+        DMP_REQUIRE(splits == 1 && q.n_tiles <= grid, "gemm statistics epilogue: %d column tiles do not fit the grid", q.n_tiles);
+        grid = grid / q.n_tiles * q.n_tiles;
+    }
     kern<<<(int)grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, q);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
@@ -333,11 +383,32 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
     p.M = M; p.N = N; p.K = K;
     p.k_blocks_per_split = dmp_ceil_div(total_kb, splits);
     splits = dmp_ceil_div(total_kb, p.k_blocks_per_split);  // no empty splits
-    p.D = D; p.ldd = ldd; p.bias = bias; p.epi = out_mode;
+    p.D = D; p.ldd = ldd; p.bias = bias; p.epi = out_mode; p.stats = nullptr;
 
     if (!a_mn && !b_mn) return dispatch_bn<false, false>(bn, tmA, tmB, p, splits, stream);
     if (!a_mn && b_mn) return dispatch_bn<false, true>(bn, tmA, tmB, p, splits, stream);
     return dispatch_bn<true, true>(bn, tmA, tmB, p, splits, stream);
+}
+
+// D[M,N] (bf16) = A[M,K] * B[N,K]^T, and stats[0..N) += column sums, stats[N..2N) += column sums of squares of the bf16-rounded
+// outputs (double, accumulated: the caller zeroes or chains them).  This is the 1x1-convolution forward with the BatchNorm
+// batch statistics produced by the GEMM epilogue, so the normalisation that follows is a single elementwise pass.
+DMP_API int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd, int M,
+                                   int N, int K, double* stats, cudaStream_t stream) {
+    DMP_REQUIRE(M > 0 && N > 0 && K > 0 && stats != nullptr, "dmp_gemm_bf16_colstats: bad arguments");
+    const int bn = N > 64 ? 128 : (N > 32 ? 64 : 32);
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM)) return rc;
+    if (int rc = make_tmap_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)bn)) return rc;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.k_blocks_per_split = dmp_ceil_div(K, BK);
+    p.D = D; p.ldd = ldd; p.bias = nullptr; p.epi = 0; p.stats = stats;
+    switch (bn) {
+        case 32: return launch_gemm<32, false, false, true>(tmA, tmB, p, 1, stream);
+        case 64: return launch_gemm<64, false, false, true>(tmA, tmB, p, 1, stream);
+        default: return launch_gemm<128, false, false, true>(tmA, tmB, p, 1, stream);
+    }
 }
 
 // ------------------------------------------------------------------ CUDA-core oracle (tests / debugging only)

@@ -14,6 +14,7 @@ loss (utils.py:58, data_parallel.py:109).
 """
 from __future__ import annotations
 
+import os
 import threading
 from collections import Counter
 from typing import Optional
@@ -135,7 +136,9 @@ def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
     return "generic"
 
 
-def _conv_fwd_cuda(x, w, conv, kind):
+def _conv_fwd_cuda(x, w, conv, kind, stats=None):
+    """``stats``: optional {double[2C]; ticket} buffer -- the producer then also accumulates the BatchNorm batch sums of its
+    output (only the "pw" and "dw" kinds have such an epilogue)."""
     lib = _k()
     sp = _sp()
     N = x.shape[0]
@@ -146,9 +149,14 @@ def _conv_fwd_cuda(x, w, conv, kind):
         cout = conv.out_channels
         y = _cl_empty(N, cout, H, W, x.device)
         wb = weight_bf16(w)
-        _ck(lib.dmp_gemm_bf16(0, x.data_ptr(), cin, wb.data_ptr(), cin, y.data_ptr(), cout, N * H * W, cout, cin, None, 0,
-                              1, sp), "conv1x1 fwd gemm")
-        _note("conv_pw:tcgen05")
+        if stats is not None:
+            _ck(lib.dmp_gemm_bf16_colstats(x.data_ptr(), cin, wb.data_ptr(), cin, y.data_ptr(), cout, N * H * W, cout, cin,
+                                           stats.data_ptr(), sp), "conv1x1 fwd gemm + stats")
+            _note("conv_pw:tcgen05+bnstats")
+        else:
+            _ck(lib.dmp_gemm_bf16(0, x.data_ptr(), cin, wb.data_ptr(), cin, y.data_ptr(), cout, N * H * W, cout, cin, None, 0,
+                                  1, sp), "conv1x1 fwd gemm")
+            _note("conv_pw:tcgen05")
         return y, x
     if kind == "dw":
         _, C, H, W = x.shape
@@ -156,8 +164,13 @@ def _conv_fwd_cuda(x, w, conv, kind):
         Ho, Wo = (H + 2 - 3) // s + 1, (W + 2 - 3) // s + 1
         y = _cl_empty(N, C, Ho, Wo, x.device)
         wb = weight_bf16(w)
-        _ck(lib.dmp_dwconv3x3_fwd(x.data_ptr(), wb.data_ptr(), 1, y.data_ptr(), N, H, W, C, s, sp), "dwconv fwd")
-        _note("conv_dw:stencil")
+        if stats is not None:
+            _ck(lib.dmp_dwconv3x3_fwd_colstats(x.data_ptr(), wb.data_ptr(), 1, y.data_ptr(), N, H, W, C, s, stats.data_ptr(), sp),
+                "dwconv fwd + stats")
+            _note("conv_dw:stencil+bnstats")
+        else:
+            _ck(lib.dmp_dwconv3x3_fwd(x.data_ptr(), wb.data_ptr(), 1, y.data_ptr(), N, H, W, C, s, sp), "dwconv fwd")
+            _note("conv_dw:stencil")
         return y, x
     if kind == "stem":
         _, cin, H, W = x.shape
@@ -303,14 +316,52 @@ def _bn_workspace(bn, which: str, C: int, dev):
     return ws
 
 
-def _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync):
-    """Train/eval BatchNorm (+residual, +ReLU) of a channels-last bf16 tensor. Returns (out, mean, invstd, count, training)."""
+# Opt-in (DMP_BN_EPILOGUE_STATS=1).  bench/epilogue_stats_bench.py: with the present register->global GEMM epilogue the statistics
+# cost the producer 3-23 us per layer, about what the lighter BatchNorm pass saves; it pays once the epilogue is TMA-stored.
+_EPILOGUE_STATS = os.environ.get("DMP_BN_EPILOGUE_STATS", "0") == "1"
+
+
+def _bn_epilogue_stats_ok(bn, sync, kind) -> bool:
+    """Can the convolution's epilogue produce this BatchNorm's batch statistics (train mode, local statistics, a producer
+    kind that has the epilogue, plain momentum)?"""
+    if not _EPILOGUE_STATS or bn is None or sync is not None or kind not in ("pw", "dw"):
+        return False
+    training = bn.training or (bn.running_mean is None)
+    return training and (bn.momentum is not None or not bn.track_running_stats)
+
+
+def _bn_sums_buffer(bn, C: int, dev):
+    """Per-layer, per-device {double sums[2C]; int ticket}: zero on creation, re-zeroed by dmp_bn_apply_sums after each use."""
+    store = bn.__dict__.setdefault("_dmp_ws", {})
+    key = (dev.index, "sums")
+    buf = store.get(key)
+    need = int(_k().dmp_bn_sums_bytes(C)) // 8
+    if buf is None or buf.numel() != need:
+        buf = torch.zeros(need, dtype=torch.float64, device=dev)
+        store[key] = buf
+    return buf
+
+
+def _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync, sums=None):
+    """Train/eval BatchNorm (+residual, +ReLU) of a channels-last bf16 tensor. Returns (out, mean, invstd, count, training).
+    ``sums``: batch sums already accumulated by the producing convolution (see _bn_epilogue_stats_ok)."""
     lib = _k()
     sp = _sp()
     N, C, Ho, Wo = y_raw.shape
     M = N * Ho * Wo
     dev = y_raw.device
     training = bn.training or (bn.running_mean is None)
+    if sums is not None:
+        mean = torch.empty(C, device=dev, dtype=torch.float32)
+        invstd = torch.empty(C, device=dev, dtype=torch.float32)
+        out = torch.empty_like(y_raw)
+        track = bn.track_running_stats and bn.running_mean is not None
+        _ck(lib.dmp_bn_apply_sums(y_raw.data_ptr(), 1, _native.ptr(residual), out.data_ptr(), M, C, _native.ptr(gamma), _native.ptr(beta),
+                                  _native.ptr(bn.running_mean if track else None), _native.ptr(bn.running_var if track else None),
+                                  _native.ptr(bn.num_batches_tracked if track else None), float(bn.momentum or 0.1), float(bn.eps),
+                                  mean.data_ptr(), invstd.data_ptr(), sums.data_ptr(), 1 if relu else 0, sp), "bn apply (epilogue sums)")
+        _note("bn:apply_from_epilogue_sums")
+        return out, mean, invstd, float(M), True
     if training and sync is None and (bn.momentum is not None or not bn.track_running_stats):
         # single cooperative launch: statistics -> grid barrier -> normalise (+residual, +ReLU), running stats, counter
         mean = torch.empty(C, device=dev, dtype=torch.float32)
@@ -444,7 +495,8 @@ class _ConvBNAct(torch.autograd.Function):
             x = _as_cl_bf16(x)
         if kind == "pw" and conv.stride != (1, 1):
             conv._dmp_in_hw = (x.shape[2], x.shape[3])
-        y_raw, x_saved = _conv_fwd_cuda(x, w, conv, kind)
+        sums = _bn_sums_buffer(bn, conv.out_channels, x.device) if _bn_epilogue_stats_ok(bn, sync, kind) else None
+        y_raw, x_saved = _conv_fwd_cuda(x, w, conv, kind, sums)
         ctx.conv, ctx.bn, ctx.relu, ctx.kind, ctx.sync = conv, bn, relu, kind, sync
         ctx.has_res = residual is not None
         ctx.x_needs_grad = ctx.needs_input_grad[0]
@@ -460,7 +512,7 @@ class _ConvBNAct(torch.autograd.Function):
             ctx.save_for_backward(x_saved, w, out if relu else None)
             ctx.bn_train = False
             return out
-        out, mean, invstd, ctx.count, ctx.bn_train = _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync)
+        out, mean, invstd, ctx.count, ctx.bn_train = _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync, sums)
         ctx.save_for_backward(x_saved, w, out if relu else None, y_raw, mean, invstd, gamma)
         return out
 

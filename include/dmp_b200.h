@@ -32,6 +32,10 @@ int dmp_l2_flush(void* buf, long long bytes, dmp_stream_t stream);    /* benchma
  * out_mode 0: bf16 store, 1: fp32 store, 2: fp32 atomic accumulate.  bias: optional fp32[N]. */
 int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd, int M,
                   int N, int K, const float* bias, int out_mode, int splits, dmp_stream_t stream);
+/* NT GEMM with bf16 output that also accumulates per-column {sum, sum of squares} of the rounded outputs into stats[2N]
+ * (double): the 1x1 convolution hands its BatchNorm the batch statistics, see dmp_bn_apply_sums. */
+int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd, int M, int N,
+                           int K, double* stats, dmp_stream_t stream);
 int dmp_gemm_ref_f32out(int layout, const void* A, long long lda, const void* B, long long ldb, float* D, long long ldd,
                         int M, int N, int K, const float* bias, int accumulate, dmp_stream_t stream); /* CUDA-core oracle */
 
@@ -75,6 +79,12 @@ int dmp_bn_bwd_params(const double* accum_local, float* dgamma, float* dbeta, in
  * dmp_bn_fused_ws_bytes(C) bytes, zeroed once (double-buffered accumulators + device-side parity, graph-replay safe).
  * Return 1 = shape not launchable cooperatively, use the split entry points above.  (T/nn/functional.py batch_norm semantics) */
 long long dmp_bn_fused_ws_bytes(int C);
+/* BatchNorm forward from sums a *_colstats producer accumulated: sums = {double[2C]; int ticket} of dmp_bn_sums_bytes(C),
+ * zeroed once by the caller and re-zeroed by the kernel itself after every use. */
+long long dmp_bn_sums_bytes(int C);
+int dmp_bn_apply_sums(const void* x, int dtype, const void* residual, void* y, long long M, int C, const float* gamma,
+                      const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked,
+                      float momentum, float eps, float* mean, float* invstd, double* sums, int relu, dmp_stream_t stream);
 int dmp_bn_fwd_fused(const void* x, int dtype, const void* residual, void* y, long long M, int C, const float* gamma,
                      const float* beta, float* running_mean, float* running_var, long long* num_batches_tracked, float momentum,
                      float eps, float* mean, float* invstd, double* ws, int relu, dmp_stream_t stream);
@@ -96,6 +106,8 @@ int dmp_bn_noalloc_max_channels(void);
 /* ------------------------------------------------------------------ depthwise 3x3 (csrc/kernels/dwconv.cu; R/model/mobilenetv2.py:19,33) */
 int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int stride,
                       dmp_stream_t stream);
+int dmp_dwconv3x3_fwd_colstats(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int stride,
+                               double* stats, dmp_stream_t stream);
 int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void* dx, int N, int H, int W, int C, int stride,
                         dmp_stream_t stream);
 int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int stride, int accumulate,

@@ -402,3 +402,65 @@ def test_conv_igemm_tcgen05(N, H, Cin, Cout, k):
     torch.cuda.synchronize()
     dw = dwp.view(Cout, k, k, Cin).permute(0, 3, 1, 2)
     _close(dw, wr.grad, 1e-2, 1e-2 * wr.grad.abs().max().item(), "igemm wgrad")
+
+
+# ------------------------------------------------------------------------------------------------ BN statistics from the producer's epilogue
+@pytest.mark.parametrize("M,N,K", [(4096, 144, 24), (131072, 96, 16), (8192, 384, 64), (2048, 960, 160), (1000, 40, 24), (8192, 32, 192)])
+def test_gemm_colstats_and_bn_apply_sums(M, N, K):
+    """1x1-conv GEMM whose epilogue accumulates the BatchNorm batch sums, followed by the single-pass apply kernel, against
+    F.batch_norm (train mode) of the same bf16 conv output in fp32.  Run twice: the sums buffer must clean itself."""
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(M + N + K)
+    a = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    b = (torch.randn(N, K, device="cuda") * 0.5 + 0.05).bfloat16()
+    y = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    sums = torch.zeros(int(lib.dmp_bn_sums_bytes(N)) // 8, dtype=torch.float64, device="cuda")
+    gamma, beta = torch.rand(N, device="cuda") + 0.5, torch.randn(N, device="cuda") * 0.1
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    sp = _sp()
+    for rep in range(2):
+        rm, rv = torch.zeros(N, device="cuda"), torch.ones(N, device="cuda")
+        nbt = torch.zeros((), dtype=torch.int64, device="cuda")
+        mean, invstd = torch.empty(N, device="cuda"), torch.empty(N, device="cuda")
+        out = torch.empty_like(y)
+        nat.check(lib.dmp_gemm_bf16_colstats(a.data_ptr(), K, b.data_ptr(), K, y.data_ptr(), N, M, N, K, sums.data_ptr(), sp), "gemm+stats")
+        torch.cuda.synchronize()
+        yref = (a.float() @ b.float().t())
+        _close(y, yref, 2e-2, 2e-2, "gemm out")
+        yf = y.float()
+        s = sums[: 2 * N].clone()
+        assert torch.allclose(s[:N], yf.double().sum(0), rtol=1e-4, atol=1e-2), "column sums"
+        assert torch.allclose(s[N:], (yf.double() ** 2).sum(0), rtol=1e-4, atol=1e-2), "column sums of squares"
+        nat.check(lib.dmp_bn_apply_sums(y.data_ptr(), 1, res.data_ptr(), out.data_ptr(), M, N, gamma.data_ptr(), beta.data_ptr(),
+                                        rm.data_ptr(), rv.data_ptr(), nbt.data_ptr(), 0.1, 1e-5, mean.data_ptr(), invstd.data_ptr(),
+                                        sums.data_ptr(), 1, sp), "apply sums")
+        torch.cuda.synchronize()
+        rm2, rv2 = torch.zeros(N, device="cuda"), torch.ones(N, device="cuda")
+        want = F.relu(F.batch_norm(yf, rm2, rv2, gamma, beta, True, 0.1, 1e-5) + res.float())
+        _close(out, want, 2e-2, 2e-2, "bn out")
+        assert torch.allclose(rm, rm2, atol=1e-4) and torch.allclose(rv, rv2, rtol=1e-3, atol=1e-4)
+        assert int(nbt) == 1
+        assert torch.allclose(mean, yf.mean(0), atol=1e-4)
+        assert float(sums.abs().max()) == 0.0 and sums.view(torch.int32)[-2:].abs().max().item() == 0, "sums buffer not cleaned"
+
+
+@pytest.mark.parametrize("N,H,C,stride", [(8, 32, 32, 1), (4, 16, 144, 2), (2, 8, 960, 1), (3, 9, 24, 2), (128, 32, 96, 1)])
+def test_dwconv_colstats(N, H, C, stride):
+    nat = _lib()
+    lib = nat.kernels()
+    torch.manual_seed(N + H + C)
+    x = torch.randn(N, H, H, C, device="cuda").bfloat16()
+    w = (torch.randn(C, 1, 3, 3, device="cuda") * 0.3).bfloat16()
+    Ho = (H + 2 - 3) // stride + 1
+    y = torch.empty(N, Ho, Ho, C, device="cuda", dtype=torch.bfloat16)
+    y0 = torch.empty_like(y)
+    sums = torch.zeros(int(lib.dmp_bn_sums_bytes(C)) // 8, dtype=torch.float64, device="cuda")
+    sp = _sp()
+    nat.check(lib.dmp_dwconv3x3_fwd(x.data_ptr(), w.data_ptr(), 1, y0.data_ptr(), N, H, H, C, stride, sp))
+    nat.check(lib.dmp_dwconv3x3_fwd_colstats(x.data_ptr(), w.data_ptr(), 1, y.data_ptr(), N, H, H, C, stride, sums.data_ptr(), sp))
+    torch.cuda.synchronize()
+    assert torch.equal(y, y0)
+    yf = y.float().reshape(-1, C).double()
+    assert torch.allclose(sums[:C], yf.sum(0), rtol=1e-4, atol=1e-2)
+    assert torch.allclose(sums[C: 2 * C], (yf ** 2).sum(0), rtol=1e-4, atol=1e-2)
