@@ -28,6 +28,7 @@ struct GemmParams {
     long long ldd;
     const float* bias;  // per-column (N) fp32 bias, nullable
     int epi;            // 0: store bf16, 1: store fp32, 2: atomic add fp32
+    int tma_store;      // epi 0 only: stage the bf16 tile in shared memory and store it with TMA (coalesced full lines)
     double* stats;      // STATS kernels: [2N] per-column sum and sum of squares of the bf16-rounded outputs, accumulated
 };
 
@@ -37,20 +38,19 @@ struct GemmParams {
 // very long split pixel axis for the weight gradient), so what matters is bytes in flight per SM: HBM needs roughly
 // 7.7 TB/s x ~1 us / 148 SMs = 50 KB outstanding per SM to stay busy, and a 3-stage ring holds at most two stages of loads
 // (32-64 KB) in the air.  One CTA per SM owns the whole 227 KB, so the ring takes ~200 KB of it: 6 stages at BN=128, 8 below.
-// Narrow tiles (BN <= 64, 20-24 KB per stage) keep two CTAs per SM instead -- their kernels are bound by the epilogue, and two
-// epilogues in flight beat a deeper ring -- so they take 4 stages (3 when the statistics scratch is also resident).
+// Narrow tiles (BN <= 64, 20-24 KB per stage) keep two CTAs per SM instead and take 3 stages.
 constexpr int STAT_SMEM_BYTES = 4 * 32 * 33 * 4;  // per epilogue warp: a padded 32 x 32 fp32 transpose tile
 constexpr int gemm_stages(int b_rows, bool stats) {
     const int per = BM * BK * 2 + b_rows * BK * 2;
-    if (per <= 24 * 1024) return stats ? 3 : 4;
-    const int s = (200 * 1024 - (stats ? STAT_SMEM_BYTES : 0)) / per;
+    if (per <= 24 * 1024) return 3;  // + 8-16 KB output staging (+ statistics scratch) stays under half an SM's shared memory
+    const int s = (200 * 1024 - 4 * 32 * b_rows * 2 - (stats ? STAT_SMEM_BYTES : 0)) / per;
     return s > 8 ? 8 : s;
 }
 
 template <int BN, bool A_MN, bool B_MN, bool STATS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;  // 16 KB
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int B_BYTES = B_ROWS * BK * 2;
@@ -61,12 +61,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint64_t* full_bar = (uint64_t*)(smem + STAGES * STAGE_BYTES);
+    // output staging for the TMA-store epilogue: per epilogue warp 32 rows x BN bf16, in panels of PW columns (128-byte rows,
+    // SWIZZLE_128B; 64-byte rows and SWIZZLE_64B when BN == 32)
+    constexpr int PW = BN >= 64 ? 64 : BN;
+    constexpr int STG_WARP_BYTES = 32 * BN * 2;
+    uint8_t* stg = smem + STAGES * STAGE_BYTES;
+    uint64_t* full_bar = (uint64_t*)(stg + 4 * STG_WARP_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
     uint32_t* tmem_ptr_smem = (uint32_t*)(tmem_empty_bar + 2);
-    float* stat_smem = (float*)(smem + STAGES * STAGE_BYTES + 256);  // STATS only (the launch adds STAT_SMEM_BYTES)
+    float* stat_smem = (float*)(stg + 4 * STG_WARP_BYTES + 256);  // STATS only (the launch adds STAT_SMEM_BYTES)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -77,6 +82,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        if (p.tma_store) tma_prefetch_desc(&tmD);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -184,6 +190,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_wait(&tmem_full_bar[buf], acc_ph);
             tcgen05_fence_after();
             const uint32_t taddr_row = tmem_base + buf * ACC_COLS + ((uint32_t)(lane_grp * 32) << 16);
+            uint8_t* my_stg = stg + lane_grp * STG_WARP_BYTES;
+            if (p.tma_store) {  // the previous tile's bulk stores must have finished reading this warp's staging area
+                if (lane == 0) tma_store_wait_read();
+                __syncwarp();
+            }
 #pragma unroll(STATS ? NCHUNK : 1)
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.N) break;  // warp-uniform
@@ -223,7 +234,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         for (int j = 0; j < 32; ++j)
                             if (n + j < p.N) v[j] += p.bias[n + j];
                     }
-                    if (p.epi == 0) {
+                    if (p.epi == 0 && p.tma_store) {
+                        // lane = row of the warp's 32 x BN slab; 16-byte chunks are XOR-swizzled exactly as the tensor map expects
+                        const int panel = c0 / PW;
+                        const int chunk0 = (c0 % PW) >> 3;
+                        const int swz = PW == 64 ? (lane & 7) : ((lane >> 1) & 3);
+                        uint8_t* rowp = my_stg + panel * (32 * PW * 2) + lane * (PW * 2);
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            bf16x8 o = float_to_bf16x8(v + j);
+                            *(int4*)(rowp + (((chunk0 + (j >> 3)) ^ swz) << 4)) = *(int4*)&o;
+                        }
+                    } else if (p.epi == 0) {
                         bf16* d = (bf16*)p.D + (long long)row * p.ldd + n;
                         if (n + 32 <= p.N && ((p.ldd & 7) == 0)) {
 #pragma unroll
@@ -260,9 +282,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
             }
             tcgen05_fence_before();
+            if (p.tma_store) fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy)
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);  // this warp is done reading the accumulator
+            if (lane == 0) {
+                mbar_arrive(&tmem_empty_bar[buf]);  // this warp is done reading the accumulator
+                if (p.tma_store && m0 + lane_grp * 32 < p.M) {
+#pragma unroll
+                    for (int pn = 0; pn < BN / PW; ++pn)
+                        if (n0 + pn * PW < p.N) tma_store_2d(&tmD, my_stg + pn * (32 * PW * 2), n0 + pn * PW, m0 + lane_grp * 32);
+                    tma_store_commit();
+                }
+            }
         }
+        if (p.tma_store && lane == 0) tma_store_wait_all();  // shared memory must outlive the last bulk store
         if (STATS && blockIdx.x < num_items) {
             const int n0 = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;
 #pragma unroll
@@ -285,7 +317,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // ------------------------------------------------------------------ host side
 // 2D bf16 tensor map: dim0 (contiguous) = inner, dim1 = outer with row pitch ld (elements).
 int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems, uint32_t box_inner,
-                 uint32_t box_outer) {
+                 uint32_t box_outer, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
     PFN_tmapEncodeTiled enc = get_encode_fn();
     DMP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled driver entry point unavailable");
     DMP_REQUIRE(((uintptr_t)base & 15) == 0, "TMA operand base must be 16-byte aligned");
@@ -296,18 +328,24 @@ int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t out
     cuuint32_t box[2] = {box_inner, box_outer};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                     CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     DMP_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu ld=%llu)", (int)r,
                 (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)ld_elems);
     return 0;
 }
 
+// DMP_GEMM_TMA_STORE=0 keeps the register -> global epilogue (A/B measurements)
+const bool g_gemm_no_tma_store = [] {
+    const char* e = getenv("DMP_GEMM_TMA_STORE");
+    return e != nullptr && e[0] == '0';
+}();
+
 template <int BN, bool A_MN, bool B_MN, bool STATS = false>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int smem_bytes = gemm_stages(B_ROWS, STATS) * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ +
-                               256 /*barriers*/ + (STATS ? STAT_SMEM_BYTES : 0);
+                               4 * 32 * BN * 2 /*output staging*/ + 256 /*barriers*/ + (STATS ? STAT_SMEM_BYTES : 0);
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, STATS>;
     static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
     static int configured_dev_mask = 0;
@@ -319,6 +357,16 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
         configured_dev_mask |= (1 << dev);
     }
     GemmParams q = p;
+    // bf16 outputs leave through TMA when the rows are 16-byte aligned: box = {one panel of PW columns, one epilogue warp's 32 rows}
+    CUtensorMap tmD = tmA;
+    q.tma_store = 0;
+    if (p.epi == 0 && (p.ldd & 7) == 0 && ((uintptr_t)p.D & 15) == 0 && !g_gemm_no_tma_store) {
+        constexpr int PW = BN >= 64 ? 64 : BN;
+        if (int rc = make_tmap_2d(&tmD, p.D, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldd, PW, 32,
+                                  PW == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
+            return rc;
+        q.tma_store = 1;
+    }
     q.m_tiles = dmp_ceil_div(p.M, BM);
     q.n_tiles = dmp_ceil_div(p.N, BN);
     q.splits = splits;
@@ -330,7 +378,7 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
         DMP_REQUIRE(splits == 1 && q.n_tiles <= grid, "gemm statistics epilogue: %d column tiles do not fit the grid", q.n_tiles);
         grid = grid / q.n_tiles * q.n_tiles;
     }
-    kern<<<(int)grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, q);
+    kern<<<(int)grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, tmD, q);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
