@@ -40,15 +40,16 @@ struct GemmParams {
 // (32-64 KB) in the air.  One CTA per SM owns the whole 227 KB, so the ring takes ~200 KB of it: 6 stages at BN=128, 8 below.
 // Narrow tiles (BN <= 64, 20-24 KB per stage) keep two CTAs per SM instead and take 3 stages.
 constexpr int STAT_SMEM_BYTES = 4 * 32 * 33 * 4;  // per epilogue warp: a padded 32 x 32 fp32 transpose tile
+constexpr int stg_warp_bytes(int bn) { return (32 * (bn * 2 + 16) + 1023) / 1024 * 1024; }  // output staging per epilogue warp
 constexpr int gemm_stages(int b_rows, bool stats) {
     const int per = BM * BK * 2 + b_rows * BK * 2;
     if (per <= 24 * 1024) return 3;  // + 8-16 KB output staging (+ statistics scratch) stays under half an SM's shared memory
-    const int s = (200 * 1024 - 4 * 32 * b_rows * 2 - (stats ? STAT_SMEM_BYTES : 0)) / per;
+    const int s = (200 * 1024 - 4 * stg_warp_bytes(b_rows) - (stats ? STAT_SMEM_BYTES : 0)) / per;
     return s > 8 ? 8 : s;
 }
 
 template <int BN, bool A_MN, bool B_MN, bool STATS>
-__global__ void __launch_bounds__(NUM_THREADS, 1)
+__global__ void __launch_bounds__(NUM_THREADS, BN <= 64 ? 2 : 1)  // narrow tiles keep two CTAs per SM (<= 168 registers)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;  // 16 KB
@@ -64,7 +65,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     // output staging for the TMA-store epilogue: per epilogue warp 32 rows x BN bf16, in panels of PW columns (128-byte rows,
     // SWIZZLE_128B; 64-byte rows and SWIZZLE_64B when BN == 32)
     constexpr int PW = BN >= 64 ? 64 : BN;
-    constexpr int STG_WARP_BYTES = 32 * BN * 2;
+    constexpr int STG_PITCH = BN * 2 + 16;                 // mode 2: padded rows, conflict-free both ways
+    constexpr int STG_WARP_BYTES = (32 * STG_PITCH + 1023) / 1024 * 1024;  // >= the 32 * BN * 2 the TMA layout needs, 1 KB aligned
     uint8_t* stg = smem + STAGES * STAGE_BYTES;
     uint64_t* full_bar = (uint64_t*)(stg + 4 * STG_WARP_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
@@ -82,7 +84,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
-        if (p.tma_store) tma_prefetch_desc(&tmD);
+        if (p.tma_store == 1) tma_prefetch_desc(&tmD);
         for (int s = 0; s < STAGES; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -191,17 +193,29 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             tcgen05_fence_after();
             const uint32_t taddr_row = tmem_base + buf * ACC_COLS + ((uint32_t)(lane_grp * 32) << 16);
             uint8_t* my_stg = stg + lane_grp * STG_WARP_BYTES;
-            if (p.tma_store) {  // the previous tile's bulk stores must have finished reading this warp's staging area
+            if (p.tma_store == 1) {  // the previous tile's bulk stores must have finished reading this warp's staging area
                 if (lane == 0) tma_store_wait_read();
                 __syncwarp();
             }
-#pragma unroll(STATS ? NCHUNK : 1)
+            // The whole accumulator row comes out of TMEM with ONE wait: there is a single epilogue warp per scheduler, so every
+            // tcgen05.wait::ld is fully exposed latency (4 serialised waits per tile used to dominate this kernel).  The
+            // accumulator buffer goes back to the MMA warp right after the loads, before any conversion or store.
+            uint32_t rall[NCHUNK][32];
+#pragma unroll
+            for (int ci = 0; ci < NCHUNK; ++ci) {
+                if (n0 + ci * 32 < p.N) {  // warp-uniform
+                    if (BN >= 32) tmem_ld_32(taddr_row + ci * 32, rall[ci]);
+                    else tmem_ld_16(taddr_row + ci * 32, rall[ci]);
+                }
+            }
+            tmem_ld_wait();
+            tcgen05_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[buf]);  // this warp is done reading the accumulator
+#pragma unroll
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.N) break;  // warp-uniform
-                uint32_t r[32];
-                if (BN >= 32) tmem_ld_32(taddr_row + c0, r);
-                else tmem_ld_16(taddr_row + c0, r);
-                tmem_ld_wait();
+                uint32_t* r = rall[c0 / 32];
                 if (STATS) {
                     // column sums over this warp's 32 rows: transpose through a padded shared tile (conflict-free both ways)
                     float* tr = stat_smem + lane_grp * (32 * 33);
@@ -234,7 +248,15 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                         for (int j = 0; j < 32; ++j)
                             if (n + j < p.N) v[j] += p.bias[n + j];
                     }
-                    if (p.epi == 0 && p.tma_store) {
+                    if (p.epi == 0 && p.tma_store == 2) {
+                        // padded row-major staging; written back below as whole 2*BN-byte rows
+                        uint8_t* rowp = my_stg + lane * STG_PITCH + c0 * 2;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            bf16x8 o = float_to_bf16x8(v + j);
+                            *(int4*)(rowp + j * 2) = *(int4*)&o;
+                        }
+                    } else if (p.epi == 0 && p.tma_store == 1) {
                         // lane = row of the warp's 32 x BN slab; 16-byte chunks are XOR-swizzled exactly as the tensor map expects
                         const int panel = c0 / PW;
                         const int chunk0 = (c0 % PW) >> 3;
@@ -281,12 +303,26 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                 }
             }
-            tcgen05_fence_before();
-            if (p.tma_store) fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy)
+            if (p.tma_store == 1) fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy)
             __syncwarp();
+            if (p.tma_store == 2) {
+                // coalesced write-back: one warp instruction stores LPR-lane-wide whole rows (16 bytes per lane), so every
+                // request is a run of full 32-byte sectors instead of 32 scattered 16-byte pieces
+                constexpr int LPR = BN / 8;             // lanes per row (16-byte pieces per row): 16 / 8 / 4
+                constexpr int RPI = 32 / LPR;           // rows per instruction
+                const int piece = lane % LPR, rsub = lane / LPR;
+                const int ncol = n0 + piece * 8;
+                bf16* dbase = (bf16*)p.D + (long long)(m0 + lane_grp * 32) * p.ldd + ncol;
+#pragma unroll 4
+                for (int r0 = 0; r0 < 32; r0 += RPI) {
+                    const int rr = r0 + rsub;
+                    if (m0 + lane_grp * 32 + rr < p.M && ncol < p.N)
+                        *(int4*)(dbase + (long long)rr * p.ldd) = *(const int4*)(my_stg + rr * STG_PITCH + piece * 16);
+                }
+                __syncwarp();  // the staging rows are rewritten by the next tile
+            }
             if (lane == 0) {
-                mbar_arrive(&tmem_empty_bar[buf]);  // this warp is done reading the accumulator
-                if (p.tma_store && m0 + lane_grp * 32 < p.M) {
+                if (p.tma_store == 1 && m0 + lane_grp * 32 < p.M) {
 #pragma unroll
                     for (int pn = 0; pn < BN / PW; ++pn)
                         if (n0 + pn * PW < p.N) tma_store_2d(&tmD, my_stg + pn * (32 * PW * 2), n0 + pn * PW, m0 + lane_grp * 32);
@@ -294,7 +330,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 }
             }
         }
-        if (p.tma_store && lane == 0) tma_store_wait_all();  // shared memory must outlive the last bulk store
+        if (p.tma_store == 1 && lane == 0) tma_store_wait_all();  // shared memory must outlive the last bulk store
         if (STATS && blockIdx.x < num_items) {
             const int n0 = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;
 #pragma unroll
@@ -335,17 +371,21 @@ int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t out
     return 0;
 }
 
-// DMP_GEMM_TMA_STORE=0 keeps the register -> global epilogue (A/B measurements)
-const bool g_gemm_no_tma_store = [] {
-    const char* e = getenv("DMP_GEMM_TMA_STORE");
-    return e != nullptr && e[0] == '0';
+// bf16 epilogue: 1 (default) = swizzled shared-memory staging + TMA store, 2 = padded staging + whole-row 16-byte global
+// stores, 0 = registers straight to global (32 scattered 16-byte pieces per instruction).  DMP_GEMM_STORE_MODE overrides.
+// Measured on the 131072 x 144 x 24 forward GEMM: 37.7 / 39.2 / 46.5 us.  (Removing the stores altogether only gets to
+// ~25 us: with one 64-wide K block per tile the kernel is bound by TMA *load* issue -- every tile re-fetches its B panel
+// and a 24-channel row still costs a full 128-byte box row -- see profiles/README.md.)
+const int g_gemm_store_mode = [] {
+    const char* e = getenv("DMP_GEMM_STORE_MODE");
+    return (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
 }();
 
 template <int BN, bool A_MN, bool B_MN, bool STATS = false>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int smem_bytes = gemm_stages(B_ROWS, STATS) * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ +
-                               4 * 32 * BN * 2 /*output staging*/ + 256 /*barriers*/ + (STATS ? STAT_SMEM_BYTES : 0);
+                               4 * stg_warp_bytes(BN) /*output staging*/ + 256 /*barriers*/ + (STATS ? STAT_SMEM_BYTES : 0);
     auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, STATS>;
     static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
     static int configured_dev_mask = 0;
@@ -360,12 +400,14 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     // bf16 outputs leave through TMA when the rows are 16-byte aligned: box = {one panel of PW columns, one epilogue warp's 32 rows}
     CUtensorMap tmD = tmA;
     q.tma_store = 0;
-    if (p.epi == 0 && (p.ldd & 7) == 0 && ((uintptr_t)p.D & 15) == 0 && !g_gemm_no_tma_store) {
-        constexpr int PW = BN >= 64 ? 64 : BN;
-        if (int rc = make_tmap_2d(&tmD, p.D, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldd, PW, 32,
-                                  PW == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
-            return rc;
-        q.tma_store = 1;
+    if (p.epi == 0 && (p.ldd & 7) == 0 && (p.N & 7) == 0 && ((uintptr_t)p.D & 15) == 0 && g_gemm_store_mode != 0) {
+        q.tma_store = g_gemm_store_mode;
+        if (q.tma_store == 1) {
+            constexpr int PW = BN >= 64 ? 64 : BN;
+            if (int rc = make_tmap_2d(&tmD, p.D, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldd, PW, 32,
+                                      PW == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
+                return rc;
+        }
     }
     q.m_tiles = dmp_ceil_div(p.M, BM);
     q.n_tiles = dmp_ceil_div(p.N, BN);
