@@ -35,4 +35,10 @@ def _entry(rank, world, port, fn, args):
 
 def run_gloo(fn, world=2, *args):
     """Runs ``fn(rank, world, *args)`` in ``world`` gloo processes; raises if any of them fails."""
-    mp.spawn(_entry, args=(world, free_port(), fn, args), nprocs=world, join=True)
+    for attempt in range(3):  # the probed port can be taken again before rank 0 listens on it: pick another one and retry
+        try:
+            mp.spawn(_entry, args=(world, free_port(), fn, args), nprocs=world, join=True)
+            return
+        except Exception as e:  # noqa: BLE001
+            if "EADDRINUSE" not in str(e) or attempt == 2:
+                raise

@@ -29,7 +29,13 @@ def _init(rank, world, port):
 
 
 def _spawn(fn, world=2, *args):
-    mp.spawn(fn, args=(world, _free_port()) + args, nprocs=world, join=True)
+    for attempt in range(3):  # the probed port can be taken again before rank 0 listens on it: pick another one and retry
+        try:
+            mp.spawn(fn, args=(world, _free_port()) + args, nprocs=world, join=True)
+            return
+        except Exception as e:  # noqa: BLE001
+            if "EADDRINUSE" not in str(e) or attempt == 2:
+                raise
 
 
 # ------------------------------------------------------------------------------------------------ collectives
