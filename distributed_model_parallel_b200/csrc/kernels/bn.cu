@@ -604,7 +604,11 @@ int bn_coop_grid(K kernel, long long nvec, int C, int vec, size_t smem) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BN_THREADS, smem) != cudaSuccess || per_sm < 1) return -1;
     if (per_sm > 2) per_sm = 2;
     long long cap = (long long)dmp_num_sms() * per_sm;
-    long long want = (nvec + BN_THREADS * 8 - 1) / (BN_THREADS * 8);
+    // 8 16-byte vectors per thread.  Measured (bench/bn_phase_bench.py): fewer, fatter blocks are slower across the board
+    // (16 per thread: +2..5 us per launch); thinner ones (4) gain ~1 us on narrow layers in isolation but cost wide layers
+    // 2 us (every block ends with 2*C double atomics) and the whole step came out slower (5.05 vs 4.96 ms).
+    const int vecs_per_thread = 8;
+    long long want = (nvec + BN_THREADS * vecs_per_thread - 1) / (BN_THREADS * vecs_per_thread);
     if (want > cap) want = cap;
     long long g = (want / q) * q;
     if (g < q) g = q;
