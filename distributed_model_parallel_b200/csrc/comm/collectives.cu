@@ -471,7 +471,8 @@ DMP_API int dmp_gather_peer(void* const* src, const long long* bytes, int n_src,
 DMP_API int dmp_copy_peer(const void* src, void* dst, long long bytes, int max_blocks, cudaStream_t stream) {
     DMP_REQUIRE(bytes % 16 == 0, "dmp_copy_peer: size must be a multiple of 16 bytes");
     if (bytes == 0) return 0;
-    if (getenv("DMP_DEBUG_PEER")) {
+    static const bool debug_peer = getenv("DMP_DEBUG_PEER") != nullptr;  // diagnostic print of where both ends live
+    if (debug_peer) {
         int dev = -1, can = -1;
         cudaGetDevice(&dev);
         cudaPointerAttributes a, b;
