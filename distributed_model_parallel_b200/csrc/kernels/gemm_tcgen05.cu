@@ -118,17 +118,30 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     uint8_t* sa = smem + s * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
                     const int k0 = kb * BK;
-                    mbar_expect_tx(&full_bar[s], STAGE_BYTES);
+                    // MN-major operands arrive as 64-wide boxes.  A box that lies entirely past M (or N) is not fetched at all:
+                    // the TMA unit would still spend a full box of issue slots on it, and these GEMMs are bound by exactly that
+                    // (Cout <= 64 halves the weight-gradient's A traffic).  The MMA then reads stale shared memory for those
+                    // rows/columns; accumulator rows and columns are independent and the epilogue masks everything >= M, N.
+                    constexpr int BOX_BYTES = 64 * BK * 2;
+                    uint32_t tx = STAGE_BYTES;
+                    const bool a_hi = !A_MN || (m0 + 64 < p.M);
+                    if (A_MN && !a_hi) tx -= BOX_BYTES;
+                    if (B_MN) {
+#pragma unroll
+                        for (int c = 1; c < B_ROWS / 64; ++c)
+                            if (n0 + c * 64 >= p.N) tx -= BOX_BYTES;
+                    }
+                    mbar_expect_tx(&full_bar[s], tx);
                     if (A_MN) {
                         tma_load_2d(sa, &tmA, &full_bar[s], m0, k0);  // global A^T [K, M]: two boxes of {64 m, 64 k}
-                        tma_load_2d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0);
+                        if (a_hi) tma_load_2d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0);
                     } else {
                         tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);  // box {64 k, 128 m}
                     }
                     if (B_MN) {
 #pragma unroll
                         for (int c = 0; c < B_ROWS / 64; ++c)
-                            tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0);
+                            if (c == 0 || n0 + c * 64 < p.N) tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0);
                     } else {
                         tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);  // box {64 k, BN n}
                     }

@@ -36,6 +36,8 @@ GEMM_SHAPES = [
     # (M, N, K)
     (128, 128, 64), (256, 64, 128), (128, 32, 16), (1000, 96, 24), (4096, 144, 24), (2048, 1280, 320),
     (333, 200, 72), (8192, 16, 32), (512, 960, 160), (128, 256, 1024),
+    # few output rows (weight-gradient shapes: M = Cout, long K): MN-major boxes that lie entirely past M / N are skipped
+    (64, 96, 256), (24, 144, 512), (144, 24, 2048), (16, 96, 4096), (160, 320, 192),
 ]
 
 
