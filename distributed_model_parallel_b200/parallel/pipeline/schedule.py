@@ -36,6 +36,17 @@ def generate_schedule(kind: str, num_stages: int, stage: int, num_microbatches: 
     return [int(out[i]) for i in range(n)]
 
 
+def max_in_flight(order: List[int]) -> int:
+    """Largest number of micro-batches whose forward has run but whose backward has not, over one stage's step order.
+    Micro-batches retire in FIFO order in every schedule generated here, so this is also the number of activation slots
+    (and captured CUDA-graph pairs) the stage needs: M for GPipe, min(M, W - stage) for 1F1B."""
+    live = peak = 0
+    for op in order:
+        live += 1 if op > 0 else -1
+        peak = max(peak, live)
+    return peak
+
+
 def simulate_schedule(kind: str, num_stages: int, num_microbatches: int, tf: float = 1.0, tb: float = 2.0):
     """(makespan, peak in-flight activations per stage) from the native event simulator; raises on deadlock."""
     peak = (C.c_int32 * num_stages)()
@@ -298,10 +309,7 @@ class PipelineStage:
         pending = None  # (tensor, peer) produced by the previous step, sent together with the next receive
         graphed = self.use_graphs and len(set(sizes)) == 1
         if graphed:
-            live = n_slots = 0  # micro-batches retire in FIFO order, so the deepest in-flight count is the number of slots
-            for o in order:
-                live += 1 if o > 0 else -1
-                n_slots = max(n_slots, live)
+            n_slots = max_in_flight(order)
             if self._slots_key != self._graph_key(sizes[0], n_slots, B):
                 self._slots = None  # releases the previous graphs and their pool
                 try:

@@ -70,6 +70,30 @@ def test_schedules_are_complete_and_deadlock_free(kind, w, m):
         assert all(p == m for p in peak)
 
 
+@settings(max_examples=60, deadline=None)
+@given(st.integers(1, 8), st.integers(1, 24), st.sampled_from(["gpipe", "1f1b"]))
+def test_graph_slot_count_and_fifo_retirement(w, m, kind):
+    """The CUDA-graph path of PipelineStage gives micro-batch i slot i % n_slots with n_slots = max_in_flight(order): that is
+    only sound if (a) the in-flight depth never exceeds n_slots and (b) the occupant of a slot has retired (its backward has
+    run) before the slot is filled again.  Checked against the native schedule generator for every stage."""
+    from distributed_model_parallel_b200.parallel.pipeline import max_in_flight
+
+    for s in range(w):
+        order = generate_schedule(kind, w, s, m)
+        n_slots = max_in_flight(order)
+        assert n_slots == (m if kind == "gpipe" else min(m, w - s))
+        occupant = {}
+        for op in order:
+            i = abs(op) - 1
+            slot = i % n_slots
+            if op > 0:
+                assert slot not in occupant, (kind, w, s, m, order)
+                occupant[slot] = i
+            else:
+                assert occupant.pop(slot) == i
+        assert not occupant
+
+
 def test_naive_schedule_is_one_batch_in_flight():
     assert generate_schedule("naive", 4, 2, 1) == [1, -1]
     with pytest.raises(ValueError):
