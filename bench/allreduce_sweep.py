@@ -43,6 +43,14 @@ def timed(fn, iters):
     return float(t.item()) * 1e-3
 
 
+try:  # NVLS multicast buffer (switch-side reduction); absent on platforms without multicast support
+    from distributed_model_parallel_b200.parallel.symm import ProcessMulticast
+    mcbuf = ProcessMulticast(args.max_mb * 1024 * 1024)
+except Exception as e:  # noqa: BLE001
+    mcbuf = None
+    if rank == 0:
+        print("# NVLS multicast unavailable: %s" % str(e)[:200], flush=True)
+
 rows = []
 mb = 1
 sizes = []
@@ -70,6 +78,9 @@ for mb in sizes:
                                  out.data_ptr() if algo == 0 else None, None, None, None, None, 0, None, None, 0, 0, sp)), iters)
         res[name + "_fused_sgd_s"] = timed(lambda: _native.check(lib.dmp_allreduce_fused(algo, 0, buf.ptrs, state.ptrs, rank, world, n, 1.0 / world,
                                            None, master.data_ptr(), mom.data_ptr(), shadow.data_ptr(), hp.data_ptr(), 0, pbuf.ptrs, sbuf.ptrs, 1, 0, sp)), iters)
+    if mcbuf is not None:
+        mcbuf.view(torch.float32, n).normal_()
+        res["nvls_s"] = timed(lambda: _native.check(lib.dmp_allreduce_nvls(mcbuf.mc_ptr, state.ptrs, rank, world, n, 1.0 / world, 0, sp)), iters)
     # NCCL + separate fused SGD kernel = what the fused variants replace
     res["nccl_plus_sgd_s"] = timed(lambda: (dist.all_reduce(ref), lib.dmp_sgd_flat(master.data_ptr(), shadow.data_ptr(), ref.data_ptr(), 0, mom.data_ptr(), n, hp.data_ptr(), 0, 1, sp)), iters)
     f = 2.0 * (world - 1) / world

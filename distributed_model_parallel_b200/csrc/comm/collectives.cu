@@ -270,6 +270,39 @@ allreduce_twoshot_kernel(PeerPtrs bufs, PeerPtrs flags, uint32_t* epoch_mem, uin
 }
 
 // ------------------------------------------------------------------------------------------------
+// NVLS all-reduce (two-shot through the switch): `mc` is the multicast address of a buffer every rank has bound its copy to
+// (csrc/comm/multicast.cu).  Rank r pulls slice r with multimem.ld_reduce -- the NVSwitch reads all W copies and returns
+// their sum, so each element crosses this GPU's link once instead of W-1 times -- scales it, and pushes it back with
+// multimem.st, which the switch replicates into every copy.  In place; slices are disjoint, so there is no hazard between
+// the phases of different ranks, and all ranks end up with bitwise identical values (one sum, broadcast).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(DMP_COMM_THREADS)
+allreduce_nvls_kernel(float* mc, PeerPtrs flags, uint32_t* epoch_mem, uint32_t* status, int rank, int W, long long nvec,
+                      float scale) {
+    uint32_t epoch = epoch_mem[blockIdx.x];
+    __syncthreads();
+    if (!barrier_ranks(flags, rank, W, epoch + 1, status, false)) return;  // every rank's input is in place
+    const long long per = (nvec + W - 1) / W;
+    const long long lo = per * rank;
+    long long hi = lo + per;
+    if (hi > nvec) hi = nvec;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; v < hi; v += stride) {
+        float a, b, c, d;
+        float4* p = (float4*)mc + v;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=f"(a), "=f"(b), "=f"(c), "=f"(d)
+                     : "l"(p)
+                     : "memory");
+        a *= scale; b *= scale; c *= scale; d *= scale;
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d)
+                     : "memory");
+    }
+    if (!barrier_ranks(flags, rank, W, epoch + 2, status)) return;  // system-scope fence inside: the multicast stores are visible
+    if (threadIdx.x == 0) epoch_mem[blockIdx.x] = epoch + 2;
+}
+
+// ------------------------------------------------------------------------------------------------
 // broadcast: the source rank stores its buffer into every destination (peer stores, or one multimem.st
 // through an NVLS multicast mapping).  Optional fp32 -> bf16 cast into a second set of destinations.
 // With flags == null pointers (single-process DataParallel) ordering comes from stream events instead.
@@ -421,6 +454,25 @@ DMP_API int dmp_allreduce_fused(int algo, int dtype, void* const* bufs, void* co
         if (dtype == 0) allreduce_twoshot_kernel<float><<<grid, DMP_COMM_THREADS, 0, stream>>>(b, f, epoch_mem, status, rank, W, nvec, scale, s, pp, sp, zero_after);
         else allreduce_twoshot_kernel<bf16><<<grid, DMP_COMM_THREADS, 0, stream>>>(b, f, epoch_mem, status, rank, W, nvec, scale, s, pp, sp, zero_after);
     }
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// In-place fp32 all-reduce (sum * scale) of the n floats behind the multicast address `mc` (see allreduce_nvls_kernel).
+// state[W]: peer pointers of a communicator state, as for dmp_allreduce_fused.  n*4 must be a multiple of 16*W bytes.
+DMP_API int dmp_allreduce_nvls(void* mc, void* const* state, int rank, int W, long long n, float scale, int max_blocks,
+                               cudaStream_t stream) {
+    DMP_REQUIRE(mc != nullptr && W >= 2 && W <= DMP_MAX_RANKS && rank >= 0 && rank < W, "dmp_allreduce_nvls: bad arguments");
+    DMP_REQUIRE((n * 4) % (16 * (long long)W) == 0, "dmp_allreduce_nvls: buffer must be padded to 16*W bytes");
+    const long long nvec = n / 4;
+    if (nvec == 0) return 0;
+    PeerPtrs f = make_ptrs(state, W);
+    uint32_t* st = (uint32_t*)state[rank];
+    uint32_t* epoch_mem = st + FLAGS_WORDS;
+    uint32_t* status = epoch_mem + DMP_COMM_MAX_BLOCKS;
+    const int grid = comm_grid(nvec / W, max_blocks);
+    allreduce_nvls_kernel<<<grid, DMP_COMM_THREADS, 0, stream>>>((float*)mc, f, epoch_mem, status, rank, W, nvec, scale);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;

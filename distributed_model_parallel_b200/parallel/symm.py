@@ -144,6 +144,85 @@ def reset_comm_status(state: SymmBuffer) -> None:
     comm_status_words(state)[0] = 0
 
 
+class ProcessMulticast:
+    """NVLS multicast buffer across the ranks of a process group (one process per GPU).
+
+    ``local`` is a uint8 tensor over this rank's copy; ``mc_ptr`` is the multicast address: ``multimem.ld_reduce`` on
+    ``mc_ptr + off`` returns the switch-side sum of every rank's bytes at ``off``, ``multimem.st`` writes all copies at once.
+    Rank 0 creates the driver object and passes its POSIX file descriptor to the peers over an abstract-namespace Unix
+    socket (SCM_RIGHTS); the socket name travels through ``torch.distributed``.  Raises RuntimeError if the platform has no
+    multicast support -- callers keep the peer-load kernels in that case."""
+
+    def __init__(self, nbytes: int, group=None, device: Optional[torch.device] = None):
+        import os
+        import socket
+        import uuid
+
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank = dist.get_rank(self.group)
+        self.world_size = dist.get_world_size(self.group)
+        self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.lib = _native.kernels()
+        dev = int(self.device.index or 0)
+        ok = bool(self.lib.dmp_mc_supported((C.c_int * 1)(dev), 1))
+        oks = [None] * self.world_size
+        dist.all_gather_object(oks, ok, group=self.group)
+        if not all(oks):
+            raise RuntimeError("NVLS multicast is not supported on every rank's device")
+        handle, size = C.c_void_p(), C.c_longlong()
+        src = dist.get_global_rank(self.group, 0) if self.group is not dist.group.WORLD else 0
+        if self.rank == 0:
+            fd = C.c_int(-1)
+            _native.check(self.lib.dmp_mc_xp_create(dev, self.world_size, int(nbytes), C.byref(handle), C.byref(fd), C.byref(size)),
+                          "mc_xp_create")
+            name = "\0dmp_mc_%d_%s" % (os.getpid(), uuid.uuid4().hex)
+            srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            srv.bind(name)
+            srv.listen(self.world_size)
+            dist.broadcast_object_list([name], src=src, group=self.group)
+            srv.settimeout(60.0)
+            for _ in range(self.world_size - 1):
+                conn, _addr = srv.accept()
+                socket.send_fds(conn, [b"fd"], [fd.value])
+                conn.recv(1)  # the peer has the descriptor: safe to close ours afterwards
+                conn.close()
+            srv.close()
+            os.close(fd.value)
+        else:
+            box = [None]
+            dist.broadcast_object_list(box, src=src, group=self.group)
+            cli = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+            cli.settimeout(60.0)
+            cli.connect(box[0])
+            _msg, fds, _flags, _addr = socket.recv_fds(cli, 16, 1)
+            cli.send(b"k")
+            cli.close()
+            _native.check(self.lib.dmp_mc_xp_import(dev, int(fds[0]), self.world_size, int(nbytes), C.byref(handle), C.byref(size)),
+                          "mc_xp_import")
+            os.close(fds[0])
+        self._handle = handle
+        _native.check(self.lib.dmp_mc_xp_add_device(handle), "mc_xp_add_device")
+        dist.barrier(group=self.group)  # every device must be part of the object before the first bind
+        uc, mc = C.c_void_p(), C.c_void_p()
+        _native.check(self.lib.dmp_mc_xp_bind_map(handle, C.byref(uc), C.byref(mc)), "mc_xp_bind_map")
+        dist.barrier(group=self.group)
+        self.size = int(size.value)
+        self.mc_ptr = int(mc.value)
+        self.local = torch.as_tensor(_RawCuda(uc.value, self.size, self), device=self.device)
+
+    def view(self, dtype: torch.dtype, numel: int, byte_offset: int = 0) -> torch.Tensor:
+        esz = torch.empty((), dtype=dtype).element_size()
+        return self.local[byte_offset: byte_offset + numel * esz].view(dtype)
+
+    def __del__(self):
+        try:
+            if getattr(self, "_handle", None):
+                self.lib.dmp_mc_xp_destroy(self._handle)
+                self._handle = None
+        except Exception:
+            pass
+
+
 class DeviceSymmGroup:
     """Peer-addressable buffers across several devices of one process (DataParallel)."""
 

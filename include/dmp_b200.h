@@ -154,6 +154,17 @@ int dmp_mc_supported(const int* devs, int ndev);
 int dmp_mc_create(const int* devs, int ndev, long long bytes, void** out_handle, void** out_unicast, void** out_mc,
                   long long* out_size);
 int dmp_mc_destroy(void* handle);
+/* Cross-process multicast object (one process per GPU).  Rank 0 creates it and hands *out_fd (a POSIX file descriptor) to the
+ * other ranks (SCM_RIGHTS over a Unix socket), which import it; then every rank adds its device, ALL ranks synchronise, and
+ * every rank binds + maps: *out_unicast is the rank's own copy, *out_mc the multicast address for multimem.* instructions. */
+int dmp_mc_xp_create(int dev, int ndev_total, long long bytes, void** out_handle, int* out_fd, long long* out_size);
+int dmp_mc_xp_import(int dev, int fd, int ndev_total, long long bytes, void** out_handle, long long* out_size);
+int dmp_mc_xp_add_device(void* handle);
+int dmp_mc_xp_bind_map(void* handle, void** out_unicast, void** out_mc);
+int dmp_mc_xp_destroy(void* handle);
+/* In-place fp32 all-reduce through the NVSwitch: multimem.ld_reduce of the caller's 1/W slice, scale, multimem.st. */
+int dmp_allreduce_nvls(void* mc, void* const* state, int rank, int W, long long n, float scale, int max_blocks,
+                       dmp_stream_t stream);
 
 /* peer-memory plumbing */
 int dmp_symm_malloc(long long bytes, void** out);

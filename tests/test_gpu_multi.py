@@ -80,6 +80,55 @@ def test_allreduce_oneshot_twoshot():
     _spawn(_w_allreduce)
 
 
+# ------------------------------------------------------------------------------------------------ NVLS (switch-side) all-reduce
+def _w_allreduce_nvls(rank, world, port):
+    """multimem.ld_reduce / multimem.st all-reduce on a cross-process multicast buffer vs the sum NCCL all-gathers."""
+    _init(rank, world, port)
+    from distributed_model_parallel_b200 import _native
+    from distributed_model_parallel_b200.parallel.symm import ProcessMulticast, ProcessSymmGroup
+
+    lib = _native.kernels()
+    g = ProcessSymmGroup()
+    state = g.new_state()
+    sp = torch.cuda.current_stream().cuda_stream
+    n = 1 << 20
+    try:
+        mc = ProcessMulticast(n * 4)
+    except RuntimeError as e:
+        if "not supported" in str(e):
+            dist.destroy_process_group()
+            return
+        raise
+    t = mc.view(torch.float32, n)
+    for rep in range(3):
+        for m in (n, 4096 * world, 64 * world):
+            torch.manual_seed(1000 * rep + 10 * rank + 1)
+            x = torch.randn(m, device="cuda")
+            t[:m].copy_(x)
+            gathered = [torch.empty_like(x) for _ in range(world)]
+            dist.all_gather(gathered, x)
+            want = sum(gathered) / world
+            torch.cuda.synchronize()
+            dist.barrier()
+            _native.check(lib.dmp_allreduce_nvls(mc.mc_ptr, state.ptrs, rank, world, m, 1.0 / world, 0, sp), "allreduce nvls")
+            torch.cuda.synchronize()
+            err = (t[:m] - want).abs().max().item()
+            assert err <= 1e-5 * max(1.0, want.abs().max().item()), (rep, m, err)
+            # bitwise identical on every rank: one switch-side sum, replicated
+            mine = t[:m].clone()
+            other = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(other, mine)
+            assert all(torch.equal(other[0], o) for o in other)
+            dist.barrier()
+    assert lib.dmp_comm_status(state.local.data_ptr(), sp) == 0
+    del t, mc
+    dist.destroy_process_group()
+
+
+def test_allreduce_nvls_multimem_cross_process():
+    _spawn(_w_allreduce_nvls)
+
+
 # ------------------------------------------------------------------------------------------------ fault injection / races
 def _w_dead_peer(rank, world, port):
     """A rank that never joins the collective (a dead peer) must turn into a status code, not a hung kernel."""
