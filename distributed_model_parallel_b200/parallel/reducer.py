@@ -181,6 +181,12 @@ class PeerBackend:
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._launched_any = False
         self.kernel_launches = 0
+        # Opt-in (DMP_DDP_NVLS=1): fp32 buckets of at least DMP_DDP_NVLS_MIN_BYTES (default 8 MiB) without a fused optimizer
+        # live in an NVLS multicast buffer and are reduced inside the switch (multimem.ld_reduce / multimem.st).  Off by
+        # default: at W = 2 the peer-load two-shot is faster (profiles/README.md); meant for W = 8.
+        self.nvls = os.environ.get("DMP_DDP_NVLS", "0") == "1" and self.world_size > 1
+        self.nvls_min_bytes = int(os.environ.get("DMP_DDP_NVLS_MIN_BYTES", 8 << 20))
+        self.nvls_launches = 0
 
     def pad_multiple(self, dtype) -> int:
         esz = torch.empty((), dtype=dtype).element_size()
@@ -190,6 +196,13 @@ class PeerBackend:
         if self.symm is None or not symmetric:
             return torch.zeros(numel, dtype=dtype, device=device), None
         esz = torch.empty((), dtype=dtype).element_size()
+        if self.nvls and symmetric == "nvls_ok" and dtype == torch.float32 and numel * esz >= self.nvls_min_bytes:
+            from .symm import ProcessMulticast
+            try:
+                mc = ProcessMulticast(numel * esz, self.group, self.device)
+                return mc.view(dtype, numel), mc
+            except RuntimeError:  # no multicast on this platform (every rank takes this branch together)
+                self.nvls = False
         buf = self.symm.alloc(numel * esz)
         return buf.view(dtype, numel), buf
 
@@ -217,7 +230,11 @@ class PeerBackend:
             return
         algo = 0 if nbytes <= self.oneshot_max_bytes else 1
         scale = 1.0 / W
-        if fused is None:
+        if fused is None and hasattr(bucket.symm, "mc_ptr"):  # bucket lives in a multicast buffer: reduce inside the switch
+            _native.check(lib.dmp_allreduce_nvls(bucket.symm.mc_ptr, self.state.ptrs, self.rank, W, flat.numel(), scale,
+                                                 self.max_blocks, sp), "allreduce nvls")
+            self.nvls_launches += 1
+        elif fused is None:
             out = None
             if algo == 0:
                 if bucket.scratch is None:
@@ -357,7 +374,8 @@ class Reducer:
         self.buckets: List[Bucket] = []
         bucket_of = [0] * len(self.params)
         for b, idxs in enumerate(assignment):
-            bk = Bucket(b, idxs, [self.params[i] for i in idxs], self.backend)
+            # plain gradient buckets (no fused optimizer state to ship to peers) may live in an NVLS multicast buffer
+            bk = Bucket(b, idxs, [self.params[i] for i in idxs], self.backend, "nvls_ok" if self.fused_cfg is None else True)
             self.buckets.append(bk)
             for i in idxs:
                 bucket_of[i] = b

@@ -129,6 +129,43 @@ def test_allreduce_nvls_multimem_cross_process():
     _spawn(_w_allreduce_nvls)
 
 
+def _w_ddp_nvls(rank, world, port):
+    """DDP with its large fp32 buckets in NVLS multicast buffers (DMP_DDP_NVLS=1): gradients equal the NCCL average."""
+    os.environ["DMP_DDP_NVLS"] = "1"
+    os.environ["DMP_DDP_NVLS_MIN_BYTES"] = str(1 << 20)
+    _init(rank, world, port)
+    import copy
+    import torch.nn as nn
+    from distributed_model_parallel_b200.parallel import DistributedDataParallel as DDP
+
+    torch.manual_seed(0)
+    base = nn.Sequential(nn.Linear(512, 1024), nn.ReLU(), nn.Linear(1024, 1024), nn.ReLU(), nn.Linear(1024, 16)).cuda()
+    ours = DDP(copy.deepcopy(base), device_ids=[rank], comm_backend="peer", bucket_cap_mb=3)
+    plain = copy.deepcopy(base)
+    if not ours.backend.nvls:  # platform without multicast: nothing to test
+        dist.destroy_process_group()
+        return
+    for it in range(3):
+        torch.manual_seed(100 + 10 * it + rank)
+        x = torch.randn(32, 512, device="cuda")
+        for m in (ours, plain):
+            m.zero_grad(set_to_none=True)
+            m(x).square().mean().backward()
+        torch.cuda.synchronize()
+        for (n, p), q in zip(ours.module.named_parameters(), plain.parameters()):
+            g = q.grad.clone()
+            dist.all_reduce(g)
+            g /= world
+            assert torch.allclose(p.grad, g, rtol=1e-4, atol=1e-6), (it, n, (p.grad - g).abs().max().item())
+    assert ours.backend.nvls_launches > 0
+    ours.check_health()
+    dist.destroy_process_group()
+
+
+def test_ddp_buckets_in_nvls_multicast_buffers():
+    _spawn(_w_ddp_nvls)
+
+
 # ------------------------------------------------------------------------------------------------ fault injection / races
 def _w_dead_peer(rank, world, port):
     """A rank that never joins the collective (a dead peer) must turn into a status code, not a hung kernel."""
