@@ -343,6 +343,24 @@ class DistributedDataParallel(nn.Module):
     def _set_static_graph(self):
         self.static_graph = True
 
+    def _get_ddp_logging_data(self) -> dict:
+        """Construction-time and run-time facts about this wrapper (torch distributed.py ``_get_ddp_logging_data`` / the
+        ``dist.Logger`` it feeds): back end, world size, bucket layout, iteration / launch / rebuild counters.  The trainers
+        write it into their JSONL logs once per epoch."""
+        red = self.reducer
+        d = dict(self.logger_data)
+        d.update(rank=self.rank, num_parameters=len(self._params), num_buffers=len(self.modules_buffers),
+                 num_buckets=len(red.buckets), bucket_sizes=red.bucket_sizes(),
+                 total_parameter_bytes=sum(p.numel() * p.element_size() for p in self._params),
+                 find_unused_parameters=self.find_unused_parameters, gradient_as_bucket_view=self.gradient_as_bucket_view,
+                 static_graph=self.static_graph, broadcast_buffers=self.broadcast_buffers,
+                 fused_optimizer=self.optimizer is not None, iterations=red.stats.get("iterations", 0),
+                 buckets_launched=red.stats.get("buckets_launched", 0), rebuilds=red.stats.get("rebuilds", 0),
+                 globally_unused_last=red.stats.get("globally_unused", 0),
+                 comm_kernel_launches=getattr(self.backend, "kernel_launches", None),
+                 nvls_launches=getattr(self.backend, "nvls_launches", None))
+        return d
+
     def check_health(self):
         if hasattr(self.backend, "check_health"):
             self.backend.check_health()

@@ -38,7 +38,8 @@ def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
     sched = CosineWithWarmup(optimizer, cfg.lr, cfg.epochs, cfg.warmup_period)
     best_acc, start_epoch = -1.0, 0  # the first validated epoch always writes a checkpoint
     if cfg.resume:
-        best_acc, start_epoch = load_checkpoint(net, cfg.checkpoint, optimizer, sched)
+        best_acc, last_epoch = load_checkpoint(net, cfg.checkpoint, optimizer, sched)
+        start_epoch = last_epoch + 1  # the stored epoch is complete (see train/dp.py)
     step = TrainStep(net, optimizer, use_graph=cfg.cuda_graph and use_cuda)
     log = EpochLogger(os.path.join(cfg.log_dir, "ddp_%d.txt" % cfg.batch_size) if rank == 0 else None,
                       os.path.join(cfg.log_dir, "ddp_rank%d.jsonl" % rank), rank)
@@ -51,7 +52,9 @@ def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
         if rank == 0 and va > best_acc:
             save_best(net, va, epoch, cfg.checkpoint, optimizer, sched)
         best_acc = max(best_acc, va)
-        line = log.log_epoch(epoch, tl, ta, vl, va, bt, dt, lr=get_lr(optimizer))
+        imgs_per_s = cfg.batch_size * world_size / bt if bt else None  # bt: seconds per (per-rank) batch on this rank
+        line = log.log_epoch(epoch, tl, ta, vl, va, bt, dt, lr=get_lr(optimizer), images_per_s=imgs_per_s,
+                             ddp=net._get_ddp_logging_data())
         if rank == 0:
             print(line)
         net.check_health()

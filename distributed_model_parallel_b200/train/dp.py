@@ -21,18 +21,22 @@ def main(cfg: TrainConfig):
     torch.manual_seed(cfg.seed)
     device = torch.device("cuda:0" if torch.cuda.is_available() else "cpu")
     _, train_loader, val_loader = prepare_dataloader(cfg)
-    net = build_model(cfg.model).to(device)
-    if device.type == "cuda" and torch.cuda.device_count() > 1:
-        net = DataParallel(net)
+    # always wrapped, like the reference (data_parallel.py:74-76): checkpoints then carry the ``module.`` key prefix whatever the
+    # device count; with fewer than two GPUs the wrapper simply calls the module
+    net = DataParallel(build_model(cfg.model).to(device))
+    multi = device.type == "cuda" and torch.cuda.device_count() > 1
     optimizer = FlatFusedSGD(net.parameters(), lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay)
     sched = CosineWithWarmup(optimizer, cfg.lr, cfg.epochs, cfg.warmup_period)
     best_acc, start_epoch = -1.0, 0  # the first validated epoch always writes a checkpoint
     if cfg.resume:
-        best_acc, start_epoch = load_checkpoint(net, cfg.checkpoint, optimizer, sched)
+        # the checkpoint is written after its epoch's validation, with the optimizer and scheduler state of that moment: go
+        # on with the next epoch (the reference restarts AT the stored epoch, data_parallel.py:86-87 -- it has no such state)
+        best_acc, last_epoch = load_checkpoint(net, cfg.checkpoint, optimizer, sched)
+        start_epoch = last_epoch + 1
         optimizer.sync_shadow()
         print("==> resumed from %s (epoch %d, acc %.2f)" % (cfg.checkpoint, start_epoch, best_acc))
     # DataParallel spawns replica threads per forward, which a CUDA graph cannot capture: graphs only on one device
-    step = TrainStep(net, optimizer, use_graph=cfg.cuda_graph and not isinstance(net, DataParallel))
+    step = TrainStep(net if multi else net.module, optimizer, use_graph=cfg.cuda_graph and not multi)
     log = EpochLogger(os.path.join(cfg.log_dir, "data_para_%d.txt" % cfg.batch_size), os.path.join(cfg.log_dir, "dp.jsonl"))
     for epoch in range(start_epoch, cfg.epochs):
         tl, ta, bt, dt = train_epoch(step, train_loader, device, cfg)

@@ -36,6 +36,9 @@ def _w_parity(rank, world):
             assert torch.allclose(p, q, atol=1e-6, rtol=1e-5), (it, n)
     assert ours.reducer.stats["rebuilds"] == 1
     assert len(ours.reducer.buckets) > 1
+    info = ours._get_ddp_logging_data()
+    assert info["world_size"] == world and info["num_buckets"] == len(ours.reducer.buckets) and info["iterations"] == 3
+    assert sum(info["bucket_sizes"]) >= info["total_parameter_bytes"] and info["rebuilds"] == 1
     assert all(k.startswith("module.") for k in ours.state_dict())
     # buffers (BN running stats) are re-broadcast from rank 0 at every forward, exactly like torch's wrapper
     for (n, b), c in zip(ours.module.named_buffers(), ref.module.buffers()):
