@@ -60,3 +60,11 @@ def test_mp_trainer_two_stage_pipeline(tmp_path):
     assert text, logs
     line = open(tmp_path / "log" / text[0]).read().strip().splitlines()[-1]
     assert line.startswith("step:0") and "time_per_batch:" in line                        # model_parallel.py:119-124
+    # every stage wrote its shard; merged they are exactly the single-model state_dict
+    from distributed_model_parallel_b200.models import MobileNetV2
+    from distributed_model_parallel_b200.utils import merge_pipeline_shards
+
+    merged = merge_pipeline_shards(str(tmp_path / "ckpt" / "pipeline"), 2)
+    full = MobileNetV2()
+    assert set(merged) == set(full.state_dict())
+    full.load_state_dict(merged, strict=True)
