@@ -154,9 +154,11 @@ def runtime():
     if _rlib is None:
         with _lock:
             if _rlib is None:
-                path = _build.RUNTIME_LIB
-                if os.environ.get("DMP_B200_NO_BUILD") != "1":
-                    path = _build.build_runtime(verbose=False)
+                path = os.environ.get("DMP_B200_RT_LIB")  # e.g. an ASan/UBSan build, see tools/sanitize_runtime.sh
+                if not path:
+                    path = _build.RUNTIME_LIB
+                    if os.environ.get("DMP_B200_NO_BUILD") != "1":
+                        path = _build.build_runtime(verbose=False)
                 lib = C.CDLL(str(path))
                 _apply(lib, _RUNTIME_SIGS)
                 _rlib = lib
