@@ -69,3 +69,52 @@ def test_native_libraries_build_and_export_the_declared_abi():
 def test_graft_entry_build():
     import __graft_entry__ as g
     g.build()
+
+
+def _c_type_code(ctype: str) -> str:
+    """Collapses a C parameter / return type of include/dmp_b200.h to the class the ctypes tables use."""
+    t = ctype.replace("const", " ").strip()
+    if "*" in t or "dmp_stream_t" in t:
+        return "ptr"
+    t = " ".join(t.split())
+    return {"int": "i32", "long long": "i64", "unsigned long long": "u64", "float": "f32", "double": "f64", "void": "void",
+            "uint32_t": "u32", "int64_t": "i64", "int32_t": "i32"}[t]
+
+
+def test_ctypes_signatures_match_the_header():
+    """Every declaration of include/dmp_b200.h against the argtypes / restype registered in _native.py (and by the modules that
+    register runtime signatures): same arity, same scalar widths, pointers where the header has pointers.  A missing or narrower
+    argtype makes ctypes pass 64-bit pointers as 32-bit ints -- silently, until a kernel faults."""
+    import ctypes as C
+
+    from distributed_model_parallel_b200 import _native
+    from distributed_model_parallel_b200.parallel import reducer  # noqa: F401  (registers runtime signatures)
+    from distributed_model_parallel_b200.parallel.pipeline import partition  # noqa: F401
+
+    header = open(os.path.join(ROOT, "include", "dmp_b200.h")).read()
+    header = re.sub(r"/\*.*?\*/", " ", header, flags=re.S)
+    decls = re.findall(r"([A-Za-z_][A-Za-z0-9_ \*]*?)\b(dmp_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", header)
+    assert len(decls) > 60
+    code_of = {C.c_void_p: "ptr", C.c_char_p: "ptr", C.c_int: "i32", C.c_longlong: "i64", C.c_ulonglong: "u64", C.c_float: "f32",
+               C.c_double: "f64", C.c_uint: "u32", None: "void"}
+    tables = dict(_native._KERNEL_SIGS)
+    tables.update(_native._RUNTIME_SIGS)
+    problems = []
+    for ret, name, params in decls:
+        if name not in tables:
+            problems.append("%s: declared in the header but has no ctypes signature" % name)
+            continue
+        restype, argtypes = tables[name]
+        want_args = [] if params.strip() in ("", "void") else [_c_type_code(re.sub(r"\b[A-Za-z_][A-Za-z0-9_]*\s*(\[\s*\])?\s*$", lambda m: "*" if m.group(1) else "", p.strip()) or p)
+                                                              for p in params.split(",")]
+        have_args = [code_of.get(a, "ptr" if hasattr(a, "contents") or getattr(a, "_type_", None) is not None and a not in code_of else "?")
+                     for a in argtypes]
+        if len(want_args) != len(have_args):
+            problems.append("%s: header has %d parameters, ctypes table %d" % (name, len(want_args), len(have_args)))
+            continue
+        for i, (w, h) in enumerate(zip(want_args, have_args)):
+            if w != h:
+                problems.append("%s: parameter %d is %s in the header but %s in the ctypes table" % (name, i, w, h))
+        if _c_type_code(ret) != code_of.get(restype, "?"):
+            problems.append("%s: return type %s vs %s" % (name, _c_type_code(ret), code_of.get(restype, "?")))
+    assert not problems, "\n".join(problems)
