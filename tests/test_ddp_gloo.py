@@ -157,3 +157,32 @@ def _w_join(rank, world):
 
 def test_ddp_join_uneven_inputs_matches_torch():
     run_gloo(_w_join, 2)
+
+
+def _w_bucket_sweep(rank, world):
+    """Bucket-size sweep: whatever the bucket layout, the synchronised gradients are the same; a smaller
+    batch on one rank (uneven last batch) is averaged per rank exactly as torch does."""
+    from distributed_model_parallel_b200.parallel import DistributedDataParallel as DDP
+
+    torch.manual_seed(0)
+    base = nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.ReLU(), nn.Flatten(), nn.Linear(8 * 8 * 8, 32), nn.ReLU(), nn.Linear(32, 10))
+    torch.manual_seed(50 + rank)
+    n = 6 if rank == 0 else 3                                   # uneven per-rank batch
+    x, y = torch.randn(n, 3, 8, 8), torch.randint(0, 10, (n,))
+    ref = torch.nn.parallel.DistributedDataParallel(copy.deepcopy(base))
+    F.cross_entropy(ref(x), y).backward()
+    want = [p.grad.clone() for p in ref.module.parameters()]
+    layouts = set()
+    for cap_mb, first in ((25.0, 1 << 20), (0.01, 1 << 20), (0.001, 256), (0.0001, 64)):
+        m = DDP(copy.deepcopy(base), bucket_cap_mb=cap_mb, first_bucket_bytes=first)
+        for _ in range(2):                                      # the second pass runs on the rebuilt (ready-order) buckets
+            m.zero_grad(set_to_none=True)
+            F.cross_entropy(m(x), y).backward()
+            for p, g in zip(m.module.parameters(), want):
+                assert torch.allclose(p.grad, g, atol=1e-6, rtol=1e-5), (cap_mb, first)
+        layouts.add(len(m.reducer.buckets))
+    assert len(layouts) >= 3, layouts                            # the sweep really produced different bucket counts
+
+
+def test_ddp_bucket_size_sweep_and_uneven_batches():
+    run_gloo(_w_bucket_sweep, 2)
