@@ -186,3 +186,51 @@ def _w_bucket_sweep(rank, world):
 
 def test_ddp_bucket_size_sweep_and_uneven_batches():
     run_gloo(_w_bucket_sweep, 2)
+
+
+def _tiny_cnn():
+    return nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.ReLU(), nn.Conv2d(8, 8, 3, padding=1, stride=2), nn.ReLU(), nn.Flatten(),
+                         nn.Linear(8 * 4 * 4, 10))
+
+
+def _w_loss_curves(rank, world):
+    """Loss-curve parity (SURVEY section 4 / the reference's de-facto integration test, Readme.md:283-294, at unit-test scale):
+    20 SGD steps of the same model on the same global batches, (a) single process on the full batch, (b) our single-process
+    DataParallel over two replicas, (c) our DistributedDataParallel over two ranks with the batch split -- the three loss
+    curves coincide."""
+    from distributed_model_parallel_b200.parallel import DataParallel
+    from distributed_model_parallel_b200.parallel import DistributedDataParallel as DDP
+
+    torch.manual_seed(0)
+    base = _tiny_cnn()
+    single, dp_m, ddp_m = copy.deepcopy(base), copy.deepcopy(base), copy.deepcopy(base)
+    dp = DataParallel(dp_m, device_ids=[torch.device("cpu"), torch.device("cpu")])
+    ddp = DDP(ddp_m, bucket_cap_mb=0.001, first_bucket_bytes=256)
+    opts = [torch.optim.SGD(m.parameters(), lr=0.05, momentum=0.9) for m in (single, dp, ddp)]
+    curves = [[], [], []]
+    half = 4
+    for step in range(20):
+        torch.manual_seed(1000 + step)                          # the same global batch on every rank
+        x, y = torch.randn(2 * half, 3, 8, 8), torch.randint(0, 10, (2 * half,))
+        for i, (m, o) in enumerate(zip((single, dp, ddp), opts)):
+            o.zero_grad()
+            if i == 2:
+                xs, ys = x[rank * half: (rank + 1) * half], y[rank * half: (rank + 1) * half]
+                loss = F.cross_entropy(m(xs), ys)
+                loss.backward()
+                t = loss.detach().clone()
+                dist.all_reduce(t)
+                curves[i].append(float(t) / world)              # mean of the per-rank means = full-batch mean (equal halves)
+            else:
+                loss = F.cross_entropy(m(x), y)
+                loss.backward()
+                curves[i].append(float(loss))
+            o.step()
+    a, b, c = (torch.tensor(v) for v in curves)
+    assert torch.allclose(a, b, atol=1e-5), (a - b).abs().max()
+    assert torch.allclose(a, c, atol=1e-5), (a - c).abs().max()
+    assert a[-1] < a[0]                                          # and it did learn something
+
+
+def test_loss_curves_single_vs_dataparallel_vs_ddp():
+    run_gloo(_w_loss_curves, 2)

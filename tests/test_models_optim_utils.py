@@ -191,3 +191,19 @@ def test_tracing_ranges_record_framework_phases():
     finally:
         tracing.enable(False)
         tracing.events.clear()
+
+
+def test_public_surface_is_importable_from_the_package_root():
+    """What a user of torch.nn.DataParallel / DistributedDataParallel (the reference's imports, data_parallel.py:74,
+    Readme.md:7-157) reaches for, from the package root and from ``parallel``."""
+    import distributed_model_parallel_b200 as d
+    from distributed_model_parallel_b200 import parallel as P
+
+    for name in ("DataParallel", "data_parallel", "DistributedDataParallel", "SyncBatchNorm", "convert_sync_batchnorm", "FusedSGD",
+                 "FlatFusedSGD", "LinearWarmup", "TrainStep"):
+        assert getattr(d, name) is not None, name
+    for name in ("scatter", "scatter_kwargs", "gather", "replicate", "parallel_apply", "Reducer", "comm"):
+        assert hasattr(P, name), name
+    assert d.pipeline.PipelineStage is not None and d.DataParallel is P.DataParallel
+    with pytest.raises(AttributeError):
+        d.no_such_thing
