@@ -365,6 +365,26 @@ class DistributedDataParallel(nn.Module):
         if hasattr(self.backend, "check_health"):
             self.backend.check_health()
 
+    def start_watchdog(self, interval_s: float = 5.0, on_fault=None):
+        """Background thread that reads the communicator status word every ``interval_s`` seconds (on its own CUDA stream) and
+        reports a timed-out peer through ``on_fault`` (default: print and exit 70).  Returns the ``CommWatchdog``; call
+        ``.stop()`` on it when training ends.  A no-op probe with the torch/gloo back end, which has its own timeouts."""
+        from .watchdog import CommWatchdog
+
+        backend = self.backend
+        stream = None
+
+        def probe():
+            nonlocal stream
+            if not hasattr(backend, "check_health") or getattr(backend, "state", None) is None:
+                return
+            if stream is None:
+                stream = torch.cuda.Stream(device=backend.device)
+            with torch.cuda.device(backend.device), torch.cuda.stream(stream):
+                backend.check_health()
+
+        return CommWatchdog(probe, interval_s, on_fault).start()
+
     def load_state_dict(self, state_dict, strict: bool = True, assign: bool = False):
         r = super().load_state_dict(state_dict, strict=strict)
         self.reducer.sync_shadow()

@@ -77,3 +77,29 @@ def test_reducer_launches_every_bucket_exactly_once_in_order(n, nb, rnd):
         launched += r.mark_ready(p, unused=rnd.random() < 0.2)
     assert launched == list(range(nb))
     assert r.finalize() == [] and r.num_launched() == nb
+
+
+def test_comm_watchdog_polls_reports_once_and_stops():
+    """Host watchdog: polls the probe, hands the first fault to the callback, then ends; stop() ends a healthy one."""
+    import time
+
+    from distributed_model_parallel_b200.parallel.watchdog import CommWatchdog
+
+    calls, faults = [], []
+
+    def probe():
+        calls.append(1)
+        if len(calls) == 3:
+            raise RuntimeError("peer collective timed out waiting for rank 1")
+
+    wd = CommWatchdog(probe, interval_s=0.02, on_fault=faults.append).start()
+    t0 = time.time()
+    while not faults and time.time() - t0 < 5:
+        time.sleep(0.01)
+    time.sleep(0.1)
+    assert len(faults) == 1 and "rank 1" in str(faults[0]) and wd.fault is faults[0]
+    assert len(calls) == 3 and wd.polls == 2                      # it stopped probing after the fault
+    healthy = CommWatchdog(lambda: None, interval_s=0.01, on_fault=faults.append)
+    with healthy:
+        time.sleep(0.1)
+    assert healthy.polls >= 2 and healthy.fault is None and not healthy._thread.is_alive()
