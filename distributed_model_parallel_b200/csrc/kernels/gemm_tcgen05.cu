@@ -48,15 +48,24 @@ constexpr int gemm_stages(int b_rows, bool stats) {
     return s > 8 ? 8 : s;
 }
 
-template <int BN, bool A_MN, bool B_MN, bool STATS>
+// BRES ("resident B"): NT forward GEMMs whose whole B panel [BN x K] fits a fixed shared-memory region load it ONCE per CTA
+// (every tile of a CTA shares one n0: the host makes the grid a multiple of n_tiles) and the ring carries A only.  The kernel is
+// bound by TMA load issue (profiles/ncu_gemm_fwd_tma_store_r1.txt), and re-fetching the 16 KB panel for every 128-row tile
+// was half of that traffic.
+constexpr int bres_bytes(int bn) { return bn >= 128 ? 64 * 1024 : 32 * 1024; }   // region for ceil(K/64) blocks of BN x 64 bf16
+constexpr int bres_stages(int bn) { return bn >= 128 ? 6 : 3; }                  // A-only ring (16 KB per stage)
+
+template <int BN, bool A_MN, bool B_MN, bool STATS, bool BRES = false>
 __global__ void __launch_bounds__(NUM_THREADS, BN <= 64 ? 2 : 1)  // narrow tiles keep two CTAs per SM (<= 168 registers)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;  // 16 KB
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int B_BYTES = B_ROWS * BK * 2;
-    constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    constexpr int STAGES = gemm_stages(B_ROWS, STATS);  // shadows the common 3-stage default: see gemm_stages()
+    static_assert(!BRES || (!A_MN && !B_MN && !STATS), "resident B is for the plain NT forward GEMM");
+    constexpr int STAGE_BYTES = BRES ? A_BYTES : A_BYTES + B_BYTES;
+    constexpr int STAGES = BRES ? bres_stages(BN) : gemm_stages(B_ROWS, STATS);  // shadows the common 3-stage default
+    constexpr int RES_BYTES = BRES ? bres_bytes(BN) : 0;
     constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;  // double-buffered accumulator (power of two: 64/128/256)
 
@@ -67,12 +76,14 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int PW = BN >= 64 ? 64 : BN;
     constexpr int STG_PITCH = BN * 2 + 16;                 // mode 2: padded rows, conflict-free both ways
     constexpr int STG_WARP_BYTES = (32 * STG_PITCH + 1023) / 1024 * 1024;  // >= the 32 * BN * 2 the TMA layout needs, 1 KB aligned
-    uint8_t* stg = smem + STAGES * STAGE_BYTES;
+    uint8_t* bres = smem + STAGES * STAGE_BYTES;             // BRES: the CTA's B panel, K block kb at bres + kb * B_BYTES
+    uint8_t* stg = bres + RES_BYTES;
     uint64_t* full_bar = (uint64_t*)(stg + 4 * STG_WARP_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
-    uint32_t* tmem_ptr_smem = (uint32_t*)(tmem_empty_bar + 2);
+    uint64_t* bres_bar = tmem_empty_bar + 2;        // BRES: the panel has landed
+    uint32_t* tmem_ptr_smem = (uint32_t*)(bres_bar + 1);
     float* stat_smem = (float*)(stg + 4 * STG_WARP_BYTES + 256);  // STATS only (the launch adds STAT_SMEM_BYTES)
 
     const int warp = threadIdx.x >> 5;
@@ -93,6 +104,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_init(&tmem_full_bar[b], 1);
             mbar_init(&tmem_empty_bar[b], 4);  // one arrive per epilogue warp
         }
+        mbar_init(bres_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr_smem, TMEM_COLS);
@@ -105,6 +117,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         // ------------------------------------------------------------------ TMA producer
         if (lane == 0) {
             int it = 0;  // global k-block counter -> smem ring position
+            if (BRES && blockIdx.x < num_items) {
+                const int n0c = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;  // the same for every tile of this CTA
+                mbar_expect_tx(bres_bar, (uint32_t)(total_kb * B_BYTES));
+                for (int kb = 0; kb < total_kb; ++kb) tma_load_2d(bres + kb * B_BYTES, &tmB, bres_bar, kb * BK, n0c);
+            }
             for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
                 const int split = item / tiles_mn, tile = item % tiles_mn;
                 const int m0 = (tile / p.n_tiles) * BM, n0 = (tile % p.n_tiles) * BN;
@@ -122,6 +139,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     // the TMA unit would still spend a full box of issue slots on it, and these GEMMs are bound by exactly that
                     // (Cout <= 64 halves the weight-gradient's A traffic).  The MMA then reads stale shared memory for those
                     // rows/columns; accumulator rows and columns are independent and the epilogue masks everything >= M, N.
+                    if (BRES) {  // the ring carries A only
+                        mbar_expect_tx(&full_bar[s], A_BYTES);
+                        tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+                        continue;
+                    }
                     constexpr int BOX_BYTES = 64 * BK * 2;
                     uint32_t tx = STAGE_BYTES;
                     const bool a_hi = !A_MN || (m0 + 64 < p.M);
@@ -153,6 +175,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (lane == 0) {
             constexpr uint32_t idesc = make_idesc(BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
             int it = 0, local = 0;
+            if (BRES && blockIdx.x < num_items) {
+                mbar_wait(bres_bar, 0);  // the resident B panel is in shared memory
+                tcgen05_fence_after();
+            }
             for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
                 const int split = item / tiles_mn;
                 const int kb_begin = split * p.k_blocks_per_split;
@@ -169,7 +195,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     mbar_wait(&full_bar[s], ph);
                     tcgen05_fence_after();
                     const uint32_t sa = smem_u32(smem + s * STAGE_BYTES);
-                    const uint32_t sb = sa + A_BYTES;
+                    const uint32_t sb = BRES ? smem_u32(bres + kb * B_BYTES) : sa + A_BYTES;
                     const int k0 = kb * BK;
                     int ksteps = (p.K - k0 + 15) / 16;  // skip the zero-filled K tail
                     if (ksteps > BK / 16) ksteps = BK / 16;
@@ -394,12 +420,14 @@ const int g_gemm_store_mode = [] {
     return (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
 }();
 
-template <int BN, bool A_MN, bool B_MN, bool STATS = false>
+template <int BN, bool A_MN, bool B_MN, bool STATS = false, bool BRES = false>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
-    constexpr int smem_bytes = gemm_stages(B_ROWS, STATS) * (BM * BK * 2 + B_ROWS * BK * 2) + 1024 /*align slack*/ +
-                               4 * stg_warp_bytes(BN) /*output staging*/ + 256 /*barriers*/ + (STATS ? STAT_SMEM_BYTES : 0);
-    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, STATS>;
+    constexpr int ring_bytes = BRES ? bres_stages(BN) * (BM * BK * 2) + bres_bytes(BN)
+                                    : gemm_stages(B_ROWS, STATS) * (BM * BK * 2 + B_ROWS * BK * 2);
+    constexpr int smem_bytes = ring_bytes + 1024 /*align slack*/ + 4 * stg_warp_bytes(BN) /*output staging*/ + 256 /*barriers*/ +
+                               (STATS ? STAT_SMEM_BYTES : 0);
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, STATS, BRES>;
     static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
     static int configured_dev_mask = 0;
     int dev = 0;
@@ -429,7 +457,7 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     const int ctas_per_sm = smem_bytes <= 110 * 1024 ? 2 : 1;
     long long grid = (long long)dmp_num_sms() * ctas_per_sm;
     if (grid > items) grid = items;
-    if (STATS) {  // every tile of a CTA must have the same n0: the item stride has to be a multiple of n_tiles
+    if (STATS || BRES) {  // every tile of a CTA must have the same n0: the item stride has to be a multiple of n_tiles
         DMP_REQUIRE(splits == 1 && q.n_tiles <= grid, "gemm statistics epilogue: %d column tiles do not fit the grid", q.n_tiles);
         grid = grid / q.n_tiles * q.n_tiles;
     }
@@ -488,7 +516,19 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
     splits = dmp_ceil_div(total_kb, p.k_blocks_per_split);  // no empty splits
     p.D = D; p.ldd = ldd; p.bias = bias; p.epi = out_mode; p.stats = nullptr;
 
-    if (!a_mn && !b_mn) return dispatch_bn<false, false>(bn, tmA, tmB, p, splits, stream);
+    if (!a_mn && !b_mn) {
+        // resident-B variant: whole [bn x K] panel in shared memory, loaded once per CTA (DMP_GEMM_BRES=0 disables).  Measured:
+        // 131072x144x24 36.7 -> 24.1 us, 131072x128x64 17.1 -> 13.2 us, 32768x192x32 11.2 -> 9.3 us (bench/gemm_sweep.py).
+        static const bool use_bres = [] { const char* e = getenv("DMP_GEMM_BRES"); return e == nullptr || e[0] != '0'; }();
+        if (use_bres && splits == 1 && (long long)total_kb * bn * BK * 2 <= bres_bytes(bn) && dmp_ceil_div(N, bn) <= dmp_num_sms()) {
+            switch (bn) {
+                case 32: return launch_gemm<32, false, false, false, true>(tmA, tmB, p, 1, stream);
+                case 64: return launch_gemm<64, false, false, false, true>(tmA, tmB, p, 1, stream);
+                default: return launch_gemm<128, false, false, false, true>(tmA, tmB, p, 1, stream);
+            }
+        }
+        return dispatch_bn<false, false>(bn, tmA, tmB, p, splits, stream);
+    }
     if (!a_mn && b_mn) return dispatch_bn<false, true>(bn, tmA, tmB, p, splits, stream);
     return dispatch_bn<true, true>(bn, tmA, tmB, p, splits, stream);
 }
