@@ -1,23 +1,27 @@
 #!/usr/bin/env python
-"""Headline benchmark: training throughput (images/s) of MobileNetV2 on CIFAR-10-shaped synthetic data,
-per-GPU batch 128 (global 128*N: the reference's published 256 @ 2 GPUs / 512 @ 4 GPUs configs, weak scaling).
+"""Headline benchmark: training throughput (images/s) on synthetic data of the named shape.
 
     python bench.py --gpus N --steps K --warmup W                   # this framework
-    python bench.py --impl reference --gpus N --steps K --warmup W  # unmodified reference model + torch DP/DDP
+    python bench.py --impl reference --gpus N --steps K --warmup W  # unmodified reference (baseline/reference_arm.py)
+
+Default config: MobileNetV2 on CIFAR-10-shaped data (what the reference trains), per-GPU batch 128 (global 128*N: the
+reference's published 256 @ 2 GPUs / 512 @ 4 GPUs, weak scaling), DistributedDataParallel.  Other configs of BASELINE.json:
+
+    --model {mobilenetv2,resnet18,resnet50,vgg16}  --batch-per-gpu B  --sync-bn
+    --parallelism ddp   multi-process DistributedDataParallel: peer-memory all-reduce fused with SGD, CUDA-graph step (default)
+    --parallelism dp    single-process DataParallel (rank 0 drives all N GPUs, thread per replica) -- the comparison point
+    --parallelism mp    layer-split pipeline over N stages with micro-batches (strong scaling: --global-batch 512)
 
 For N > 1 launch with ``python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1
---master-port P bench.py --gpus N ...`` (one rank per GPU).  Rank 0 prints ONE JSON line.
-
-ours:       DistributedDataParallel (peer-memory all-reduce fused with SGD) around the sm_100a kernel model,
-            whole step replayed from a CUDA graph; bf16 compute, fp32 master weights.
-reference:  the reference's own ``model.MobileNetV2`` (from baseline/_ref, unmodified) trained exactly like its
-            data_parallel.py does: torch.nn.DataParallel over N GPUs driven by rank 0, CrossEntropyLoss,
-            SGD(momentum 0.9, wd 1e-4), cudnn.benchmark, fp32.  torch DistributedDataParallel (NCCL) on the same
-            model is measured too and reported as ``torch_ddp_value``.
+--master-port P bench.py --gpus N ...`` (one rank per GPU).  Rank 0 prints ONE JSON line.  With N > 1 the default (ddp)
+line also carries ``dp_value`` (our DataParallel on the same N GPUs), ``allreduce_busGBs`` (largest gradient bucket,
+device-timed fused all-reduce+SGD kernel, NCCL bus-bandwidth convention) and ``roofline_frac`` (that kernel against the
+NVLink floor 2(W-1)/W * bytes / 900 GB/s).
 """
 from __future__ import annotations
 
 import argparse
+import contextlib
 import json
 import os
 import statistics
@@ -25,11 +29,14 @@ import subprocess
 import sys
 import threading
 import time
+import types
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 PUBLISHED = {2: 705.0, 4: 1293.0}  # nn.DataParallel img/s derived from /root/reference/Readme.md:283-292
+PUBLISHED_MP = {2: 332.0, 4: 317.0}
+NVLINK_GBS = 900.0                 # per direction per GPU (NVLink 5 through NVSwitch)
 
 
 def parse():
@@ -39,10 +46,15 @@ def parse():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--model", default="mobilenetv2")
+    ap.add_argument("--parallelism", default="ddp", choices=["ddp", "dp", "mp"])
     ap.add_argument("--batch-per-gpu", type=int, default=128)
+    ap.add_argument("--global-batch", type=int, default=0, help="mp only (default 512, the reference's)")
+    ap.add_argument("--microbatches", type=int, default=4)
+    ap.add_argument("--schedule", default="1f1b", choices=["naive", "gpipe", "1f1b"])
+    ap.add_argument("--sync-bn", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip dp_value / allreduce_busGBs on the ddp line")
     ap.add_argument("--comm", default="peer", choices=["peer", "torch"])
-    ap.add_argument("--ref-dtype", default="fp32", choices=["fp32", "bf16"])
     ap.add_argument("--lr", type=float, default=0.1)
     return ap.parse_args()
 
@@ -129,6 +141,10 @@ def max_over_ranks(value: float, world: int) -> float:
     return float(t.item())
 
 
+TOOLS = types.SimpleNamespace(setup_dist=setup_dist, barrier_sync=barrier_sync, max_over_ranks=max_over_ranks,
+                              ClockSampler=ClockSampler)
+
+
 def input_shape(model_name):
     return (3, 224, 224) if model_name == "resnet50" else (3, 32, 32)
 
@@ -137,7 +153,91 @@ def num_classes(model_name):
     return 1000 if model_name == "resnet50" else 10
 
 
+L2_NOTE = "per-step activation working set (>1 GB) exceeds the 126 MB L2; inputs rotate over %d batches"
+
+
+def timed_steps(step, batches, n, world, local, read_stats=False, sample=True):
+    """Device-timed loop (CUDA events, barrier + synchronize on both sides, max over ranks).  Returns ms/step, clocks."""
+    import torch
+
+    barrier_sync(world)
+    sampler = ClockSampler(local) if sample else None
+    if sampler:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    e0.record()
+    stats = None
+    for i in range(n):
+        step(*batches[i % len(batches)])
+        if read_stats:
+            stats = step.read_stats()
+    e1.record()
+    barrier_sync(world)
+    wall = (time.perf_counter() - t0) / n * 1e3
+    ms = max_over_ranks(e0.elapsed_time(e1), world) / n
+    return ms, (sampler.stop() if sampler else None), wall, stats
+
+
 # ---------------------------------------------------------------------------------------------------------
+def measure_largest_bucket(model, world, iters=20):
+    """Device-timed launches of the fused all-reduce(+SGD) kernel on the largest gradient bucket, all ranks in lock-step on
+    the communication stream.  Returns (bytes, ms per launch max over ranks, bus GB/s, fraction of the NVLink floor)."""
+    import torch
+
+    red = getattr(model, "reducer", None)
+    if red is None or world < 2 or not hasattr(red.backend, "stream"):
+        return None
+    bk = max(red.buckets, key=lambda b: b.nbytes())
+    be = red.backend
+    for _ in range(3):
+        be.launch(bk)
+    be.end_iteration()
+    barrier_sync(world)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(be.stream):
+        e0.record()
+    for _ in range(iters):
+        be.launch(bk)
+    with torch.cuda.stream(be.stream):
+        e1.record()
+    be.end_iteration()
+    barrier_sync(world)
+    ms = max_over_ranks(e0.elapsed_time(e1), world) / iters
+    nbytes = bk.nbytes()
+    bus = nbytes / (ms * 1e-3) * 2 * (world - 1) / world / 1e9
+    return {"bucket_bytes": nbytes, "n_buckets": len(red.buckets), "bucket_sizes": red.bucket_sizes(), "ms": ms,
+            "busGBs": bus, "roofline_frac": bus / NVLINK_GBS}
+
+
+def measure_dataparallel(args, world, steps, warmup):
+    """Our single-process DataParallel over the same N GPUs (rank 0's process drives all of them), same model and batch."""
+    import torch
+    from distributed_model_parallel_b200.data import pinned_batches
+    from distributed_model_parallel_b200.models import build_model
+    from distributed_model_parallel_b200.optim import FlatFusedSGD
+    from distributed_model_parallel_b200.parallel import DataParallel
+    from distributed_model_parallel_b200.train.engine import TrainStep
+
+    gb = args.batch_per_gpu * world
+    torch.manual_seed(1234)
+    dev = torch.device("cuda", 0)
+    with torch.cuda.device(dev):
+        net = build_model(args.model, num_classes=num_classes(args.model)).to(dev)
+        dp = DataParallel(net, device_ids=list(range(world))) if world > 1 else net
+        opt = FlatFusedSGD(net.parameters(), lr=args.lr, momentum=0.9, weight_decay=1e-4)
+        step = TrainStep(dp, opt, use_graph=(world == 1 and not args.no_graph))
+        host = pinned_batches(4, gb, input_shape(args.model), num_classes(args.model), seed=0)
+        devb = [(x.to(dev), y.to(dev)) for x, y in host]
+        for i in range(max(warmup, 3)):
+            step(*devb[i % 4])
+        ms, clocks, _, _ = timed_steps(step, devb, steps, 1, 0, sample=False)
+        for i in range(2):
+            step(*host[i % 4]); step.read_stats()
+        ms_e2e, _, _, _ = timed_steps(step, host, steps, 1, 0, read_stats=True, sample=False)
+    return {"value": gb / ms * 1e3, "ms_per_step": ms, "e2e_value": gb / ms_e2e * 1e3, "launches_per_step": step.launches_per_iteration}
+
+
 def run_ours(args):
     import torch
     from distributed_model_parallel_b200 import _native
@@ -150,76 +250,103 @@ def run_ours(args):
 
     world, rank, local = setup_dist(args)
     dev = torch.device("cuda", local)
-    torch.manual_seed(1234)
     B = args.batch_per_gpu
-    model = build_model(args.model, num_classes=num_classes(args.model)).to(dev)
-    sgd = dict(lr=args.lr, momentum=0.9, weight_decay=1e-4)
-    if world > 1:
-        model = DistributedDataParallel(model, device_ids=[local], comm_backend=args.comm,
-                                        fused_sgd=sgd if args.comm == "peer" else None)
-        opt = model.optimizer if args.comm == "peer" else FlatFusedSGD(model.parameters(), **sgd)
-    else:
-        opt = FlatFusedSGD(model.parameters(), **sgd)
-    step = TrainStep(model, opt, use_graph=not args.no_graph)
-
-    n_batches = 8
-    host = pinned_batches(n_batches, B, input_shape(args.model), num_classes(args.model), seed=rank)
-    devb = [(x.to(dev), y.to(dev)) for x, y in host]
-    _native.kernels().dmp_reset_launch_count()
-    step(*devb[0])  # builds static buffers, warm-up iterations, graph capture
-    torch.cuda.synchronize()
-    launches_per_step = step.launches_per_iteration  # our kernels per iteration (what each graph replay re-issues)
-
-    for i in range(args.warmup):
-        step(*devb[i % n_batches])
-    # ---- kernel-only: inputs already on the device
-    barrier_sync(world)
-    sampler = ClockSampler(local)
-    sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for i in range(args.steps):
-        step(*devb[i % n_batches])
-    e1.record()
-    barrier_sync(world)
-    ms = max_over_ranks(e0.elapsed_time(e1), world) / args.steps
-    clocks = sampler.stop()
-    # ---- end to end: pinned host batch -> device every step, loss/accuracy read back every step
-    for i in range(2):
-        step(*host[i % n_batches]); step.read_stats()
-    barrier_sync(world)
-    t0 = time.perf_counter()
-    e0.record()
-    for i in range(args.steps):
-        step(*host[i % n_batches])
-        stats = step.read_stats()
-    e1.record()
-    barrier_sync(world)
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1), world) / args.steps
-    wall_e2e = (time.perf_counter() - t0) / args.steps * 1e3
-    if hasattr(model, "check_health"):
-        model.check_health()
-    x0, y0 = host[0]
     gb = B * world
-    res = {
-        "metric": "images/sec (device-timed, max over ranks)", "impl": "ours",
-        "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": (gb / ms * 1e3) / PUBLISHED[world] if world in PUBLISHED else None,
-        "dtype": "bf16", "data": "synthetic",
-        "config": {"model": args.model, "global_batch": gb, "per_gpu_batch": B, "image": list(input_shape(args.model)),
-                   "parallelism": "ddp%d" % world if world > 1 else "single", "optimizer": "sgd(m=0.9,wd=1e-4) fused",
-                   "comm": args.comm if world > 1 else "none", "cuda_graph": step.graph is not None,
-                   "l2": "per-step activation working set (>1 GB) exceeds the 126 MB L2; inputs rotate over %d batches" % n_batches},
-        "clocks": clocks,
-        "e2e": {"value": gb / ms_e2e * 1e3, "unit": "images/s", "ms_per_step": ms_e2e, "wall_ms_per_step": wall_e2e,
-                "h2d_bytes_per_step": x0.numel() * x0.element_size() + y0.numel() * y0.element_size(),
-                "d2h_bytes_per_step": 12},
-        "gpu_launches": int(launches_per_step) * args.steps,
-        "launches_per_step": int(launches_per_step),
-        "op_paths": dict(OF.path_counts),
-        "final_loss": stats[0],
-    }
+    n_batches = 8
+    dp_only = args.parallelism == "dp"
+    res = None
+    if not dp_only:
+        torch.manual_seed(1234)
+        model = build_model(args.model, num_classes=num_classes(args.model)).to(dev)
+        if args.sync_bn and world > 1:
+            from distributed_model_parallel_b200.parallel import SyncBatchNorm
+            model = SyncBatchNorm.convert_sync_batchnorm(model)
+        sgd = dict(lr=args.lr, momentum=0.9, weight_decay=1e-4)
+        if world > 1:
+            model = DistributedDataParallel(model, device_ids=[local], comm_backend=args.comm,
+                                            fused_sgd=sgd if args.comm == "peer" else None)
+            opt = model.optimizer if args.comm == "peer" else FlatFusedSGD(model.parameters(), **sgd)
+        else:
+            opt = FlatFusedSGD(model.parameters(), **sgd)
+        step = TrainStep(model, opt, use_graph=not args.no_graph)
+
+        host = pinned_batches(n_batches, B, input_shape(args.model), num_classes(args.model), seed=rank)
+        devb = [(x.to(dev), y.to(dev)) for x, y in host]
+        _native.kernels().dmp_reset_launch_count()
+        step(*devb[0])  # builds static buffers, warm-up iterations, graph capture
+        torch.cuda.synchronize()
+        launches_per_step = step.launches_per_iteration  # our kernels per iteration (what each graph replay re-issues)
+        for i in range(args.warmup):
+            step(*devb[i % n_batches])
+        # ---- kernel-only: inputs already on the device
+        ms, clocks, _, _ = timed_steps(step, devb, args.steps, world, local)
+        # ---- end to end: pinned host batch -> device every step, loss/accuracy read back every step
+        for i in range(2):
+            step(*host[i % n_batches]); step.read_stats()
+        ms_e2e, _, wall_e2e, stats = timed_steps(step, host, args.steps, world, local, read_stats=True, sample=False)
+        if hasattr(model, "check_health"):
+            model.check_health()
+        x0, y0 = host[0]
+        res = {
+            "metric": "images/sec (device-timed, max over ranks)", "impl": "ours",
+            "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": (gb / ms * 1e3) / PUBLISHED[world] if (world in PUBLISHED and args.model == "mobilenetv2") else None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"model": args.model, "global_batch": gb, "per_gpu_batch": B, "image": list(input_shape(args.model)),
+                       "parallelism": "ddp%d" % world if world > 1 else "single", "optimizer": "sgd(m=0.9,wd=1e-4) fused",
+                       "sync_bn": bool(args.sync_bn and world > 1),
+                       "comm": args.comm if world > 1 else "none", "cuda_graph": step.graph is not None,
+                       "l2": L2_NOTE % n_batches},
+            "clocks": clocks,
+            "e2e": {"value": gb / ms_e2e * 1e3, "unit": "images/s", "ms_per_step": ms_e2e, "wall_ms_per_step": wall_e2e,
+                    "h2d_bytes_per_step": x0.numel() * x0.element_size() + y0.numel() * y0.element_size(),
+                    "d2h_bytes_per_step": 12},
+            "gpu_launches": int(launches_per_step) * args.steps,
+            "launches_per_step": int(launches_per_step),
+            "op_paths": dict(OF.path_counts),
+            "final_loss": stats[0],
+        }
+        if world > 1 and not args.no_extras and args.comm == "peer":
+            try:
+                ar = measure_largest_bucket(model, world)
+                if ar is not None:
+                    res["allreduce_busGBs"] = ar["busGBs"]
+                    res["roofline_frac"] = ar["roofline_frac"]
+                    res["allreduce"] = ar
+            except Exception as e:  # noqa: BLE001
+                res["allreduce_error"] = repr(e)[:300]
+    # ---- our DataParallel on the same GPUs (single process: rank 0 drives, the others wait on a CPU barrier)
+    if dp_only or (world > 1 and not args.no_extras):
+        import torch.distributed as dist
+        ctrl = dist.new_group(backend="gloo") if world > 1 else None
+        barrier_sync(world)
+        dpres = None
+        if rank == 0:
+            try:
+                dpres = measure_dataparallel(args, world, args.steps if dp_only else max(5, min(args.steps, 20)), args.warmup)
+            except Exception as e:  # noqa: BLE001
+                dpres = {"error": repr(e)[:400]}
+        if ctrl is not None:
+            torch.cuda.synchronize()
+            dist.barrier(group=ctrl)
+        if rank == 0:
+            if dp_only:
+                ok = "value" in dpres
+                res = {"metric": "images/sec (device-timed, max over ranks)", "impl": "ours",
+                       "value": dpres.get("value"), "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                       "ms_per_step": dpres.get("ms_per_step"), "higher_is_better": True, "scaling": "weak",
+                       "vs_baseline": dpres["value"] / PUBLISHED[world] if ok and world in PUBLISHED and args.model == "mobilenetv2" else None,
+                       "dtype": "bf16", "data": "synthetic",
+                       "config": {"model": args.model, "global_batch": gb, "per_gpu_batch": B, "image": list(input_shape(args.model)),
+                                  "parallelism": "dp%d (single process, thread per replica)" % world, "l2": L2_NOTE % 4},
+                       "e2e": {"value": dpres.get("e2e_value"), "unit": "images/s",
+                               "h2d_bytes_per_step": gb * (4 * 3 * input_shape(args.model)[1] * input_shape(args.model)[2] + 8),
+                               "d2h_bytes_per_step": 12},
+                       "gpu_launches": int(dpres.get("launches_per_step", 0)) * args.steps, "error": dpres.get("error")}
+            else:
+                res["dp_value"] = dpres.get("value")
+                res["dp"] = dpres
     if rank == 0:
         print(json.dumps(res))
     if world > 1:
@@ -228,154 +355,83 @@ def run_ours(args):
 
 
 # ---------------------------------------------------------------------------------------------------------
-def run_reference(args):
-    ref_dir = os.path.join(ROOT, "baseline", "_ref")
-    if not os.path.isdir(os.path.join(ref_dir, "model")):
-        try:
-            subprocess.run(["bash", os.path.join(ROOT, "baseline", "install_reference.sh")], check=True, capture_output=True,
-                           timeout=300)
-        except Exception as e:  # noqa: BLE001
-            print(json.dumps({"impl": "reference", "unavailable": "reference install failed: %s" % str(e)[:120]}))
-            return
-    sys.path.insert(0, ref_dir)
+def run_ours_mp(args):
+    """Layer-split pipeline (one stage per GPU) with micro-batches: strong scaling, global batch 512 like the reference's
+    model_parallel.py:92.  Every step stage 0 copies the batch from pinned host memory and the loss is read back from the
+    stage that owns it, so the device-timed number is already end to end."""
     import torch
-    import torch.nn as nn
-    import torch.backends.cudnn as cudnn
-    try:
-        from model import MobileNetV2 as RefMobileNetV2  # the reference's own, unmodified, model file
-    except Exception as e:  # noqa: BLE001
-        print(json.dumps({"impl": "reference", "unavailable": "cannot import reference model: %s" % str(e)[:120]}))
-        return
-    if args.model != "mobilenetv2":
-        print(json.dumps({"impl": "reference", "unavailable": "the reference only ships MobileNetV2 (no %s)" % args.model}))
-        return
+    import torch.distributed as dist
+    from distributed_model_parallel_b200 import _native
+    from distributed_model_parallel_b200.data import pinned_batches
+    from distributed_model_parallel_b200.models import build_model
+    from distributed_model_parallel_b200.ops import functional as OF
+    from distributed_model_parallel_b200.optim import FlatFusedSGD
+    from distributed_model_parallel_b200.parallel.pipeline import PipelineStage, layer_costs, reference_split, split_sequential
 
     world, rank, local = setup_dist(args)
-    import torch.distributed as dist
-    B = args.batch_per_gpu
-    gb = B * world
-    cudnn.benchmark = True  # data_parallel.py:78
-    dtype_ctx = (lambda: torch.autocast("cuda", dtype=torch.bfloat16)) if args.ref_dtype == "bf16" else None
-
-    def make_batches(n, batch, device, seed):
-        g = torch.Generator().manual_seed(seed)
-        out = []
-        for _ in range(n):
-            x = torch.randn(batch, 3, 32, 32, generator=g).pin_memory()
-            y = torch.randint(0, 10, (batch,), generator=g).pin_memory()
-            out.append((x, y))
-        return out
-
-    def train_loop(net, optimizer, criterion, batches, steps, device, e2e):
-        """The body of the reference's train() (data_parallel.py:105-115)."""
-        total = correct = 0
-        for i in range(steps):
-            inputs, targets = batches[i % len(batches)]
-            inputs, targets = inputs.to(device), targets.to(device)
-            optimizer.zero_grad()
-            if dtype_ctx is not None:
-                with dtype_ctx():
-                    outputs = net(inputs)
-                    loss = criterion(outputs.float(), targets)
-            else:
-                outputs = net(inputs)
-                loss = criterion(outputs, targets)
-            loss.backward()
-            optimizer.step()
-            if e2e:
-                _ = loss.item()
-                _, predicted = outputs.max(1)
-                total += targets.size(0)
-                correct += predicted.eq(targets).sum().item()
-        return total
-
-    def timed(net, optimizer, criterion, host_batches, device, everyone):
-        dev_batches = [(x.to(device), y.to(device)) for x, y in host_batches]
-        train_loop(net, optimizer, criterion, dev_batches, max(args.warmup, 3), device, False)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        sampler = ClockSampler(local)
-        sampler.start()
-        e0.record()
-        train_loop(net, optimizer, criterion, dev_batches, args.steps, device, False)
-        e1.record()
-        torch.cuda.synchronize()
-        clocks = sampler.stop()
-        ms = e0.elapsed_time(e1) / args.steps
-        train_loop(net, optimizer, criterion, host_batches, 2, device, True)
-        torch.cuda.synchronize()
-        e0.record()
-        train_loop(net, optimizer, criterion, host_batches, args.steps, device, True)
-        e1.record()
-        torch.cuda.synchronize()
-        ms_e2e = e0.elapsed_time(e1) / args.steps
-        return ms, ms_e2e, clocks
-
+    dev = torch.device("cuda", local)
+    gb = args.global_batch or 512
     torch.manual_seed(1234)
-    dev0 = torch.device("cuda", local)
-    result = {}
-    # ---- (a) the reference's literal path: nn.DataParallel, single process (rank 0 drives all N GPUs).
-    # The other ranks wait on a CPU (gloo) barrier so that nothing of theirs runs on the GPUs rank 0 is using.
-    ctrl = dist.new_group(backend="gloo") if world > 1 else None
+    full = build_model(args.model, num_classes=num_classes(args.model))
+    if args.model == "mobilenetv2" and world == 4:
+        stages = reference_split(full, stem_relu=True)
+        split = "reference 3/6/6/2"
+    else:
+        seq = full.as_sequential()
+        stages = split_sequential(seq, world, layer_costs(seq, "params"))
+        split = "balanced"
+    module = stages[rank].to(dev)
+    params = list(module.parameters())
+    opt = FlatFusedSGD(params, lr=args.lr, momentum=0.9, weight_decay=1e-4) if params else None
+
+    def loss_fn(logits, target):
+        return OF.cross_entropy(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), target)
+
+    stage = PipelineStage(module, rank, world, optimizer=opt, loss_fn=loss_fn, schedule=args.schedule, loss_on="last", device=dev)
+    host = pinned_batches(8, gb, input_shape(args.model), num_classes(args.model), seed=0) if rank == 0 else None
+    loss_host = torch.zeros(1).pin_memory()
+
+    def one(i):
+        x, y = host[i % 8] if rank == 0 else (None, None)
+        loss = stage.train_step(x, y, args.microbatches)
+        if loss is not None:
+            loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        one(i)
+    c0 = _native.launch_count()
     barrier_sync(world)
-    if rank == 0:
-        host_batches = make_batches(8, gb, "cuda:0", 0)
-        variants = [True] if world == 1 else [True, False]
-        for bench_flag in variants:
-            # stock: cudnn.benchmark = True (data_parallel.py:78).  With N > 1 torch's DataParallel starts fresh replica
-            # threads every forward and cuDNN's autotune cache is per thread, so the stock setting re-tunes every
-            # convolution every step; the run with the flag off is reported next to it and the better one is `value`.
-            cudnn.benchmark = bench_flag
-            net = RefMobileNetV2().to("cuda:0")
-            net = torch.nn.DataParallel(net, device_ids=list(range(world)))
-            criterion = nn.CrossEntropyLoss()
-            optimizer = torch.optim.SGD(net.parameters(), lr=args.lr, momentum=0.9, weight_decay=1e-4)
-            ms, ms_e2e, clocks = timed(net, optimizer, criterion, host_batches, torch.device("cuda:0"), False)
-            result["dp_%s" % ("stock" if bench_flag else "nobench")] = (ms, ms_e2e, clocks)
-            del net, optimizer
-            torch.cuda.empty_cache()
-        cudnn.benchmark = True
-    if ctrl is not None:
-        torch.cuda.synchronize()
-        dist.barrier(group=ctrl)
+    sampler = ClockSampler(local)
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        one(i)
+    e1.record()
     barrier_sync(world)
-    # ---- (b) torch DistributedDataParallel + NCCL on the same reference model (stronger baseline)
-    ddp_ms = ddp_ms_e2e = None
+    ms = max_over_ranks(e0.elapsed_time(e1), world) / args.steps
+    clocks = sampler.stop()
+    launches = _native.launch_count() - c0
+    lv = torch.tensor([float(loss_host[0]) if rank == world - 1 else 0.0], device=dev)
     if world > 1:
-        net = RefMobileNetV2().to(dev0)
-        net = torch.nn.parallel.DistributedDataParallel(net, device_ids=[local])
-        criterion = nn.CrossEntropyLoss()
-        optimizer = torch.optim.SGD(net.parameters(), lr=args.lr, momentum=0.9, weight_decay=1e-4)
-        host_batches = make_batches(8, B, dev0, rank)
-        barrier_sync(world)
-        ms, ms_e2e, _ = timed(net, optimizer, criterion, host_batches, dev0, True)
-        ddp_ms = max_over_ranks(ms, world)
-        ddp_ms_e2e = max_over_ranks(ms_e2e, world)
+        dist.all_reduce(lv)
     if rank == 0:
-        best = min(result, key=lambda k: result[k][0])
-        ms, ms_e2e, clocks = result[best]
-        x_bytes = gb * 3 * 32 * 32 * 4 + gb * 8
-        out = {
-            "metric": "images/sec (device-timed, max over ranks)", "impl": "reference",
-            "value": gb / ms * 1e3, "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": (gb / ms * 1e3) / PUBLISHED[world] if world in PUBLISHED else None,
-            "dtype": args.ref_dtype, "data": "synthetic",
-            "config": {"model": "mobilenetv2 (reference model/mobilenetv2.py, unmodified)", "global_batch": gb, "per_gpu_batch": B,
-                       "image": [3, 32, 32], "parallelism": "torch.nn.DataParallel x%d (reference data_parallel.py path)" % world,
-                       "optimizer": "torch.optim.SGD(m=0.9,wd=1e-4)", "cudnn_benchmark": best == "dp_stock",
-                       "variant_used_for_value": best},
+        shape = input_shape(args.model)
+        print(json.dumps({
+            "metric": "images/sec (device-timed, max over ranks)", "impl": "ours", "value": gb / ms * 1e3, "unit": "images/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": (gb / ms * 1e3) / PUBLISHED_MP[world] if world in PUBLISHED_MP and args.model == "mobilenetv2" else None,
+            "dtype": "bf16", "data": "synthetic",
+            "config": {"model": args.model, "global_batch": gb, "image": list(shape), "split": split,
+                       "parallelism": "mp%d layer-split pipeline, %s x%d micro-batches, NCCL p2p" % (world, args.schedule, args.microbatches),
+                       "cuda_graph": bool(stage.use_graphs), "l2": L2_NOTE % 8},
             "clocks": clocks,
-            "e2e": {"value": gb / ms_e2e * 1e3, "unit": "images/s", "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_bytes,
-                    "d2h_bytes_per_step": 8},
-            "gpu_launches": 0,
-            "dataparallel_variants_images_per_s": {k: gb / v[0] * 1e3 for k, v in result.items()},
-        }
-        if ddp_ms is not None:
-            out["torch_ddp_value"] = gb / ddp_ms * 1e3
-            out["torch_ddp_ms_per_step"] = ddp_ms
-            out["torch_ddp_e2e_value"] = gb / ddp_ms_e2e * 1e3
-        print(json.dumps(out))
+            "e2e": {"value": gb / ms * 1e3, "unit": "images/s", "ms_per_step": ms,
+                    "h2d_bytes_per_step": gb * (4 * shape[0] * shape[1] * shape[2] + 8), "d2h_bytes_per_step": 4,
+                    "note": "the timed loop copies each batch from pinned host memory and reads the loss back: it is the end-to-end number"},
+            "gpu_launches": int(launches), "graph_replays_rank0": stage.stats["graph_replays"], "final_loss": float(lv[0]),
+        }))
     if world > 1:
         dist.destroy_process_group()
 
@@ -383,6 +439,30 @@ def run_reference(args):
 if __name__ == "__main__":
     a = parse()
     if a.impl == "reference":
-        run_reference(a)
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        import reference_arm
+        real_stdout = sys.stdout
+
+        class _Tee:
+            """The reference's own loops print progress lines (utils.py:69-70); anything that is not our JSON line goes to stderr."""
+            json_line = False
+
+            def write(self, s):
+                if s.lstrip().startswith('{"'):
+                    self.json_line = True
+                (real_stdout if self.json_line else sys.stderr).write(s)
+                if s.endswith("\n"):
+                    self.json_line = False
+
+            def flush(self):
+                real_stdout.flush(); sys.stderr.flush()
+
+        sys.stdout = _Tee()
+        try:
+            (reference_arm.run_mp if a.parallelism == "mp" else reference_arm.run_dp)(a, TOOLS)
+        finally:
+            sys.stdout = real_stdout
+    elif a.parallelism == "mp":
+        run_ours_mp(a)
     else:
         run_ours(a)

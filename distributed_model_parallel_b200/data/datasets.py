@@ -92,3 +92,11 @@ def prepare_dataloader(cfg, distributed: bool = False, rank: int = 0, world_size
     val_loader = DataLoader(val_ds, batch_size=cfg.val_batch_size, shuffle=False, num_workers=cfg.workers, pin_memory=pin,
                             persistent_workers=cfg.workers > 0)
     return sampler, train_loader, val_loader
+
+
+def sample_batch(cfg, batch: int) -> torch.Tensor:
+    """One random input batch of the shape ``cfg``'s model trains on (cost probing for the pipeline partitioner)."""
+    if cfg.model.startswith("bert"):
+        return torch.randint(0, 30522, (batch, 128))
+    hw = 224 if cfg.model == "resnet50" or cfg.dataset_type in ("Imagenet", "CUB200", "Place365") else 32
+    return torch.randn(batch, 3, hw, hw)

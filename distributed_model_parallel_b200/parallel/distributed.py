@@ -180,6 +180,23 @@ class DistributedDataParallel(nn.Module):
         # ---- reducer
         if comm_backend is None:
             comm_backend = "peer" if self.device_type == "cuda" else "torch"
+        if find_unused_parameters and fused_sgd is not None:
+            raise ValueError("find_unused_parameters=True cannot be combined with fused_sgd: the update runs inside the bucket "
+                             "kernels during backward, before it is known which parameters no rank used (their weight decay "
+                             "and momentum would still be applied); use comm_backend='peer' without fused_sgd")
+        self._ctor = dict(comm_backend=comm_backend, fused_sgd=dict(fused_sgd) if fused_sgd is not None else None,
+                          first_bucket_bytes=int(first_bucket_bytes))
+        self._build_reducer()
+        self._rebuild_checked = False
+        self._join_active, self._join_iters = False, 0
+        self.logger_data = {"backend": self.backend.name, "world_size": self.world_size,
+                            "bucket_cap_bytes": self.bucket_bytes_cap}
+
+    def _build_reducer(self):
+        """Back end + Reducer (+ fused optimizer facade, peer-visible buffer arena) from the stored constructor arguments; also
+        what ``__setstate__`` runs after unpickling (torch distributed.py:1306-1336 rebuilds its reducer the same way)."""
+        comm_backend, fused_sgd = self._ctor["comm_backend"], self._ctor["fused_sgd"]
+        params, names = self._params, self._param_names
         if comm_backend == "peer":
             if self.device_type != "cuda":
                 raise ValueError("comm_backend='peer' needs CUDA parameters")
@@ -192,16 +209,13 @@ class DistributedDataParallel(nn.Module):
             raise ValueError("unknown comm_backend %r" % comm_backend)
         if fused_sgd is not None and not self.backend.supports_fused:
             raise ValueError("fused_sgd needs comm_backend='peer'")
-        self.reducer = Reducer(params, self.backend, self.bucket_bytes_cap, first_bucket_bytes, find_unused_parameters,
-                               gradient_as_bucket_view, names, fused_sgd, static_graph)
+        self.reducer = Reducer(params, self.backend, self.bucket_bytes_cap, self._ctor["first_bucket_bytes"],
+                               self.find_unused_parameters, self.gradient_as_bucket_view, names, fused_sgd, self.static_graph)
         self.optimizer = FusedSGD(self.reducer, fused_sgd) if fused_sgd is not None else None
         self._buffer_arena = None
-        if isinstance(self.backend, PeerBackend) and self.backend.symm is not None and self.modules_buffers and broadcast_buffers:
+        if isinstance(self.backend, PeerBackend) and self.backend.symm is not None and self.modules_buffers and self.broadcast_buffers:
             self._build_buffer_arena()
-        self._rebuild_checked = False
-        self._join_active, self._join_iters = False, 0
-        self.logger_data = {"backend": self.backend.name, "world_size": self.world_size,
-                            "bucket_cap_bytes": self.bucket_bytes_cap}
+        self._static_unused = None
 
     # ------------------------------------------------------------------------------------------ init helpers
     def _verify_param_shape_across_processes(self):
@@ -253,6 +267,10 @@ class DistributedDataParallel(nn.Module):
     def forward(self, *inputs, **kwargs):
         with torch.autograd.profiler.record_function("DistributedDataParallel.forward"):
             will_sync = torch.is_grad_enabled() and self.require_backward_grad_sync
+            if self.optimizer is not None and will_sync and not (self.device_type == "cuda" and torch.cuda.is_current_stream_capturing()):
+                # the fused kernel reads lr / momentum / weight decay from device memory DURING backward: publish what a stock
+                # LR scheduler or warm-up wrote into param_groups since the last step (a tuple comparison when nothing changed)
+                self.optimizer.push_hyperparameters()
             if self._join_active:
                 self._join_count(1)  # tells the ranks that already ran out of data that one more iteration is coming
                 self._join_iters += 1
@@ -269,8 +287,13 @@ class DistributedDataParallel(nn.Module):
             if will_sync:
                 unused = ()
                 if self.find_unused_parameters:
-                    reach = _reachable_params(out)
-                    unused = [i for i, p in enumerate(self._params) if id(p) not in reach]
+                    if self.static_graph and self._static_unused is not None:
+                        unused = self._static_unused  # static_graph: the set found in the first iteration holds for all
+                    else:
+                        reach = _reachable_params(out)
+                        unused = [i for i, p in enumerate(self._params) if id(p) not in reach]
+                        if self.static_graph:
+                            self._static_unused = unused
                 self.reducer.require_sync = True
                 self.reducer.prepare_for_backward(unused)
             else:
@@ -341,7 +364,10 @@ class DistributedDataParallel(nn.Module):
         self.reducer.comm_hook_state = state
 
     def _set_static_graph(self):
+        """The autograd graph is the same in every iteration: the set of unused parameters is searched once, in the first
+        synchronised forward, and reused (torch distributed.py ``_set_static_graph``)."""
         self.static_graph = True
+        self.reducer.static_graph = True
 
     def _get_ddp_logging_data(self) -> dict:
         """Construction-time and run-time facts about this wrapper (torch distributed.py ``_get_ddp_logging_data`` / the
@@ -391,14 +417,33 @@ class DistributedDataParallel(nn.Module):
         return r
 
     def __getstate__(self):
+        """Process group, back end, Reducer and everything that holds peer mappings stay behind (torch distributed.py
+        :1306-1320); the fused optimizer's momentum travels as a plain state_dict."""
         d = self.__dict__.copy()
-        for k in ("reducer", "backend", "process_group", "optimizer"):
+        opt = d.get("optimizer")
+        d["_pickled_optimizer_state"] = opt.state_dict() if opt is not None else None
+        for k in ("reducer", "backend", "process_group", "optimizer", "_buffer_arena", "_buffer_state", "_buffer_dst"):
             d.pop(k, None)
+        # parameters / buffers are views into peer-visible arenas here; pickle them as ordinary tensors
         return d
 
     def __setstate__(self, state):
+        """Rebuilds the process-group handle, back end, Reducer (hooks included), fused optimizer facade and buffer arena in
+        the unpickling process (torch distributed.py:1322-1336).  Needs ``torch.distributed`` initialised for world sizes > 1."""
+        opt_sd = state.pop("_pickled_optimizer_state", None)
         self.__dict__.update(state)
         self.process_group = dist.group.WORLD if dist.is_initialized() else None
+        self.world_size = dist.get_world_size(self.process_group) if self.process_group is not None else 1
+        self.rank = dist.get_rank(self.process_group) if self.process_group is not None else 0
+        # the unpickled parameters are fresh tensors: refresh the lists the Reducer is built from
+        byname = dict(self.module.named_parameters())
+        self._params = [byname[n] for n in self._param_names]
+        self.modules_buffers = [b for n, b in self.module.named_buffers() if n not in self.parameters_to_ignore]
+        self._build_reducer()
+        if opt_sd is not None and self.optimizer is not None:
+            self.optimizer.load_state_dict(opt_sd)
+        self._rebuild_checked = False
+        self._join_active, self._join_iters = False, 0
 
 
 def _to_device(obj, dev):

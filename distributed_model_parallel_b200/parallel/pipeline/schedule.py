@@ -94,7 +94,10 @@ class PipelineStage:
             use_graphs = os.environ.get("DMP_PIPELINE_GRAPHS", "1") != "0"
         self.use_graphs = bool(use_graphs) and self.device.type == "cuda" and loss_on == "last"
         self._slots, self._slots_key, self._gstream = None, None, None
-        self.stats = {"steps": 0, "p2p_messages": 0, "graph_replays": 0}
+        self._slot_cache: Dict[tuple, list] = {}   # captured micro-batch graphs per shape key (full batch, short last batch)
+        self.last_train_hits = None                # device scalar: top-1 hits of the last train_step (loss-owning stage)
+        self.last_eval_targets = None              # targets of the last eval_step on the loss-owning stage
+        self.stats = {"steps": 0, "p2p_messages": 0, "graph_replays": 0, "graph_builds": 0}
         if self.device.type == "cuda" and num_stages > 1:
             self._warmup_p2p()
 
@@ -226,6 +229,8 @@ class PipelineStage:
                 x.requires_grad_(True)
             return x
 
+        # The warm-up passes run in train mode on zeros: they must not leak into BatchNorm running statistics / counters.
+        saved_buffers = [b.detach().clone() for b in self.module.buffers()]
         with torch.cuda.stream(side):  # eager warm-up so that lazy initialisation does not end up inside a capture
             for _ in range(2):
                 x = make_x()
@@ -236,6 +241,9 @@ class PipelineStage:
                 else:
                     torch.autograd.backward(y, torch.zeros_like(y))
             self._zero_param_grads()
+            with torch.no_grad():
+                for b, v in zip(self.module.buffers(), saved_buffers):
+                    b.copy_(v)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
         # One private memory pool per slot.  A backward capture returns the slot's saved activations to its pool, so with a
@@ -250,6 +258,8 @@ class PipelineStage:
             with torch.cuda.graph(sl["gf"], pool=pool, stream=side):
                 y = self.module(sl["x"])
                 if self.last:
+                    with torch.no_grad():
+                        sl["hits"] = (y.detach().argmax(1) == sl["t"]).sum()
                     y = self.loss_fn(y, sl["t"]) * scale
             sl["y"] = y
             sl["g"] = None if self.last else p2p.TensorMeta.of(y).empty(dev).zero_()
@@ -263,6 +273,10 @@ class PipelineStage:
             slots.append(sl)
         self._zero_param_grads()
         self._slots, self._slots_key = slots, self._graph_key(mb, n_slots, B)
+        self.stats["graph_builds"] += 1
+        if len(self._slot_cache) >= 3:  # full batch + short last batch is the expected population; bound the pools held
+            self._slot_cache.pop(next(iter(self._slot_cache)))
+        self._slot_cache[self._slots_key] = slots
 
     def _graph_key(self, mb: int, n_slots: int, B: int):
         """Everything a captured micro-batch graph has baked in: shapes, the loss scale mb/B, and the addresses of the gradient
@@ -285,6 +299,7 @@ class PipelineStage:
             B, M, _ = self._control(None, None)
         sizes = self._split_sizes(B, M)
         M = len(sizes)
+        self.last_batch = B
         kind = self.schedule if M > 1 else "naive"
         order = generate_schedule(kind, self.W, self.stage, M)
         loss_here = (self.loss_on == "last" and self.last) or (self.loss_on == "first" and self.first)
@@ -306,12 +321,15 @@ class PipelineStage:
         saved_in: Dict[int, torch.Tensor] = {}
         saved_out: Dict[int, torch.Tensor] = {}
         total_loss = None
+        hits = None
         pending = None  # (tensor, peer) produced by the previous step, sent together with the next receive
         graphed = self.use_graphs and len(set(sizes)) == 1
         if graphed:
             n_slots = max_in_flight(order)
-            if self._slots_key != self._graph_key(sizes[0], n_slots, B):
-                self._slots = None  # releases the previous graphs and their pool
+            key = self._graph_key(sizes[0], n_slots, B)
+            if self._slots_key != key and key in self._slot_cache:
+                self._slots, self._slots_key = self._slot_cache[key], key
+            elif self._slots_key != key:
                 try:
                     self._build_slots(sizes[0], M, B, n_slots)
                 except Exception as e:  # e.g. the module cannot be captured: keep training, eagerly (every stage decides alone;
@@ -342,6 +360,7 @@ class PipelineStage:
                         sl["gf"].replay()
                     if self.last:
                         total_loss = sl["y"].detach().clone() if total_loss is None else total_loss + sl["y"].detach()
+                        hits = sl["hits"].clone() if hits is None else hits + sl["hits"]
                     else:
                         pending = (sl["y"], self.next)
                 else:
@@ -377,6 +396,9 @@ class PipelineStage:
                     pending = (y, self.next)
                 elif self.loss_on == "last":
                     loss = self.loss_fn(y, tgt_chunks[m]) * (sizes[m] / B)
+                    with torch.no_grad():
+                        h = (y.detach().argmax(1) == tgt_chunks[m]).sum()
+                        hits = h if hits is None else hits + h
                     saved_out[m] = loss
                     total_loss = loss.detach() if total_loss is None else total_loss + loss.detach()
                 else:  # ring: logits go back to stage 0, which owns targets and loss
@@ -389,6 +411,9 @@ class PipelineStage:
                     lg.requires_grad_(True)
                     loss = self.loss_fn(lg, tgt_chunks[m]) * (sizes[m] / B)
                     total_loss = loss.detach() if total_loss is None else total_loss + loss.detach()
+                    with torch.no_grad():
+                        h = (lg.detach().argmax(1) == tgt_chunks[m]).sum()
+                        hits = h if hits is None else hits + h
                     loss.backward()
                     self._exchange((lg.grad, self.rank_last), None, None)
             else:  # ---------------------------------------------------------------------- backward of micro-batch m
@@ -417,14 +442,17 @@ class PipelineStage:
             else:
                 self.optimizer.zero_grad()
         self.stats["steps"] += 1
+        self.last_train_hits = hits if loss_here else None
         return total_loss if loss_here else None
 
     # ------------------------------------------------------------------------------------------ evaluation
     @torch.no_grad()
     def eval_step(self, inputs: Optional[torch.Tensor] = None, targets: Optional[torch.Tensor] = None):
         """Forward-only pass of one batch (the reference's val_header / val_medium / val_last, utils.py:81-210).
-        Returns (loss, logits) on the stage that owns the loss, else (None, None)."""
+        Returns (loss, logits) on the stage that owns the loss, else (None, None); that stage also keeps the batch's targets
+        in ``last_eval_targets`` (with ``loss_on="last"`` they were shipped there), for accuracy bookkeeping."""
         self.module.eval()
+        self.last_eval_targets = None
         if self.first:
             inputs = inputs.to(self.device)
             B, _, _ = self._control([int(inputs.shape[0]), 1, 0], inputs)
@@ -445,13 +473,15 @@ class PipelineStage:
                     dist.recv(t, self.rank0, group=self.group)
                 else:
                     t = targets.to(self.device)
+                self.last_eval_targets = t
                 result = (self.loss_fn(y, t), y)
         else:
             if self.last and self.W > 1:
                 self._exchange((y, self.rank0), None, None)
             if self.first:
                 lg = self._exchange(None, self._logits_meta.with_batch(B), self.rank_last) if self.W > 1 else y
-                result = (self.loss_fn(lg, targets.to(self.device)), lg)
+                self.last_eval_targets = targets.to(self.device)
+                result = (self.loss_fn(lg, self.last_eval_targets), lg)
         p2p.wait_all(self._send_works)
         self._keepalive, self._send_works = [], []
         return result

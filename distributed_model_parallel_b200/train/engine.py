@@ -36,18 +36,40 @@ class TrainStep:
         self.steps = 0
         self.launches_per_iteration = 0
 
-    # one eager iteration on the current stream, reading the static buffers
-    def _iteration(self):
-        out = self.model(self.x_static)
+    # one eager iteration on the current stream; reads the static buffers unless given a batch of another shape
+    def _iteration(self, x=None, y=None):
+        x = self.x_static if x is None else x
+        y = self.y_static if y is None else y
+        out = self.model(x)
         if self.loss_fn is not None:
-            loss = self.loss_fn(out, self.y_static)
+            loss = self.loss_fn(out, y)
             self.stats[0].copy_(loss.detach())
         else:
-            loss = OF.cross_entropy(out.float() if out.dtype not in (torch.float32, torch.bfloat16) else out, self.y_static,
-                                    self.stats)
+            loss = OF.cross_entropy(out.float() if out.dtype not in (torch.float32, torch.bfloat16) else out, y, self.stats)
         loss.backward()
         self.optimizer.step()
         self.optimizer.zero_grad()
+
+    def _snapshot(self):
+        """Everything the warm-up iterations mutate: parameters and buffers (BatchNorm running statistics, counters) and the
+        optimizer's momentum.  Restored after the capture so that batch 0 is trained on once, like every other batch."""
+        with torch.no_grad():
+            model_sd = {k: v.detach().clone() for k, v in self.model.state_dict().items()}
+            opt_sd = self.optimizer.state_dict()
+            for st in opt_sd.get("state", {}).values():
+                for k, v in list(st.items()):
+                    if isinstance(v, torch.Tensor):
+                        st[k] = v.detach().clone()
+        return model_sd, opt_sd
+
+    def _restore(self, snap):
+        model_sd, opt_sd = snap
+        with torch.no_grad():
+            self.model.load_state_dict(model_sd)
+            self.optimizer.load_state_dict(opt_sd)
+            for obj in (self.optimizer, getattr(self.model, "reducer", None)):
+                if obj is not None and hasattr(obj, "sync_shadow"):
+                    obj.sync_shadow()
 
     def _setup(self, x, y, device):
         self.x_static = torch.empty(x.shape, dtype=x.dtype, device=device)
@@ -60,6 +82,7 @@ class TrainStep:
         self.y_static.copy_(y, non_blocking=True)
         if not self.use_graph:
             return
+        snap = self._snapshot()
         s = torch.cuda.Stream(device=device)
         s.wait_stream(torch.cuda.current_stream(device))
         with torch.cuda.stream(s):
@@ -74,13 +97,27 @@ class TrainStep:
         with torch.cuda.graph(self.graph):
             self._iteration()
         self.launches_per_iteration = _native.launch_count() - c0  # our kernels re-issued by every replay
-        self.steps += self.warmup_iters + 1
+        torch.cuda.synchronize(device)
+        self._restore(snap)  # capture does not execute; the warm-up iterations did: undo them
 
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """Runs one step on (x, y) (host pinned or device tensors). Returns the device stats tensor."""
         if self.x_static is None:
             p = next(self.model.parameters())
             self._setup(x, y, p.device)
+        if x.shape != self.x_static.shape or y.shape != self.y_static.shape:
+            # A batch of another shape (the short last batch of an epoch: 50000 % 512 = 336 in the reference's setting, which
+            # its dynamic p2p headers exist for, distributed_layers.py:11-12) runs eagerly on fresh device tensors; the
+            # captured graph keeps its shape.  Under DDP every rank sees the same batch sizes (DistributedSampler pads), so
+            # all ranks take this branch together.
+            dev = self.x_static.device
+            if hasattr(self.optimizer, "push_hyperparameters"):
+                self.optimizer.push_hyperparameters()
+            c0 = _native.launch_count()
+            self._iteration(x.to(dev, non_blocking=True), y.to(dev, non_blocking=True))
+            self.eager_fallback_steps = getattr(self, "eager_fallback_steps", 0) + 1
+            self.steps += 1
+            return self.stats
         self.x_static.copy_(x, non_blocking=True)
         self.y_static.copy_(y, non_blocking=True)
         if self.graph is not None:

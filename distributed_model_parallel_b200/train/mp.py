@@ -20,13 +20,33 @@ from ..data import prepare_dataloader
 from ..models import build_model
 from ..ops import functional as OF
 from ..optim import FlatFusedSGD
-from ..parallel.pipeline import PipelineStage, layer_costs, reference_split, split_sequential
+from ..parallel.pipeline import PipelineStage, layer_costs, partition_balanced, reference_split, split_sequential
 from ..utils import AverageMeter, EpochLogger, TrainConfig, accuracy, get_lr, save_pipeline_shard, stage_key_map
 from .common import CosineWithWarmup, limit
 
 
 def _loss(logits, target):
     return OF.cross_entropy(logits if logits.dtype in (torch.float32, torch.bfloat16) else logits.float(), target)
+
+
+def _boundaries(seq, world_size: int, cfg: TrainConfig, device, rank: int):
+    """Stage boundaries.  On GPUs the cost of a layer is its measured forward+backward time on one micro-batch (parameter counts
+    put 13 of VGG-16's 19 layers -- nearly all of its FLOPs -- into stage 0); rank 0 measures and every rank adopts its cut so
+    that all stages agree.  On CPU (tests, plumbing) the parameter count is used: deterministic and good enough."""
+    mode = getattr(cfg, "partition", None) or ("time" if device.type == "cuda" else "params")
+    if mode != "time":
+        return partition_balanced(layer_costs(seq, mode), world_size)
+    b = torch.zeros(world_size + 1, dtype=torch.int64, device=device)
+    if rank == 0:
+        from ..data.datasets import sample_batch
+        mb = max(1, cfg.batch_size // max(1, cfg.microbatches))
+        x = sample_batch(cfg, mb).to(device)
+        seq.to(device)
+        costs = layer_costs(seq, "time", sample=x)
+        seq.to("cpu")
+        b.copy_(torch.tensor(partition_balanced(costs, world_size), dtype=torch.int64))
+    dist.broadcast(b, src=0)
+    return [int(v) for v in b.tolist()]
 
 
 def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
@@ -44,7 +64,7 @@ def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
         stages = reference_split(full, stem_relu=False)
     else:
         seq = full.as_sequential()
-        stages = split_sequential(seq, world_size, layer_costs(seq, "params"))
+        stages = split_sequential(seq, world_size, boundaries=_boundaries(seq, world_size, cfg, device, rank))
     module = stages[rank].to(device)
     key_map = stage_key_map(full, module)
     sgd = dict(lr=cfg.lr, momentum=cfg.momentum, weight_decay=cfg.weight_decay)
@@ -69,7 +89,7 @@ def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
                       os.path.join(cfg.log_dir, "mp_rank%d.jsonl" % rank), rank)
     best = 0.0
     for epoch in range(cfg.epochs):
-        loss_m, bt, dt = AverageMeter(), AverageMeter(), AverageMeter()
+        loss_m, acc_m, bt, dt = AverageMeter(), AverageMeter(), AverageMeter(), AverageMeter()
         it = iter(limit(train_loader, cfg.steps_per_epoch)) if first else None
         t0 = time.perf_counter()
         for i in range(n_train):
@@ -78,8 +98,11 @@ def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
             loss = stage.train_step(x, y, cfg.microbatches)
             if loss is not None:
                 loss_m.update(loss)
+                nb = stage.last_batch
+                if stage.last_train_hits is not None:  # top-1 of this batch, counted on device by the stage that owns the loss
+                    acc_m.update(stage.last_train_hits * (100.0 / nb), nb)
                 if cfg.print_freq and i % cfg.print_freq == 0:
-                    print("train_loss: %.4f" % float(loss))
+                    print("train_loss: %.4f train_acc1 %.2f" % (float(loss), float(acc_m.avg)))
             bt.update(time.perf_counter() - t0)
             t0 = time.perf_counter()
         vloss, vacc = AverageMeter(), AverageMeter()
@@ -88,16 +111,20 @@ def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
         for i in range(n_val):
             x, y = next(it) if first else (None, None)
             l, logits = stage.eval_step(x, y)
-            if l is not None:
-                vloss.update(l)
-                if cfg.loss_on == "first":
-                    vacc.update(accuracy(logits, y.to(device))[0])
+            if l is not None:  # the stage that owns the loss holds logits and targets (utils.py:97-98 of the reference: rank 0)
+                t = stage.last_eval_targets
+                vloss.update(l, t.shape[0])
+                vacc.update(accuracy(logits, t)[0], t.shape[0])
         if sched is not None:
             sched.step()
-        save_pipeline_shard(module, rank, key_map, os.path.join(os.path.dirname(cfg.checkpoint) or ".", "pipeline"), epoch, vacc.avg)
+        # every stage stores the epoch's validation accuracy with its shard: the owner tells the others
+        va = torch.tensor([float(vacc.avg) if owner else 0.0], dtype=torch.float32, device=device)
+        dist.broadcast(va, src=(0 if cfg.loss_on == "first" else world_size - 1))
+        vacc_all = float(va[0])
+        save_pipeline_shard(module, rank, key_map, os.path.join(os.path.dirname(cfg.checkpoint) or ".", "pipeline"), epoch, vacc_all)
         if owner:
-            print(log.log_epoch(epoch, loss_m.avg, 0.0, vloss.avg, vacc.avg, bt.avg, dt.avg, lr=get_lr(optimizer) if optimizer else 0.0))
-        best = max(best, vacc.avg)
+            print(log.log_epoch(epoch, loss_m.avg, acc_m.avg, vloss.avg, vacc.avg, bt.avg, dt.avg, lr=get_lr(optimizer) if optimizer else 0.0))
+        best = max(best, vacc_all)
     if init_pg:
         dist.barrier()
         dist.destroy_process_group()

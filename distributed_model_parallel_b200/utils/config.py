@@ -37,6 +37,7 @@ class TrainConfig:
     seed: int = 0
     cuda_graph: bool = True
     reference_split: bool = False        # reproduce the reference's 3/6/6/2 MobileNetV2 split (needs world_size 4)
+    partition: str = ""                  # pipeline cost model: time | params | uniform ("" = time on GPUs, params on CPU)
 
     def to_dict(self):
         return asdict(self)
@@ -72,6 +73,7 @@ def build_parser(description: str = "distributed_model_parallel_b200 trainer") -
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--no-cuda-graph", action="store_false", dest="cuda_graph")
     p.add_argument("--reference-split", action="store_true")
+    p.add_argument("--partition", default=TrainConfig.partition, choices=["", "time", "params", "uniform"])
     return p
 
 

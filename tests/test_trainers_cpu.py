@@ -54,12 +54,17 @@ def test_ddp_trainer_two_gloo_ranks(tmp_path):
 def test_mp_trainer_two_stage_pipeline(tmp_path):
     url = "tcp://127.0.0.1:%d" % _port()
     assert cli.main(["mp", *_common(tmp_path, ["--world-size", "2", "--dist-backend", "gloo", "--dist-url", url, "--schedule", "1f1b",
-                                                "--microbatches", "2"])]) == 0
+                                                "--microbatches", "2", "-b", "32", "--val-batch-size", "64"])]) == 0
     logs = os.listdir(tmp_path / "log")
     text = [f for f in logs if f.endswith(".txt")]
     assert text, logs
     line = open(tmp_path / "log" / text[0]).read().strip().splitlines()[-1]
     assert line.startswith("step:0") and "time_per_batch:" in line                        # model_parallel.py:119-124
+    # the stage that owns the loss logs real accuracies (reference: utils.py:65-78,98-109), not placeholders
+    fields = dict(tok.split(":", 1) for tok in line.split() if ":" in tok)
+    assert float(fields["acc1_val"]) > 0.0 and float(fields["acc1_train"]) > 0.0, line
+    shard = torch.load(tmp_path / "ckpt" / "pipeline" / "stage0.pth", map_location="cpu", weights_only=False)
+    assert shard["acc"] == float(fields["acc1_val"]) or abs(shard["acc"] - float(fields["acc1_val"])) < 1e-3
     # every stage wrote its shard; merged they are exactly the single-model state_dict
     from distributed_model_parallel_b200.models import MobileNetV2
     from distributed_model_parallel_b200.utils import merge_pipeline_shards
@@ -68,3 +73,20 @@ def test_mp_trainer_two_stage_pipeline(tmp_path):
     full = MobileNetV2()
     assert set(merged) == set(full.state_dict())
     full.load_state_dict(merged, strict=True)
+
+
+def test_train_step_accepts_a_short_last_batch():
+    """50000 % 512 = 336: the last batch of an epoch is short (drop_last=False, like the reference's loaders); the step engine
+    must take it instead of failing on its static input buffers."""
+    from distributed_model_parallel_b200.models import MobileNetV2
+    from distributed_model_parallel_b200.train.engine import TrainStep
+
+    torch.manual_seed(0)
+    net = MobileNetV2()
+    opt = torch.optim.SGD(net.parameters(), lr=0.01, momentum=0.9)
+    step = TrainStep(net, opt, use_graph=False)
+    g = torch.Generator().manual_seed(1)
+    for n in (16, 10, 16):
+        stats = step(torch.randn(n, 3, 32, 32, generator=g), torch.randint(0, 10, (n,), generator=g))
+        assert torch.isfinite(stats[0])
+    assert step.steps == 3 and step.eager_fallback_steps == 1
