@@ -52,6 +52,12 @@ _KERNEL_SIGS = {
     "dmp_gemm_bf16_colstats": (i32, [vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, vp]),
     "dmp_dwconv3x3_fwd_colstats": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp, vp]),
     "dmp_bn_sums_bytes": (i64, [i32]),
+    # conv -> bn -> relu chain fusions (BatchNorm reductions in the producers' epilogues, normalisation on load)
+    "dmp_gemm_bf16_dgrad_bnbwd": (i32, [vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i64, vp, vp, vp, vp, i32, vp, vp]),
+    "dmp_dwconv3x3_fwd_bnin_colstats": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp, vp, vp]),
+    "dmp_dwconv3x3_dgrad_bnbwd": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp, vp]),
+    "dmp_dwconv3x3_wgrad_bnin": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp]),
+    "dmp_bn_bwd_dx_sums": (i32, [vp, vp, i32, vp, vp, vp, vp, vp, vp, i32, i64, i32, vp, vp]),
     "dmp_bn_apply_sums": (i32, [vp, i32, vp, vp, i64, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, i32, vp]),
     "dmp_bn_fwd_fused": (i32, [vp, i32, vp, vp, i64, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, i32, vp]),
     "dmp_bn_bwd_fused": (i32, [vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, vp, vp]),

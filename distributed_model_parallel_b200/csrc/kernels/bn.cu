@@ -593,6 +593,74 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
     }
 }
 
+// BatchNorm backward when the two reductions already exist: g is the incoming gradient with the ReLU mask applied, and
+// sums = {sum g, sum g * xhat} (double[2C] + int ticket) were accumulated by the kernel that produced g (the data-gradient
+// kernel of the consuming convolution: dmp_gemm_bf16_dgrad_bnbwd / dmp_dwconv3x3_dgrad_bnbwd).  One elementwise pass:
+//   dx = gamma * invstd * (g - s1/M - xhat * s2/M)        (dx may alias g)
+// Block 0 writes dgamma = s2, dbeta = s1 (or accumulates); the last block to have read the sums clears them (ticket).
+template <typename T>
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_dx_sums_kernel(const T* g, const T* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ invstd,
+                      const float* __restrict__ gamma, double count, T* dx, float* __restrict__ dgamma, float* __restrict__ dbeta,
+                      int accumulate_params, long long nvec, int C, double* __restrict__ sums) {
+    constexpr int VEC = Vec<T>::N;
+    constexpr int U = 4;
+    __shared__ int s_last;
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const int ch0 = (int)((tid * VEC) % C);
+    const double inv_count = 1.0 / count;
+    float mu[VEC], is[VEC], a[VEC], b[VEC], c[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        mu[j] = mean[ch0 + j];
+        is[j] = invstd[ch0 + j];
+        a[j] = (gamma ? gamma[ch0 + j] : 1.f) * is[j];
+        b[j] = (float)(sums[ch0 + j] * inv_count);
+        c[j] = (float)(sums[C + ch0 + j] * inv_count);
+    }
+    if (blockIdx.x == 0) {
+        for (int ch = threadIdx.x; ch < C; ch += BN_THREADS) {
+            const float db = (float)sums[ch], dg = (float)sums[C + ch];
+            if (dgamma) dgamma[ch] = accumulate_params ? dgamma[ch] + dg : dg;
+            if (dbeta) dbeta[ch] = accumulate_params ? dbeta[ch] + db : db;
+        }
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int* ticket = (int*)(sums + 2 * (long long)C);
+        s_last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last) {
+        for (int i = threadIdx.x; i < 2 * C; i += BN_THREADS) sums[i] = 0.0;
+        if (threadIdx.x == 0) *(int*)(sums + 2 * (long long)C) = 0;
+    }
+    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+        int4 rg[U], rx[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                rg[u] = Vec<T>::load_raw(g, v0 + u * stride);
+                rx[u] = Vec<T>::load_raw(x, v0 + u * stride);
+            }
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (v0 + u * stride < nvec) {
+                float gv[VEC], xv[VEC];
+                Vec<T>::unpack(rg[u], gv);
+                Vec<T>::unpack(rx[u], xv);
+#pragma unroll
+                for (int j = 0; j < VEC; ++j) {
+                    const float xh = (xv[j] - mu[j]) * is[j];
+                    gv[j] = a[j] * (gv[j] - b[j] - xh * c[j]);
+                }
+                Vec<T>::store(dx, v0 + u * stride, gv);
+            }
+    }
+}
+
 // grid for a cooperative launch: a multiple of q (channel alignment) that fits co-resident on the device
 template <typename K>
 int bn_coop_grid(K kernel, long long nvec, int C, int vec, size_t smem) {
@@ -785,6 +853,26 @@ DMP_API int dmp_bn_apply_sums(const void* x, int dtype, const void* residual, vo
         bn_apply_sums_kernel<float><<<grid, BN_THREADS, 0, stream>>>((const float*)x, (const float*)residual, (float*)y, nvec, C, (double)M,
                                                                      gamma, beta, running_mean, running_var, num_batches_tracked,
                                                                      momentum, eps, mean, invstd, sums, relu);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// BatchNorm backward from reductions produced by the kernel that wrote g (see bn_bwd_dx_sums_kernel).  dx may alias g.
+DMP_API int dmp_bn_bwd_dx_sums(const void* g, const void* x, int dtype, const float* mean, const float* invstd, const float* gamma,
+                               void* dx, float* dgamma, float* dbeta, int accumulate_params, long long M, int C, double* sums,
+                               cudaStream_t stream) {
+    if (int rc = bn_check("dmp_bn_bwd_dx_sums", M, C, dtype)) return rc;
+    DMP_REQUIRE(sums && mean && invstd, "dmp_bn_bwd_dx_sums: null sums/mean/invstd");
+    const int vec = dtype == 1 ? 8 : 4;
+    const long long nvec = M * C / vec;
+    const int grid = bn_grid(nvec, C, vec);
+    if (dtype == 1)
+        bn_bwd_dx_sums_kernel<bf16><<<grid, BN_THREADS, 0, stream>>>((const bf16*)g, (const bf16*)x, mean, invstd, gamma, (double)M,
+                                                                     (bf16*)dx, dgamma, dbeta, accumulate_params, nvec, C, sums);
+    else
+        bn_bwd_dx_sums_kernel<float><<<grid, BN_THREADS, 0, stream>>>((const float*)g, (const float*)x, mean, invstd, gamma, (double)M,
+                                                                      (float*)dx, dgamma, dbeta, accumulate_params, nvec, C, sums);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;

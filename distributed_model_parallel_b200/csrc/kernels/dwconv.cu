@@ -42,6 +42,110 @@ __device__ __forceinline__ void store8(bf16* p, const float* f) {
     *(int4*)p = *(int4*)&b;
 }
 
+// Fusions with the BatchNorm layers around a depthwise convolution (the expand -> bn1 -> relu -> depthwise -> bn2 chain of
+// /root/reference/code/distributed_training/model/mobilenetv2.py:32-33):
+//   BNIN == 1  the input is the RAW output y1 of the previous convolution; relu(bn1(y1)) is applied while loading, with the
+//              coefficients derived from the batch sums the producer's epilogue accumulated (`sums`, double[2C] + int ticket).
+//              Block 0 publishes mean / invstd / running statistics, the last block to have read the sums clears them.
+//              The normalised activation is never written to memory.
+//   BNIN == 2  same transform from saved mean / invstd (backward passes re-create the activation on the fly).
+//   BNBWD      (data gradient) the result is d(relu(bn1(y1))); the ReLU mask and xhat are recomputed from y1 at the output
+//              pixel, the masked gradient g is stored and sum(g), sum(g * xhat) are accumulated into `bwd_sums` (double[2C]).
+struct DwBn {
+    const double* sums;          // BNIN 1
+    double inv_count;            // BNIN 1: 1 / (N*H*W of the input)
+    double count;
+    const float* gamma;
+    const float* beta;
+    float eps, momentum;
+    float* running_mean;
+    float* running_var;
+    long long* num_batches_tracked;
+    float* mean_out;             // BNIN 1: published by block 0
+    float* invstd_out;
+    const float* mean;           // BNIN 2 / BNBWD
+    const float* invstd;
+    const bf16* y_raw;           // BNBWD: the BatchNorm input at the OUTPUT resolution of this kernel
+    double* bwd_sums;            // BNBWD
+};
+
+// scale / shift (and mean / invstd) of channels ch0..ch0+7
+template <int BNIN>
+__device__ __forceinline__ void dw_bn_coeffs(const DwBn& a, int ch0, int C, float* sc, float* sh, float* mu, float* is) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int c = ch0 + j;
+        float m, r;
+        if (BNIN == 1) {
+            const double md = a.sums[c] * a.inv_count;
+            double var = a.sums[C + c] * a.inv_count - md * md;
+            if (var < 0.0) var = 0.0;
+            m = (float)md;
+            r = 1.0f / sqrtf((float)var + a.eps);
+        } else {
+            m = a.mean[c];
+            r = a.invstd[c];
+        }
+        const float g = a.gamma ? a.gamma[c] : 1.f, b = a.beta ? a.beta[c] : 0.f;
+        sc[j] = g * r;
+        sh[j] = b - m * g * r;
+        mu[j] = m;
+        is[j] = r;
+    }
+}
+
+// BNIN == 1 bookkeeping, reached by every thread of the block: block 0 publishes the statistics, the last block clears the sums.
+__device__ __forceinline__ void dw_bn_publish_and_release(const DwBn& a, int C) {
+    __shared__ int s_last;
+    if (blockIdx.x == 0) {
+        for (int c = threadIdx.x; c < C; c += DW_THREADS) {
+            const double m = a.sums[c] / a.count;
+            double var = a.sums[C + c] / a.count - m * m;
+            if (var < 0.0) var = 0.0;
+            a.mean_out[c] = (float)m;
+            a.invstd_out[c] = (float)(1.0 / sqrt(var + (double)a.eps));
+            if (a.running_mean != nullptr) {
+                const double unbiased = a.count > 1.0 ? var * a.count / (a.count - 1.0) : var;
+                a.running_mean[c] = (1.f - a.momentum) * a.running_mean[c] + a.momentum * (float)m;
+                a.running_var[c] = (1.f - a.momentum) * a.running_var[c] + a.momentum * (float)unbiased;
+            }
+        }
+        if (threadIdx.x == 0 && a.num_batches_tracked != nullptr) *a.num_batches_tracked += 1;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int* ticket = (int*)(a.sums + 2 * (long long)C);
+        s_last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+    }
+    __syncthreads();
+    if (s_last) {
+        double* sm = const_cast<double*>(a.sums);
+        for (int i = threadIdx.x; i < 2 * C; i += DW_THREADS) sm[i] = 0.0;
+        if (threadIdx.x == 0) *(int*)(sm + 2 * (long long)C) = 0;
+    }
+}
+
+// Block-level combine of per-thread {sum[8], sumsq[8]} partials of channels ch0..ch0+7 into global double accumulators.
+// Channel vectors repeat over the block's threads with period P = C/8, so thread g < min(P, 256) folds threads g, g+P, ...
+// out of shared memory and issues the 16 atomics of its channel vector.  Must be reached by every thread of the block.
+__device__ __forceinline__ void dw_block_channel_reduce(const float* vals, int ch0, int C, double* __restrict__ accum) {
+    __shared__ float s_part[DW_THREADS * 17];  // padded rows: 17 floats per thread
+    __shared__ int s_ch0[DW_THREADS];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) s_part[threadIdx.x * 17 + i] = vals[i];
+    s_ch0[threadIdx.x] = ch0;
+    __syncthreads();
+    const int P = C >> 3;
+    const int ngroups = P < DW_THREADS ? P : DW_THREADS;
+    for (int item = threadIdx.x; item < ngroups * 16; item += DW_THREADS) {
+        const int g = item >> 4, i = item & 15;
+        float sacc = 0.f;
+        for (int t = g; t < DW_THREADS; t += P) sacc += s_part[t * 17 + i];
+        atomicAdd(&accum[(long long)(i >> 3) * C + s_ch0[g] + (i & 7)], (double)sacc);
+    }
+}
+
 // y[n,ho,wo,c] = sum_{kh,kw} x[n, ho*s+kh-1, wo*s+kw-1, c] * w[c,kh,kw]
 template <typename WT>
 __global__ void __launch_bounds__(DW_THREADS)
@@ -126,81 +230,83 @@ dw_dgrad_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __r
 //   dx[2a+1][2b  ] = dy[a+1][b] w01 + dy[a][b] w21      dx[2a+1][2b+1] = dy[a+1][b+1] w00 + dy[a+1][b] w02 + dy[a][b+1] w20 + dy[a][b] w22
 // One thread writes two such blocks (2 x 4 pixels of its 8 channels) from six 16-byte loads -- no divisibility tests, 0.75
 // loads per output instead of 2.25, and the 72 weights are fetched once per eight outputs instead of once per output.
-template <typename WT>
+template <typename WT, bool BNBWD = false>
 __global__ void __launch_bounds__(DW_THREADS, 2)
 dw_dgrad_s2_kernel(const bf16* __restrict__ dy, const WT* __restrict__ w, bf16* __restrict__ dx, int N, int H, int W, int C,
-                   int Ho, int Wo) {
+                   int Ho, int Wo, const DwBn aux) {
     constexpr int TQ = 2;
     const int P = C >> 3;
     const int tiles_w = (Wo + TQ - 1) / TQ;
     const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
     const long long total = (long long)N * Ho * tiles_w * P;
-    if (idx >= total) return;
-    const int cv = (int)(idx % P);
-    long long t = idx / P;
-    const int tw = (int)(t % tiles_w); t /= tiles_w;
-    const int a = (int)(t % Ho);
-    const int n = (int)(t / Ho);
-    const int ch0 = cv * 8;
-    const int b0 = tw * TQ;
-    float wt[72];
-    load_w72<WT>(w, ch0, wt);
-    float d0[TQ + 1][8], d1[TQ + 1][8];
+    const bool active = idx < total;
+    if (!BNBWD && !active) return;
+    const int ch0 = (int)(idx % P) * 8;
+    float st[BNBWD ? 16 : 1];
+    if (BNBWD) {
 #pragma unroll
-    for (int c = 0; c <= TQ; ++c) {
-        const int col = b0 + c;
-        const bool okc = col < Wo;
-        if (okc) load8(dy + (((long long)n * Ho + a) * Wo + col) * C + ch0, d0[c]);
-        else {
+        for (int i = 0; i < 16; ++i) st[i] = 0.f;
+    }
+    if (active) {
+        long long t = idx / P;
+        const int tw = (int)(t % tiles_w); t /= tiles_w;
+        const int a = (int)(t % Ho);
+        const int n = (int)(t / Ho);
+        const int b0 = tw * TQ;
+        float wt[72];
+        load_w72<WT>(w, ch0, wt);
+        float sc[8], sh[8], mu[8], is[8];
+        if (BNBWD) dw_bn_coeffs<2>(aux, ch0, C, sc, sh, mu, is);
+        float d0[TQ + 1][8], d1[TQ + 1][8];
 #pragma unroll
-            for (int j = 0; j < 8; ++j) d0[c][j] = 0.f;
+        for (int c = 0; c <= TQ; ++c) {
+            const int col = b0 + c;
+            const bool okc = col < Wo;
+            if (okc) load8(dy + (((long long)n * Ho + a) * Wo + col) * C + ch0, d0[c]);
+            else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) d0[c][j] = 0.f;
+            }
+            if (okc && a + 1 < Ho) load8(dy + (((long long)n * Ho + a + 1) * Wo + col) * C + ch0, d1[c]);
+            else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) d1[c][j] = 0.f;
+            }
         }
-        if (okc && a + 1 < Ho) load8(dy + (((long long)n * Ho + a + 1) * Wo + col) * C + ch0, d1[c]);
-        else {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) d1[c][j] = 0.f;
+        for (int q = 0; q < TQ; ++q) {
+            const int b = b0 + q;
+            if (b >= Wo) continue;
+            float o[4][8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const float* k = wt + j * 9;
+                o[0][j] = d0[q][j] * k[4];
+                o[1][j] = d0[q + 1][j] * k[3] + d0[q][j] * k[5];
+                o[2][j] = d1[q][j] * k[1] + d0[q][j] * k[7];
+                o[3][j] = d1[q + 1][j] * k[0] + d1[q][j] * k[2] + d0[q + 1][j] * k[6] + d0[q][j] * k[8];
+            }
+            const long long off = (((long long)n * H + 2 * a) * W + 2 * b) * C + ch0;
+            const long long offs[4] = {off, off + C, off + (long long)W * C, off + (long long)W * C + C};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                if (BNBWD) {  // the results are d(relu(bn(y1))): mask from y1, store g, accumulate the BatchNorm-backward sums
+                    float yv[8];
+                    load8(aux.y_raw + offs[e], yv);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float g = (yv[j] * sc[j] + sh[j] > 0.f) ? o[e][j] : 0.f;
+                        g = __bfloat162float(__float2bfloat16_rn(g));
+                        o[e][j] = g;
+                        st[j] += g;
+                        st[8 + j] += g * ((yv[j] - mu[j]) * is[j]);
+                    }
+                }
+                store8(dx + offs[e], o[e]);
+            }
         }
     }
-#pragma unroll
-    for (int q = 0; q < TQ; ++q) {
-        const int b = b0 + q;
-        if (b >= Wo) break;
-        float o00[8], o01[8], o10[8], o11[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-            const float* k = wt + j * 9;
-            o00[j] = d0[q][j] * k[4];
-            o01[j] = d0[q + 1][j] * k[3] + d0[q][j] * k[5];
-            o10[j] = d1[q][j] * k[1] + d0[q][j] * k[7];
-            o11[j] = d1[q + 1][j] * k[0] + d1[q][j] * k[2] + d0[q + 1][j] * k[6] + d0[q][j] * k[8];
-        }
-        bf16* r0 = dx + (((long long)n * H + 2 * a) * W + 2 * b) * C + ch0;
-        bf16* r1 = r0 + (long long)W * C;
-        store8(r0, o00);
-        store8(r0 + C, o01);
-        store8(r1, o10);
-        store8(r1 + C, o11);
-    }
-}
-
-// Block-level combine of per-thread {sum[8], sumsq[8]} partials of channels ch0..ch0+7 into global double accumulators.
-// Channel vectors repeat over the block's threads with period P = C/8, so thread g < min(P, 256) folds threads g, g+P, ...
-// out of shared memory and issues the 16 atomics of its channel vector.  Must be reached by every thread of the block.
-__device__ __forceinline__ void dw_block_channel_reduce(const float* vals, int ch0, int C, double* __restrict__ accum) {
-    __shared__ float s_part[DW_THREADS * 17];  // padded rows: 17 floats per thread
-    __shared__ int s_ch0[DW_THREADS];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) s_part[threadIdx.x * 17 + i] = vals[i];
-    s_ch0[threadIdx.x] = ch0;
-    __syncthreads();
-    const int P = C >> 3;
-    const int ngroups = P < DW_THREADS ? P : DW_THREADS;
-    for (int item = threadIdx.x; item < ngroups * 16; item += DW_THREADS) {
-        const int g = item >> 4, i = item & 15;
-        float sacc = 0.f;
-        for (int t = g; t < DW_THREADS; t += P) sacc += s_part[t * 17 + i];
-        atomicAdd(&accum[(long long)(i >> 3) * C + s_ch0[g] + (i & 7)], (double)sacc);
-    }
+    if (BNBWD) dw_block_channel_reduce(st, ch0, C, aux.bwd_sums);
 }
 
 // Strip version of the forward stencil: one thread produces TW horizontally adjacent output pixels of its 8 channels,
@@ -208,17 +314,21 @@ __device__ __forceinline__ void dw_block_channel_reduce(const float* vals, int c
 // stride 1).  FLIP=true mirrors the taps: with stride 1 the data gradient is the same stencil applied to dy.
 // STATS=true additionally accumulates, per channel, the sum and sum of squares of the bf16-rounded outputs into
 // stats[0..C) / stats[C..2C) (double): the BatchNorm batch statistics come out of the convolution itself.
-template <typename WT, int STRIDE, int TW, bool FLIP, bool STATS>
+template <typename WT, int STRIDE, int TW, bool FLIP, bool STATS, int BNIN = 0, bool BNBWD = false>
 __global__ void __launch_bounds__(DW_THREADS, 2)  // 2 blocks/SM: the few spilled registers cost less than half occupancy
 dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
-                int Ho, int Wo, double* __restrict__ stats) {
+                int Ho, int Wo, double* __restrict__ stats, const DwBn aux) {
+    // One work item (a strip of TW output pixels of one channel vector) per thread, many more blocks than SMs.  A persistent
+    // variant (each thread keeps its channel vector and weights across items) measured 83 us against 53 us on 128x32x32x144:
+    // block turnover hides the load latency of this register-bound kernel better than a loop inside 16 resident warps does.
     constexpr int NC = (TW - 1) * STRIDE + 3;  // input columns feeding the strip
+    constexpr bool ALL_THREADS = STATS || BNBWD || BNIN == 1;  // block-wide steps follow: no early exit
     const int P = C >> 3;
     const int tiles_w = (Wo + TW - 1) / TW;
     const long long idx = blockIdx.x * (long long)DW_THREADS + threadIdx.x;
     const long long total = (long long)N * Ho * tiles_w * P;
     const bool active = idx < total;
-    if (!STATS && !active) return;
+    if (!ALL_THREADS && !active) return;
     const int cv = (int)(idx % P);
     long long t = idx / P;
     const int wt_ = (int)(t % tiles_w); t /= tiles_w;
@@ -226,11 +336,14 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
     const int n = (int)(t / Ho);
     const int ch0 = cv * 8;
     const int wo0 = wt_ * TW;
-    float st[STATS ? 16 : 1];
-    if (STATS) {
+    float st[(STATS || BNBWD) ? 16 : 1];
+    if (STATS || BNBWD) {
 #pragma unroll
         for (int i = 0; i < 16; ++i) st[i] = 0.f;
     }
+    float sc[8], sh[8], mu[8], is[8];
+    if (BNIN != 0 && active) dw_bn_coeffs<BNIN>(aux, ch0, C, sc, sh, mu, is);
+    if (BNBWD && active) dw_bn_coeffs<2>(aux, ch0, C, sc, sh, mu, is);
     if (active) {
         float wt[72];
         load_w72<WT>(w, ch0, wt);
@@ -249,8 +362,13 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
 #pragma unroll
             for (int c = 0; c < NC; ++c) {
                 const int wi = wi0 + c;
-                if (wi >= 0 && wi < W) load8(row + (long long)wi * C, col[c]);
-                else {
+                if (wi >= 0 && wi < W) {
+                    load8(row + (long long)wi * C, col[c]);
+                    if (BNIN != 0) {  // the convolution's real input is relu(bn(y1)); the zero padding stays zero
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) col[c][j] = fmaxf(col[c][j] * sc[j] + sh[j], 0.f);
+                    }
+                } else {
 #pragma unroll
                     for (int j = 0; j < 8; ++j) col[c][j] = 0.f;
                 }
@@ -267,6 +385,18 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
 #pragma unroll
         for (int i = 0; i < TW; ++i)
             if (wo0 + i < Wo) {
+                if (BNBWD) {  // acc = d(relu(bn(y1))) at this pixel: mask, store g, accumulate sum g and sum g * xhat
+                    float yv[8];
+                    load8(aux.y_raw + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0, yv);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        float g = (yv[j] * sc[j] + sh[j] > 0.f) ? acc[i][j] : 0.f;
+                        g = __bfloat162float(__float2bfloat16_rn(g));
+                        acc[i][j] = g;
+                        st[j] += g;
+                        st[8 + j] += g * ((yv[j] - mu[j]) * is[j]);
+                    }
+                }
                 store8(y + (((long long)n * Ho + ho) * Wo + wo0 + i) * C + ch0, acc[i]);
                 if (STATS) {
 #pragma unroll
@@ -279,6 +409,8 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
             }
     }
     if (STATS) dw_block_channel_reduce(st, ch0, C, stats);  // reached by every thread of the block (idle tail threads add zeros)
+    if (BNBWD) dw_block_channel_reduce(st, ch0, C, aux.bwd_sums);
+    if (BNIN == 1) dw_bn_publish_and_release(aux, C);  // this block read its coefficients long ago: the ticket goes last
 }
 
 // Strip version of the weight gradient.  A warp owns TWO adjacent channel vectors (lane & 1) and its 16 lane pairs walk
@@ -286,10 +418,10 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
 // partial sums that must be combined live in the same warp: 4 xor-shuffle rounds fold the 16 items, then lanes 0/1 issue
 // the 72 fp32 atomics of their channel vector.  (An earlier version combined threads through shared-memory atomics and
 // spent most of its time serialised on bank conflicts.)
-template <int STRIDE, int TW>
+template <int STRIDE, int TW, bool BNIN = false>
 __global__ void __launch_bounds__(DW_THREADS)
 dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, float* __restrict__ dw, int N, int H, int W,
-                      int C, int Ho, int Wo) {
+                      int C, int Ho, int Wo, const DwBn aux) {
     constexpr int NC = (TW - 1) * STRIDE + 3;
     const int P2 = C >> 4;                       // pairs of channel vectors (host guarantees C % 16 == 0)
     const int lane = threadIdx.x & 31, sub = lane & 1, li = lane >> 1;
@@ -303,6 +435,9 @@ dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, f
     float acc[72];
 #pragma unroll
     for (int i = 0; i < 72; ++i) acc[i] = 0.f;
+    float sc[8], sh[8], mu[8], is[8];
+    if (BNIN) dw_bn_coeffs<2>(aux, ch0, C, sc, sh, mu, is);  // x holds the raw y1: the convolution saw relu(bn(y1))
+    (void)mu; (void)is;
     for (long long item = (gw / P2) * 16 + li; item < nitems; item += istride) {
         long long t = item;
         const int wt_ = (int)(t % tiles_w); t /= tiles_w;
@@ -321,10 +456,12 @@ dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, f
             if (hi < 0 || hi >= H) continue;
             const bf16* row = x + (((long long)n * H + hi) * W) * C + ch0;
             int4 col[NC];
+            bool cok[NC];
 #pragma unroll
             for (int c = 0; c < NC; ++c) {
                 const int wi = wi0 + c;
-                col[c] = (wi >= 0 && wi < W) ? *(const int4*)(row + (long long)wi * C) : make_int4(0, 0, 0, 0);
+                cok[c] = (wi >= 0 && wi < W);
+                col[c] = cok[c] ? *(const int4*)(row + (long long)wi * C) : make_int4(0, 0, 0, 0);
             }
 #pragma unroll
             for (int i = 0; i < TW; ++i) {
@@ -334,6 +471,11 @@ dw_wgrad_strip_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, f
                 for (int kw = 0; kw < 3; ++kw) {
                     float cf[8];
                     bf16x8_to_float(*(bf16x8*)&col[i * STRIDE + kw], cf);
+                    if (BNIN) {
+                        if (!cok[i * STRIDE + kw]) continue;  // zero padding of the normalised activation
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) cf[j] = fmaxf(cf[j] * sc[j] + sh[j], 0.f);
+                    }
 #pragma unroll
                     for (int j = 0; j < 8; ++j) acc[j * 9 + kh * 3 + kw] += gf[j] * cf[j];
                 }
@@ -415,6 +557,22 @@ dw_wgrad_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, float* 
 
 }  // namespace
 
+// grid of the strip weight-gradient kernel: the total warp count must be a multiple of P2 = C/16 (pairs of channel vectors)
+static int dw_wgrad_grid(int N, int Ho, int Wo, int C, int stride) {
+    const int P2 = C / 16;
+    const int warps_per_block = DW_THREADS / 32;
+    int a = P2, b = warps_per_block;
+    while (b) { int t = a % b; a = b; b = t; }
+    const int q = P2 / a;
+    const int TWs = stride == 1 ? 4 : 2;
+    const long long nitems = (long long)N * Ho * ((Wo + TWs - 1) / TWs);
+    long long want = (nitems * P2 / 16 + (long long)warps_per_block * 4 - 1) / ((long long)warps_per_block * 4);  // ~4 items per lane pair
+    const long long cap = (long long)dmp_num_sms();  // 160-190 registers per thread: one 256-thread block per SM
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    return (int)(((want + q - 1) / q) * q);
+}
+
 static int dw_check(const char* name, int N, int H, int W, int C, int stride) {
     DMP_REQUIRE(N > 0 && H > 0 && W > 0 && C > 0, "%s: empty tensor", name);
     DMP_REQUIRE(C % 8 == 0, "%s: C=%d must be a multiple of 8", name, C);
@@ -430,13 +588,13 @@ DMP_API int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y
     if (stride == 1) {
         const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
-        else dw_strip_kernel<bf16, 1, 4, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr, DwBn{});
+        else dw_strip_kernel<bf16, 1, 4, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr, DwBn{});
     } else {
         const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
-        else dw_strip_kernel<bf16, 2, 2, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr);
+        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr, DwBn{});
+        else dw_strip_kernel<bf16, 2, 2, false, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, nullptr, DwBn{});
     }
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
@@ -453,13 +611,13 @@ DMP_API int dmp_dwconv3x3_fwd_colstats(const void* x, const void* w, int w_dtype
     if (stride == 1) {
         const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
-        else dw_strip_kernel<bf16, 1, 4, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats, DwBn{});
+        else dw_strip_kernel<bf16, 1, 4, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats, DwBn{});
     } else {
         const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
-        else dw_strip_kernel<bf16, 2, 2, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);
+        if (w_dtype == 0) dw_strip_kernel<float, 2, 2, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const float*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats, DwBn{});
+        else dw_strip_kernel<bf16, 2, 2, false, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats, DwBn{});
     }
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
@@ -473,13 +631,13 @@ DMP_API int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void
     if (stride == 1) {  // dx = dy (*) flipped taps: the forward strip stencil applied to dy (Ho == H, Wo == W)
         const long long total = (long long)N * H * ((W + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W, nullptr);
-        else dw_strip_kernel<bf16, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, H, W, nullptr);
+        if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W, nullptr, DwBn{});
+        else dw_strip_kernel<bf16, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, H, W, nullptr, DwBn{});
     } else if (stride == 2 && H % 2 == 0 && W % 2 == 0) {
         const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
-        if (w_dtype == 0) dw_dgrad_s2_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, Ho, Wo);
-        else dw_dgrad_s2_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, Ho, Wo);
+        if (w_dtype == 0) dw_dgrad_s2_kernel<float><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, Ho, Wo, DwBn{});
+        else dw_dgrad_s2_kernel<bf16><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)w, (bf16*)dx, N, H, W, C, Ho, Wo, DwBn{});
     } else {
         const long long total = (long long)N * H * W * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
@@ -500,21 +658,9 @@ DMP_API int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N,
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
     if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)C, stream));
     if (C % 16 == 0) {
-        const int P2 = C / 16;
-        const int warps_per_block = DW_THREADS / 32;
-        // total warps must be a multiple of P2
-        int a = P2, b = warps_per_block;
-        while (b) { int t = a % b; a = b; b = t; }
-        const int q = P2 / a;
-        const int TWs = stride == 1 ? 4 : 2;
-        const long long nitems = (long long)N * Ho * ((Wo + TWs - 1) / TWs);
-        long long want = (nitems * P2 / 16 + (long long)warps_per_block * 4 - 1) / ((long long)warps_per_block * 4);  // ~4 items per lane pair
-        const long long cap = (long long)dmp_num_sms();
-        if (want > cap) want = cap;
-        if (want < 1) want = 1;
-        const int grid = (int)(((want + q - 1) / q) * q);
-        if (stride == 1) dw_wgrad_strip_kernel<1, 4><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
-        else dw_wgrad_strip_kernel<2, 2><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo);
+        const int grid = dw_wgrad_grid(N, Ho, Wo, C, stride);
+        if (stride == 1) dw_wgrad_strip_kernel<1, 4><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo, DwBn{});
+        else dw_wgrad_strip_kernel<2, 2><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo, DwBn{});
     } else {
         const int P = C / 8;
         int a = P, b = DW_THREADS;
@@ -531,6 +677,93 @@ DMP_API int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N,
         DMP_REQUIRE(smem <= 48 * 1024, "dmp_dwconv3x3_wgrad: C=%d (not a multiple of 16) is too wide for the fallback kernel", C);
         dw_wgrad_kernel<<<grid, DW_THREADS, smem, stream>>>((const bf16*)dy, (const bf16*)x, dw, N, H, W, C, Ho, Wo, stride);
     }
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Fused entry points for the expand -> bn1 -> relu -> depthwise -> bn2 chain (bf16 weights, bf16 NHWC activations).
+// ---------------------------------------------------------------------------------------------------------------------
+static DwBn dw_bn_args(const double* in_sums, double count, const float* gamma, const float* beta, float eps, float momentum,
+                       float* running_mean, float* running_var, long long* nbt, float* mean_out, float* invstd_out,
+                       const float* mean, const float* invstd, const void* y_raw, double* bwd_sums) {
+    DwBn a;
+    a.sums = in_sums; a.count = count; a.inv_count = count > 0 ? 1.0 / count : 0.0;
+    a.gamma = gamma; a.beta = beta; a.eps = eps; a.momentum = momentum;
+    a.running_mean = running_mean; a.running_var = running_var; a.num_batches_tracked = nbt;
+    a.mean_out = mean_out; a.invstd_out = invstd_out; a.mean = mean; a.invstd = invstd;
+    a.y_raw = (const bf16*)y_raw; a.bwd_sums = bwd_sums;
+    return a;
+}
+
+// y = depthwise3x3(relu(bn1(x_raw))) where bn1's batch sums `in_sums` (double[2C] + ticket, see dmp_bn_sums_bytes) were
+// accumulated by the producer of x_raw; also publishes bn1's mean / invstd / running statistics, clears `in_sums`, and
+// accumulates the batch sums of y into `out_stats` (double[2C], for the BatchNorm that follows the depthwise convolution).
+DMP_API int dmp_dwconv3x3_fwd_bnin_colstats(const void* x_raw, const void* w_bf16, void* y, int N, int H, int W, int C, int stride,
+                                            double* in_sums, const float* gamma, const float* beta, float eps, float momentum,
+                                            float* running_mean, float* running_var, long long* num_batches_tracked,
+                                            float* mean_out, float* invstd_out, double* out_stats, cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_fwd_bnin_colstats", N, H, W, C, stride)) return rc;
+    DMP_REQUIRE(in_sums && mean_out && invstd_out && out_stats, "dmp_dwconv3x3_fwd_bnin_colstats: null buffers");
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    const DwBn a = dw_bn_args(in_sums, (double)N * H * W, gamma, beta, eps, momentum, running_mean, running_var, num_batches_tracked,
+                              mean_out, invstd_out, nullptr, nullptr, nullptr, nullptr);
+    if (stride == 1) {
+        const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
+        dw_strip_kernel<bf16, 1, 4, false, true, 1><<<dmp_ceil_div(total, DW_THREADS), DW_THREADS, 0, stream>>>(
+            (const bf16*)x_raw, (const bf16*)w_bf16, (bf16*)y, N, H, W, C, Ho, Wo, out_stats, a);
+    } else {
+        const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
+        dw_strip_kernel<bf16, 2, 2, false, true, 1><<<dmp_ceil_div(total, DW_THREADS), DW_THREADS, 0, stream>>>(
+            (const bf16*)x_raw, (const bf16*)w_bf16, (bf16*)y, N, H, W, C, Ho, Wo, out_stats, a);
+    }
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// g = mask * depthwise_dgrad(dy) with mask = (bn1(y_raw) > 0), stored bf16, and bwd_sums[0..C) += sum g,
+// bwd_sums[C..2C) += sum g * xhat: the data gradient of the depthwise convolution fused with the reduction phase of the
+// backward of the relu(bn1(.)) that produced its input.  y_raw: [N,H,W,C] (the raw input of bn1).  H, W even for stride 2.
+DMP_API int dmp_dwconv3x3_dgrad_bnbwd(const void* dy, const void* w_bf16, void* g, int N, int H, int W, int C, int stride,
+                                      const void* y_raw, const float* mean, const float* invstd, const float* gamma,
+                                      const float* beta, double* bwd_sums, cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_dgrad_bnbwd", N, H, W, C, stride)) return rc;
+    DMP_REQUIRE(y_raw && mean && invstd && bwd_sums, "dmp_dwconv3x3_dgrad_bnbwd: null buffers");
+    DMP_REQUIRE(stride == 1 || (H % 2 == 0 && W % 2 == 0), "dmp_dwconv3x3_dgrad_bnbwd: stride 2 needs even H, W");
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    const DwBn a = dw_bn_args(nullptr, (double)N * H * W, gamma, beta, 0.f, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr, mean,
+                              invstd, y_raw, bwd_sums);
+    if (stride == 1) {
+        const long long total = (long long)N * H * ((W + 3) / 4) * (C / 8);
+        dw_strip_kernel<bf16, 1, 4, true, false, 0, true><<<dmp_ceil_div(total, DW_THREADS), DW_THREADS, 0, stream>>>(
+            (const bf16*)dy, (const bf16*)w_bf16, (bf16*)g, N, H, W, C, H, W, nullptr, a);
+    } else {
+        const long long total = (long long)N * Ho * ((Wo + 1) / 2) * (C / 8);
+        dw_dgrad_s2_kernel<bf16, true><<<dmp_ceil_div(total, DW_THREADS), DW_THREADS, 0, stream>>>(
+            (const bf16*)dy, (const bf16*)w_bf16, (bf16*)g, N, H, W, C, Ho, Wo, a);
+    }
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// dw += / = sum dy * relu(bn1(x_raw)) taps: the depthwise weight gradient with the normalised input re-created on the fly.
+DMP_API int dmp_dwconv3x3_wgrad_bnin(const void* dy, const void* x_raw, float* dw, int N, int H, int W, int C, int stride,
+                                     int accumulate, const float* mean, const float* invstd, const float* gamma, const float* beta,
+                                     cudaStream_t stream) {
+    if (int rc = dw_check("dmp_dwconv3x3_wgrad_bnin", N, H, W, C, stride)) return rc;
+    DMP_REQUIRE(C % 16 == 0, "dmp_dwconv3x3_wgrad_bnin: C=%d must be a multiple of 16", C);
+    DMP_REQUIRE(mean && invstd, "dmp_dwconv3x3_wgrad_bnin: null statistics");
+    const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * 9 * (size_t)C, stream));
+    const DwBn a = dw_bn_args(nullptr, (double)N * H * W, gamma, beta, 0.f, 0.f, nullptr, nullptr, nullptr, nullptr, nullptr, mean,
+                              invstd, nullptr, nullptr);
+    const int grid = dw_wgrad_grid(N, Ho, Wo, C, stride);
+    if (stride == 1) dw_wgrad_strip_kernel<1, 4, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x_raw, dw, N, H, W, C, Ho, Wo, a);
+    else dw_wgrad_strip_kernel<2, 2, true><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const bf16*)x_raw, dw, N, H, W, C, Ho, Wo, a);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;

@@ -16,6 +16,7 @@
 // ring slots and finally signals the epilogue.  K tails rely on TMA out-of-bounds zero fill; M/N tails are
 // masked in the epilogue.
 #include "tcgen05_common.cuh"
+#include <atomic>
 
 namespace {
 
@@ -29,7 +30,12 @@ struct GemmParams {
     const float* bias;  // per-column (N) fp32 bias, nullable
     int epi;            // 0: store bf16, 1: store fp32, 2: atomic add fp32
     int tma_store;      // epi 0 only: stage the bf16 tile in shared memory and store it with TMA (coalesced full lines)
-    double* stats;      // STATS kernels: [2N] per-column sum and sum of squares of the bf16-rounded outputs, accumulated
+    double* stats;      // ECOL kernels: [2N] per-column sums of the bf16-rounded outputs, accumulated (see the column pass)
+    // ECOL == 2 (data-gradient GEMM feeding a BatchNorm backward): the BatchNorm's input y_raw [M, N] and its coefficients
+    const bf16* aux;
+    long long ld_aux;
+    const float *bn_mean, *bn_invstd, *bn_gamma, *bn_beta;
+    int relu;
 };
 
 // Persistent kernel: CTA b processes work items b, b+gridDim.x, ...  A work item is one 128 x BN output tile of one
@@ -39,12 +45,12 @@ struct GemmParams {
 // 7.7 TB/s x ~1 us / 148 SMs = 50 KB outstanding per SM to stay busy, and a 3-stage ring holds at most two stages of loads
 // (32-64 KB) in the air.  One CTA per SM owns the whole 227 KB, so the ring takes ~200 KB of it: 6 stages at BN=128, 8 below.
 // Narrow tiles (BN <= 64, 20-24 KB per stage) keep two CTAs per SM instead and take 3 stages.
-constexpr int STAT_SMEM_BYTES = 4 * 32 * 33 * 4;  // per epilogue warp: a padded 32 x 32 fp32 transpose tile
+constexpr int STAT_SMEM_BYTES = 8 * 2 * 128 * 4;  // ECOL: per-CTA combine of the epilogue warps' column partials
 constexpr int stg_warp_bytes(int bn) { return (32 * (bn * 2 + 16) + 1023) / 1024 * 1024; }  // output staging per epilogue warp
-constexpr int gemm_stages(int b_rows, bool stats) {
+constexpr int gemm_stages(int b_rows, int ecol) {
     const int per = BM * BK * 2 + b_rows * BK * 2;
-    if (per <= 24 * 1024) return 3;  // + 8-16 KB output staging (+ statistics scratch) stays under half an SM's shared memory
-    const int s = (200 * 1024 - 4 * stg_warp_bytes(b_rows) - (stats ? STAT_SMEM_BYTES : 0)) / per;
+    if (per <= 24 * 1024 && ecol != 2) return 3;  // + 8-16 KB output staging (+ statistics scratch) stays under half an SM's shared memory
+    const int s = (200 * 1024 - (ecol == 2 ? 8 : 4) * stg_warp_bytes(b_rows) - (ecol != 0 ? STAT_SMEM_BYTES : 0)) / per;
     return s > 8 ? 8 : s;
 }
 
@@ -55,16 +61,16 @@ constexpr int gemm_stages(int b_rows, bool stats) {
 constexpr int bres_bytes(int bn) { return bn >= 128 ? 64 * 1024 : 32 * 1024; }   // region for ceil(K/64) blocks of BN x 64 bf16
 constexpr int bres_stages(int bn) { return bn >= 128 ? 6 : 3; }                  // A-only ring (16 KB per stage)
 
-template <int BN, bool A_MN, bool B_MN, bool STATS, bool BRES = false>
+template <int BN, bool A_MN, bool B_MN, int ECOL, bool BRES = false>
 __global__ void __launch_bounds__(NUM_THREADS, BN <= 64 ? 2 : 1)  // narrow tiles keep two CTAs per SM (<= 168 registers)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmD, const GemmParams p) {
+                    const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmY, const GemmParams p) {
     constexpr int A_BYTES = BM * BK * 2;  // 16 KB
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int B_BYTES = B_ROWS * BK * 2;
-    static_assert(!BRES || (!A_MN && !B_MN && !STATS), "resident B is for the plain NT forward GEMM");
+    static_assert(!BRES || (!A_MN && !B_MN), "resident B is for the NT forward GEMM");
     constexpr int STAGE_BYTES = BRES ? A_BYTES : A_BYTES + B_BYTES;
-    constexpr int STAGES = BRES ? bres_stages(BN) : gemm_stages(B_ROWS, STATS);  // shadows the common 3-stage default
+    constexpr int STAGES = BRES ? bres_stages(BN) : gemm_stages(B_ROWS, ECOL);  // shadows the common 3-stage default
     constexpr int RES_BYTES = BRES ? bres_bytes(BN) : 0;
     constexpr uint32_t ACC_COLS = BN < 32 ? 32 : BN;
     constexpr uint32_t TMEM_COLS = 2 * ACC_COLS;  // double-buffered accumulator (power of two: 64/128/256)
@@ -78,13 +84,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     constexpr int STG_WARP_BYTES = (32 * STG_PITCH + 1023) / 1024 * 1024;  // >= the 32 * BN * 2 the TMA layout needs, 1 KB aligned
     uint8_t* bres = smem + STAGES * STAGE_BYTES;             // BRES: the CTA's B panel, K block kb at bres + kb * B_BYTES
     uint8_t* stg = bres + RES_BYTES;
-    uint64_t* full_bar = (uint64_t*)(stg + 4 * STG_WARP_BYTES);
+    // ECOL == 2: a second staging area of the same shape, filled by TMA with the matching tile of the BatchNorm input y_raw
+    constexpr int YSTG_BYTES = ECOL == 2 ? 4 * STG_WARP_BYTES : 0;
+    uint8_t* ystg = stg + 4 * STG_WARP_BYTES;
+    uint64_t* full_bar = (uint64_t*)(stg + 4 * STG_WARP_BYTES + YSTG_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;   // [2]
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;   // [2]
     uint64_t* bres_bar = tmem_empty_bar + 2;        // BRES: the panel has landed
     uint32_t* tmem_ptr_smem = (uint32_t*)(bres_bar + 1);
-    float* stat_smem = (float*)(stg + 4 * STG_WARP_BYTES + 256);  // STATS only (the launch adds STAT_SMEM_BYTES)
+    uint64_t* ybar = (uint64_t*)((uint8_t*)full_bar + 192);  // [4], ECOL == 2: one per epilogue warp (the barrier block is 256 bytes)
+    float* stat_smem = (float*)(stg + 4 * STG_WARP_BYTES + YSTG_BYTES + 256);  // ECOL only (the launch adds STAT_SMEM_BYTES)
 
     const int warp = threadIdx.x >> 5;
     const int lane = threadIdx.x & 31;
@@ -105,6 +115,10 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             mbar_init(&tmem_empty_bar[b], 4);  // one arrive per epilogue warp
         }
         mbar_init(bres_bar, 1);
+        if (ECOL == 2) {
+            tma_prefetch_desc(&tmY);
+            for (int b = 0; b < 4; ++b) mbar_init(&ybar[b], 1);
+        }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(tmem_ptr_smem, TMEM_COLS);
@@ -215,12 +229,42 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     } else {
         // ------------------------------------------------------------------ epilogue (warps 2..5)
         const int lane_grp = warp & 3;  // TMEM lane quarter this warp may access
-        // STATS: this CTA's tiles all share one n0 (the host makes gridDim.x a multiple of n_tiles), so lane l keeps the running
-        // column sums of columns n0 + 32 c + l in registers across all of its tiles and issues its atomics once, at the end.
+        // ECOL (column pass): this CTA's tiles all share one n0 (the host makes gridDim.x a multiple of n_tiles), so a lane keeps
+        // the running sums of ITS two columns per panel in registers across all of its tiles and issues its atomics once, at the end.
         constexpr int NCHUNK = BN >= 32 ? BN / 32 : 1;
-        float st1[NCHUNK], st2[NCHUNK];
+        constexpr int NPAN = BN / PW;          // output panels per tile (PW columns each)
+        constexpr int WPR = PW / 2;            // 32-bit words (column pairs) per staged panel row: 32 or 16
+        constexpr int RPI = 32 / WPR;          // staged rows covered by one warp instruction: 1 or 2
+        const int cw = lane % WPR, crs = lane / WPR;
+        uint32_t cxo[8];                       // byte offset of the lane's word inside a staged row, per swizzle phase t
 #pragma unroll
-        for (int c = 0; c < NCHUNK; ++c) st1[c] = st2[c] = 0.f;
+        for (int t = 0; t < 8; ++t) cxo[t] = ((((uint32_t)cw >> 2) ^ (uint32_t)t) << 4) + ((uint32_t)cw & 3) * 4;
+        float cs1[NPAN][2], cs2[NPAN][2];      // [panel][column of the pair]: sum / second statistic
+        float cmu[NPAN][2], cis[NPAN][2], csc[NPAN][2], csh[NPAN][2];  // ECOL == 2: BatchNorm coefficients of the lane's columns
+        uint32_t ycount = 0;                   // ECOL == 2: y_raw slabs consumed so far (parity of ybar)
+#pragma unroll
+        for (int pn = 0; pn < NPAN; ++pn)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                cs1[pn][e] = cs2[pn][e] = 0.f;
+                cmu[pn][e] = cis[pn][e] = csc[pn][e] = csh[pn][e] = 0.f;
+            }
+        if (ECOL == 2 && blockIdx.x < num_items) {
+            const int n0c = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;
+#pragma unroll
+            for (int pn = 0; pn < NPAN; ++pn)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const int col = n0c + pn * PW + 2 * cw + e;
+                    if (col < p.N) {
+                        const float g = p.bn_gamma ? p.bn_gamma[col] : 1.f, b = p.bn_beta ? p.bn_beta[col] : 0.f;
+                        cmu[pn][e] = p.bn_mean[col];
+                        cis[pn][e] = p.bn_invstd[col];
+                        csc[pn][e] = g * cis[pn][e];                       // same expressions as the forward apply kernels
+                        csh[pn][e] = b - cmu[pn][e] * g * cis[pn][e];
+                    }
+                }
+        }
         int local = 0;
         for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
             const int tile = item % tiles_mn;
@@ -228,6 +272,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             const int buf = local & 1;
             const uint32_t acc_ph = (local >> 1) & 1;
             const int row = m0 + lane_grp * 32 + lane;
+            if (ECOL == 2) {
+                // fetch this warp's 32 x BN slab of y_raw while the tile's MMAs are still running (the previous tile's column
+                // pass, the last reader of ystg, is behind us in program order)
+                __syncwarp();
+                if (lane == 0 && m0 + lane_grp * 32 < p.M) {
+                    uint32_t bytes = 0;
+#pragma unroll
+                    for (int pn = 0; pn < BN / PW; ++pn)
+                        if (n0 + pn * PW < p.N) bytes += 32 * PW * 2;
+                    mbar_expect_tx(&ybar[lane_grp], bytes);
+#pragma unroll
+                    for (int pn = 0; pn < BN / PW; ++pn)
+                        if (n0 + pn * PW < p.N)
+                            tma_load_2d(ystg + lane_grp * STG_WARP_BYTES + pn * (32 * PW * 2), &tmY, &ybar[lane_grp], n0 + pn * PW,
+                                        m0 + lane_grp * 32);
+                }
+            }
             mbar_wait(&tmem_full_bar[buf], acc_ph);
             tcgen05_fence_after();
             const uint32_t taddr_row = tmem_base + buf * ACC_COLS + ((uint32_t)(lane_grp * 32) << 16);
@@ -255,28 +316,6 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int c0 = 0; c0 < BN; c0 += 32) {
                 if (n0 + c0 >= p.N) break;  // warp-uniform
                 uint32_t* r = rall[c0 / 32];
-                if (STATS) {
-                    // column sums over this warp's 32 rows: transpose through a padded shared tile (conflict-free both ways)
-                    float* tr = stat_smem + lane_grp * (32 * 33);
-                    const bool rowok = row < p.M;
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        float q = __uint_as_float(r[j]);
-                        q = (rowok && n0 + c0 + j < p.N) ? __bfloat162float(__float2bfloat16_rn(q)) : 0.f;
-                        tr[lane * 33 + j] = q;
-                    }
-                    __syncwarp();
-                    float a = 0.f, b = 0.f;
-#pragma unroll
-                    for (int rr = 0; rr < 32; ++rr) {
-                        const float q = tr[rr * 33 + lane];
-                        a += q;
-                        b += q * q;
-                    }
-                    __syncwarp();
-                    st1[c0 / 32] += a;
-                    st2[c0 / 32] += b;
-                }
                 if (row < p.M) {
                     const int n = n0 + c0;
                     float v[32];
@@ -342,6 +381,66 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                 }
             }
+            if (ECOL != 0) {
+                // Column pass over the staged bf16 tile (this warp's 32 rows x BN columns, SWIZZLE_128B / 64B panels): lane cw
+                // owns the column pair (2cw, 2cw+1) of every panel, i.e. one 32-bit word per staged row.  Across a warp
+                // instruction the words of one row (two rows when PW == 32) cover 128 contiguous, swizzle-permuted bytes: every
+                // bank once.  No shuffles, no transpose.  The row loop is fully unrolled over compile-time row numbers, so the
+                // XOR swizzle folds into eight (four) per-lane base addresses computed once per kernel and every row is
+                // LDS [base_t + imm] + 6 arithmetic instructions (an earlier rolled version recomputed the swizzle per row:
+                // ~20 instructions and two branches per row, and the epilogue warps -- one per scheduler -- became the kernel's bound).
+                //   ECOL == 1: cs1 += y, cs2 += y^2                      (BatchNorm batch sums of the bf16-rounded output)
+                //   ECOL == 2: the tile is dA of a convolution whose input was act(BatchNorm(y_raw)); the ReLU mask is
+                //              recomputed from y_raw (coalesced 128-byte row reads), applied IN the staged tile, and
+                //              cs1 += g, cs2 += g * xhat -- the two reductions of the BatchNorm backward.
+                __syncwarp();
+                int rows_valid = p.M - (m0 + lane_grp * 32);
+                if (rows_valid > 32) rows_valid = 32;
+                const uint32_t stg_s = smem_u32(my_stg);
+                const uint32_t ydelta = smem_u32(ystg + lane_grp * STG_WARP_BYTES) - stg_s;  // same swizzled layout, other buffer
+                if (ECOL == 2 && rows_valid > 0) {
+                    mbar_wait(&ybar[lane_grp], ycount & 1);  // the y_raw slab has landed
+                    ++ycount;
+                }
+#pragma unroll
+                for (int pn = 0; pn < NPAN; ++pn) {
+                    if (n0 + pn * PW >= p.N) break;  // warp-uniform
+                    const bool colok = n0 + pn * PW + 2 * cw < p.N;  // N % 8 == 0: a pair is valid or invalid as a whole
+                    const uint32_t pbase = stg_s + pn * (32 * PW * 2) + crs * (PW * 2);
+                    float a1 = 0.f, a2 = 0.f, b1 = 0.f, b2 = 0.f;
+#pragma unroll
+                    for (int r0 = 0; r0 < 32; r0 += RPI) {
+                        const int t = PW == 64 ? (r0 & 7) : ((r0 >> 1) & 3);
+                        const uint32_t addr = pbase + cxo[t] + r0 * (PW * 2);
+                        const bool rowok = r0 + crs < rows_valid;  // all true except in the last row tile
+                        uint32_t w;
+                        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(w) : "r"(addr));
+                        float lo = __uint_as_float(w << 16), hi = __uint_as_float(w & 0xffff0000u);
+                        if (!rowok) lo = hi = 0.f;  // rows past M were never staged
+                        if (ECOL == 1) {
+                            a1 += lo; a2 = fmaf(lo, lo, a2);
+                            b1 += hi; b2 = fmaf(hi, hi, b2);
+                        } else {
+                            uint32_t yw;
+                            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(yw) : "r"(addr + ydelta));
+                            if (!rowok) yw = 0;
+                            const float ylo = __uint_as_float(yw << 16), yhi = __uint_as_float(yw & 0xffff0000u);
+                            if (p.relu) {
+                                if (!(fmaf(ylo, csc[pn][0], csh[pn][0]) > 0.f)) lo = 0.f;
+                                if (!(fmaf(yhi, csc[pn][1], csh[pn][1]) > 0.f)) hi = 0.f;
+                                const uint32_t wm = (__float_as_uint(lo) >> 16) | (__float_as_uint(hi) & 0xffff0000u);
+                                asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(wm) : "memory");
+                            }
+                            a1 += lo; a2 = fmaf(lo, (ylo - cmu[pn][0]) * cis[pn][0], a2);
+                            b1 += hi; b2 = fmaf(hi, (yhi - cmu[pn][1]) * cis[pn][1], b2);
+                        }
+                    }
+                    if (colok) {  // lanes past N read stale staging columns: drop them
+                        cs1[pn][0] += a1; cs2[pn][0] += a2;
+                        cs1[pn][1] += b1; cs2[pn][1] += b2;
+                    }
+                }
+            }
             if (p.tma_store == 1) fence_proxy_async();  // generic-proxy smem writes -> visible to the TMA (async proxy)
             __syncwarp();
             if (p.tma_store == 2) {
@@ -370,14 +469,31 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             }
         }
         if (p.tma_store == 1 && lane == 0) tma_store_wait_all();  // shared memory must outlive the last bulk store
-        if (STATS && blockIdx.x < num_items) {
-            const int n0 = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;
+        if (ECOL != 0) {
+            // Combine the four epilogue warps' partials (and the two half-warps when PW == 32) in shared memory and issue ONE
+            // double atomic per column and statistic per CTA: with every lane adding on its own, ~2400 atomics landed on each of
+            // the 48 addresses of a 24-channel layer and the serialisation at L2 cost 35 us.
+            float* part = stat_smem + (lane_grp * RPI + crs) * (2 * BN);
 #pragma unroll
-            for (int c = 0; c < NCHUNK; ++c) {
-                const int col = n0 + c * 32 + lane;
+            for (int pn = 0; pn < NPAN; ++pn)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    part[pn * PW + 2 * cw + e] = cs1[pn][e];
+                    part[BN + pn * PW + 2 * cw + e] = cs2[pn][e];
+                }
+            asm volatile("bar.sync 1, 128;" ::: "memory");  // the four epilogue warps only
+            const int e = (warp - 2) * 32 + lane;
+            if (blockIdx.x < num_items && e < BN) {
+                const int col = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN + e;
+                float t1 = 0.f, t2 = 0.f;
+#pragma unroll
+                for (int g = 0; g < 4 * RPI; ++g) {
+                    t1 += stat_smem[g * (2 * BN) + e];
+                    t2 += stat_smem[g * (2 * BN) + BN + e];
+                }
                 if (col < p.N) {
-                    atomicAdd(p.stats + col, (double)st1[c]);
-                    atomicAdd(p.stats + p.N + col, (double)st2[c]);
+                    atomicAdd(p.stats + col, (double)t1);
+                    atomicAdd(p.stats + p.N + col, (double)t2);
                 }
             }
         }
@@ -420,29 +536,30 @@ const int g_gemm_store_mode = [] {
     return (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
 }();
 
-template <int BN, bool A_MN, bool B_MN, bool STATS = false, bool BRES = false>
+template <int BN, bool A_MN, bool B_MN, int ECOL = 0, bool BRES = false>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int ring_bytes = BRES ? bres_stages(BN) * (BM * BK * 2) + bres_bytes(BN)
-                                    : gemm_stages(B_ROWS, STATS) * (BM * BK * 2 + B_ROWS * BK * 2);
-    constexpr int smem_bytes = ring_bytes + 1024 /*align slack*/ + 4 * stg_warp_bytes(BN) /*output staging*/ + 256 /*barriers*/ +
-                               (STATS ? STAT_SMEM_BYTES : 0);
-    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, STATS, BRES>;
-    static bool configured = false;  // per template instantiation; attribute is per-device-context idempotent
-    static int configured_dev_mask = 0;
+                                    : gemm_stages(B_ROWS, ECOL) * (BM * BK * 2 + B_ROWS * BK * 2);
+    constexpr int smem_bytes = ring_bytes + 1024 /*align slack*/ + (ECOL == 2 ? 8 : 4) * stg_warp_bytes(BN) /*output (+ y_raw) staging*/ +
+                               256 /*barriers*/ + (ECOL != 0 ? STAT_SMEM_BYTES : 0);
+    auto kern = gemm_tcgen05_kernel<BN, A_MN, B_MN, ECOL, BRES>;
+    // per template instantiation and per device; DataParallel replicas call this from one thread per device, so the "already
+    // configured" mask is atomic (setting the attribute twice is harmless, a torn read-modify-write is not)
+    static std::atomic<unsigned long long> configured_dev_mask{0};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (!configured || !(configured_dev_mask & (1 << dev))) {
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (!(configured_dev_mask.load(std::memory_order_acquire) & bit)) {
         DMP_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-        configured = true;
-        configured_dev_mask |= (1 << dev);
+        configured_dev_mask.fetch_or(bit, std::memory_order_release);
     }
     GemmParams q = p;
     // bf16 outputs leave through TMA when the rows are 16-byte aligned: box = {one panel of PW columns, one epilogue warp's 32 rows}
     CUtensorMap tmD = tmA;
     q.tma_store = 0;
-    if (p.epi == 0 && (p.ldd & 7) == 0 && (p.N & 7) == 0 && ((uintptr_t)p.D & 15) == 0 && g_gemm_store_mode != 0) {
-        q.tma_store = g_gemm_store_mode;
+    if (p.epi == 0 && (p.ldd & 7) == 0 && (p.N & 7) == 0 && ((uintptr_t)p.D & 15) == 0 && (g_gemm_store_mode != 0 || ECOL != 0)) {
+        q.tma_store = ECOL != 0 ? 1 : g_gemm_store_mode;  // the column pass reads the swizzled staging of mode 1
         if (q.tma_store == 1) {
             constexpr int PW = BN >= 64 ? 64 : BN;
             if (int rc = make_tmap_2d(&tmD, p.D, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldd, PW, 32,
@@ -457,11 +574,19 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     const int ctas_per_sm = smem_bytes <= 110 * 1024 ? 2 : 1;
     long long grid = (long long)dmp_num_sms() * ctas_per_sm;
     if (grid > items) grid = items;
-    if (STATS || BRES) {  // every tile of a CTA must have the same n0: the item stride has to be a multiple of n_tiles
+    if (ECOL != 0 || BRES) {  // every tile of a CTA must have the same n0: the item stride has to be a multiple of n_tiles
         DMP_REQUIRE(splits == 1 && q.n_tiles <= grid, "gemm statistics epilogue: %d column tiles do not fit the grid", q.n_tiles);
         grid = grid / q.n_tiles * q.n_tiles;
     }
-    kern<<<(int)grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, tmD, q);
+    if (ECOL != 0) DMP_REQUIRE(q.tma_store == 1, "gemm column-pass epilogue needs the TMA-store staging (N and ldd multiples of 8, 16-byte aligned D)");
+    CUtensorMap tmY = tmA;
+    if (ECOL == 2) {
+        constexpr int PW = BN >= 64 ? 64 : BN;
+        if (int rc = make_tmap_2d(&tmY, p.aux, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ld_aux, PW, 32,
+                                  PW == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
+            return rc;
+    }
+    kern<<<(int)grid, NUM_THREADS, smem_bytes, stream>>>(tmA, tmB, tmD, tmY, q);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
@@ -515,6 +640,7 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
     p.k_blocks_per_split = dmp_ceil_div(total_kb, splits);
     splits = dmp_ceil_div(total_kb, p.k_blocks_per_split);  // no empty splits
     p.D = D; p.ldd = ldd; p.bias = bias; p.epi = out_mode; p.stats = nullptr;
+    p.aux = nullptr; p.ld_aux = 0; p.bn_mean = p.bn_invstd = p.bn_gamma = p.bn_beta = nullptr; p.relu = 0;
 
     if (!a_mn && !b_mn) {
         // resident-B variant: whole [bn x K] panel in shared memory, loaded once per CTA (DMP_GEMM_BRES=0 disables).  Measured:
@@ -522,9 +648,9 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
         static const bool use_bres = [] { const char* e = getenv("DMP_GEMM_BRES"); return e == nullptr || e[0] != '0'; }();
         if (use_bres && splits == 1 && (long long)total_kb * bn * BK * 2 <= bres_bytes(bn) && dmp_ceil_div(N, bn) <= dmp_num_sms()) {
             switch (bn) {
-                case 32: return launch_gemm<32, false, false, false, true>(tmA, tmB, p, 1, stream);
-                case 64: return launch_gemm<64, false, false, false, true>(tmA, tmB, p, 1, stream);
-                default: return launch_gemm<128, false, false, false, true>(tmA, tmB, p, 1, stream);
+                case 32: return launch_gemm<32, false, false, 0, true>(tmA, tmB, p, 1, stream);
+                case 64: return launch_gemm<64, false, false, 0, true>(tmA, tmB, p, 1, stream);
+                default: return launch_gemm<128, false, false, 0, true>(tmA, tmB, p, 1, stream);
             }
         }
         return dispatch_bn<false, false>(bn, tmA, tmB, p, splits, stream);
@@ -547,11 +673,45 @@ DMP_API int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, 
     p.M = M; p.N = N; p.K = K;
     p.k_blocks_per_split = dmp_ceil_div(K, BK);
     p.D = D; p.ldd = ldd; p.bias = nullptr; p.epi = 0; p.stats = stats;
-    switch (bn) {
-        case 32: return launch_gemm<32, false, false, true>(tmA, tmB, p, 1, stream);
-        case 64: return launch_gemm<64, false, false, true>(tmA, tmB, p, 1, stream);
-        default: return launch_gemm<128, false, false, true>(tmA, tmB, p, 1, stream);
+    p.aux = nullptr; p.ld_aux = 0; p.bn_mean = p.bn_invstd = p.bn_gamma = p.bn_beta = nullptr; p.relu = 0;
+    static const bool use_bres = [] { const char* e = getenv("DMP_GEMM_BRES"); return e == nullptr || e[0] != '0'; }();
+    if (use_bres && (long long)p.k_blocks_per_split * bn * BK * 2 <= bres_bytes(bn) && dmp_ceil_div(N, bn) <= dmp_num_sms()) {
+        switch (bn) {
+            case 32: return launch_gemm<32, false, false, 1, true>(tmA, tmB, p, 1, stream);
+            case 64: return launch_gemm<64, false, false, 1, true>(tmA, tmB, p, 1, stream);
+            default: return launch_gemm<128, false, false, 1, true>(tmA, tmB, p, 1, stream);
+        }
     }
+    switch (bn) {
+        case 32: return launch_gemm<32, false, false, 1>(tmA, tmB, p, 1, stream);
+        case 64: return launch_gemm<64, false, false, 1>(tmA, tmB, p, 1, stream);
+        default: return launch_gemm<128, false, false, 1>(tmA, tmB, p, 1, stream);
+    }
+}
+
+// Data-gradient GEMM of a 1x1 convolution whose INPUT was act(BatchNorm(y_raw)):  G[M,N] (bf16) = mask * (A[M,K] * B[K,N])
+// with mask = (y_raw * scale + shift > 0) when relu != 0 (else 1), and stats[0..N) += sum_m G, stats[N..2N) += sum_m G * xhat
+// (xhat = (y_raw - mean) * invstd): the two reductions the BatchNorm backward needs come out of the producer of its incoming
+// gradient, so that backward is one elementwise pass (dmp_bn_bwd_dx_sums) instead of reduce -> grid barrier -> dx.
+// A = dY [M,K] K-major, B = W [K,N] N-contiguous (layout NN of dmp_gemm_bf16).  N, ldd, ld_y multiples of 8.
+DMP_API int dmp_gemm_bf16_dgrad_bnbwd(const void* A, long long lda, const void* B, long long ldb, void* G, long long ldd, int M, int N,
+                                      int K, const void* y_raw, long long ld_y, const float* mean, const float* invstd,
+                                      const float* gamma, const float* beta, int relu, double* stats, cudaStream_t stream) {
+    DMP_REQUIRE(M > 0 && N > 0 && K > 0 && stats != nullptr && y_raw != nullptr && mean != nullptr && invstd != nullptr,
+                "dmp_gemm_bf16_dgrad_bnbwd: bad arguments");
+    DMP_REQUIRE((ld_y & 7) == 0 && ((uintptr_t)y_raw & 15) == 0, "dmp_gemm_bf16_dgrad_bnbwd: y_raw rows must be 16-byte aligned");
+    int bn = N > 64 ? 128 : 64;
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM)) return rc;
+    if (int rc = make_tmap_2d(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK)) return rc;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.k_blocks_per_split = dmp_ceil_div(K, BK);
+    p.D = G; p.ldd = ldd; p.bias = nullptr; p.epi = 0; p.stats = stats;
+    p.aux = (const bf16*)y_raw; p.ld_aux = ld_y; p.bn_mean = mean; p.bn_invstd = invstd; p.bn_gamma = gamma; p.bn_beta = beta;
+    p.relu = relu;
+    if (bn == 64) return launch_gemm<64, false, true, 2>(tmA, tmB, p, 1, stream);
+    return launch_gemm<128, false, true, 2>(tmA, tmB, p, 1, stream);
 }
 
 // ------------------------------------------------------------------ CUDA-core oracle (tests / debugging only)

@@ -49,8 +49,8 @@ class Block(nn.Module):
         return getattr(self, "bn%d" % i) if self.batchnorm else None
 
     def forward(self, x):
-        out = OF.conv_bn_act(x, self.conv1, self._bn(1), relu=True)
-        out = OF.conv_bn_act(out, self.conv2, self._bn(2), relu=True)
+        # expand -> bn1 -> relu -> depthwise -> bn2 -> relu: one fused chain on the kernel path; its output feeds conv3 only
+        out = OF.expand_dw_bn_act(x, self.conv1, self._bn(1), self.conv2, self._bn(2), single_consumer=True)
         if self.stride != 1:
             return OF.conv_bn_act(out, self.conv3, self._bn(3), relu=False)
         if len(self.shortcut) == 0:

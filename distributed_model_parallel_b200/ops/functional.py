@@ -93,8 +93,76 @@ def weight_bf16(w: torch.Tensor) -> torch.Tensor:
     return w.detach().to(torch.bfloat16)
 
 
-def _deliver_grad(param: Optional[torch.Tensor], writer):
+class _SideStreams:
+    """One side stream per device for weight-gradient kernels, joined back into the stream that ran backward by a callback
+    queued on the autograd engine (so ``.grad`` is complete when ``backward()`` returns, also inside a CUDA-graph capture)."""
+
+    NSIDE = max(1, int(os.environ.get("DMP_WGRAD_STREAMS", "2")))  # side streams per device, used round-robin
+
+    def __init__(self):
+        self.streams = {}
+        self.pending = {}      # device index -> [main stream, side streams...] with unjoined work
+        self._queued = False
+        self._rr = 0
+
+    def side(self, dev):
+        sts = self.streams.get(dev.index)
+        if sts is None:
+            sts = [torch.cuda.Stream(device=dev) for _ in range(self.NSIDE)]
+            self.streams[dev.index] = sts
+        self._rr = (self._rr + 1) % len(sts)
+        return sts[self._rr]
+
+    def fork(self, dev):
+        """A side stream ordered after everything issued so far on the current stream of ``dev``."""
+        main = torch.cuda.current_stream(dev)
+        side = self.side(dev)
+        if main.cuda_stream == side.cuda_stream:
+            return None
+        side.wait_stream(main)
+        if dev.index not in self.pending or not self._queued:
+            self.pending[dev.index] = [main] + list(self.streams[dev.index])
+            if not self._queued:
+                try:
+                    torch.autograd.Variable._execution_engine.queue_callback(self.join_all)
+                    self._queued = True
+                except RuntimeError:  # not inside a backward pass (direct call): the caller joins
+                    pass
+        return side
+
+    def join_all(self):
+        self._queued = False
+        for idx, sts in self.pending.items():
+            main = sts[0]
+            cur = torch.cuda.current_stream(torch.device("cuda", idx))
+            for side in sts[1:]:
+                main.wait_stream(side)
+                if cur.cuda_stream != main.cuda_stream:  # backward() was called from another stream than the forward ran on
+                    cur.wait_stream(side)
+        self.pending.clear()
+
+    def gradient_streams(self, dev):
+        """Every stream that may still be writing gradients on ``dev`` in the running backward pass (the stream backward runs
+        on and the side streams): a collective launched from a gradient-ready callback must order itself after all of them."""
+        return list(self.pending.get(dev.index, ()))
+
+
+_tls_side = threading.local()
+
+
+def side_streams() -> _SideStreams:
+    # one manager per Python thread: DataParallel replicas run backward on one autograd thread per device
+    m = getattr(_tls_side, "m", None)
+    if m is None:
+        m = _tls_side.m = _SideStreams()
+    return m
+
+
+def _deliver_grad(param: Optional[torch.Tensor], writer, side_inputs=()):
     """Produce the gradient of ``param``.
+
+    ``side_inputs``: the tensors the writer's kernels read.  When given (and the side stream is enabled) the kernels are launched
+    on the per-device side stream, forked from the current stream, so they overlap with the data-gradient chain.
 
     ``writer(dst, accumulate)`` launches the kernel(s) writing the fp32 gradient into ``dst``.
     If ``param.grad`` is a pre-allocated fp32 buffer flagged ``_dmp_direct`` (a Reducer bucket view), the
@@ -105,9 +173,19 @@ def _deliver_grad(param: Optional[torch.Tensor], writer):
         return None
     g = param.grad
     if g is not None and getattr(param, "_dmp_direct", False) and g.dtype == torch.float32 and g.is_contiguous():
-        writer(g, True)
-        for cb in grad_ready_callbacks:
-            cb(param)
+        side = side_streams().fork(g.device) if (_WGRAD_SIDE and side_inputs and g.is_cuda) else None
+        if side is None:
+            writer(g, True)
+            for cb in grad_ready_callbacks:
+                cb(param)
+            return None
+        with torch.cuda.stream(side):
+            for t in side_inputs:
+                if t is not None:
+                    t.record_stream(side)  # the caching allocator must not hand these out again before the side work is done
+            writer(g, True)
+            for cb in grad_ready_callbacks:  # a bucket launched from here orders itself after the side stream
+                cb(param)
         return None
     dst = torch.empty_like(param, dtype=torch.float32, memory_format=torch.contiguous_format)
     writer(dst, False)
@@ -204,8 +282,15 @@ def _conv_fwd_cuda(x, w, conv, kind, stats=None):
     return y.contiguous(memory_format=torch.channels_last), x
 
 
-def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
-    """dy: [N,Cout,Ho,Wo] channels_last bf16. Returns (dx or None, dw_writer)."""
+def _link_usable(link, x) -> bool:
+    """Can this convolution's data-gradient kernel take over the BatchNorm-backward reductions of the op that produced x?"""
+    return (link is not None and _FUSE_BN_BWD and link.consumers == 1 and link.y_raw is not None
+            and link.y_raw.shape == x.shape and x.shape[1] % 8 == 0)
+
+
+def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx, link_in=None):
+    """dy: [N,Cout,Ho,Wo] channels_last bf16. Returns (dx or None, dw_writer).  With a usable ``link_in`` the returned dx is
+    the ReLU-masked gradient g and the producer's BatchNorm reductions have been accumulated (link_in.reduced)."""
     lib = _k()
     sp = _sp()
     N = x.shape[0]
@@ -217,8 +302,17 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
         if need_dx:
             wb = weight_bf16(w)
             dxs = _cl_empty(N, cin, H, W, x.device)
-            _ck(lib.dmp_gemm_bf16(1, dy.data_ptr(), cout, wb.data_ptr(), cin, dxs.data_ptr(), cin, M, cin, cout, None, 0, 1,
-                                  sp), "conv1x1 dgrad gemm")
+            if conv.stride == (1, 1) and _link_usable(link_in, x):
+                L = link_in
+                _ck(lib.dmp_gemm_bf16_dgrad_bnbwd(dy.data_ptr(), cout, wb.data_ptr(), cin, dxs.data_ptr(), cin, M, cin, cout,
+                                                  L.y_raw.data_ptr(), cin, L.mean.data_ptr(), L.invstd.data_ptr(),
+                                                  _native.ptr(L.gamma), _native.ptr(L.beta), 1 if L.relu else 0,
+                                                  L.bsums.data_ptr(), sp), "conv1x1 dgrad gemm + bn-bwd reductions")
+                L.reduced = True
+                _note("conv_pw:dgrad+bnbwd")
+            else:
+                _ck(lib.dmp_gemm_bf16(1, dy.data_ptr(), cout, wb.data_ptr(), cin, dxs.data_ptr(), cin, M, cin, cout, None, 0, 1,
+                                      sp), "conv1x1 dgrad gemm")
             if conv.stride != (1, 1):
                 s0, s1 = conv.stride
                 Hin, Win = conv._dmp_in_hw
@@ -232,7 +326,7 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
             if not accumulate:
                 dst.zero_()
             _ck(lib.dmp_gemm_bf16(2, dy.data_ptr(), cout, x.data_ptr(), cin, dst.data_ptr(), cin, cout, cin, M, None, 2, 0,
-                                  sp), "conv1x1 wgrad gemm")
+                                  _sp()), "conv1x1 wgrad gemm")
 
         return dx, write_dw
     if kind == "dw":
@@ -244,7 +338,7 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
             _ck(lib.dmp_dwconv3x3_dgrad(dy.data_ptr(), wb.data_ptr(), 1, dx.data_ptr(), N, H, W, C, s, sp), "dwconv dgrad")
 
         def write_dw(dst, accumulate):
-            _ck(lib.dmp_dwconv3x3_wgrad(dy.data_ptr(), x.data_ptr(), dst.data_ptr(), N, H, W, C, s, 1 if accumulate else 0, sp),
+            _ck(lib.dmp_dwconv3x3_wgrad(dy.data_ptr(), x.data_ptr(), dst.data_ptr(), N, H, W, C, s, 1 if accumulate else 0, _sp()),
                 "dwconv wgrad")
 
         return dx, write_dw
@@ -258,7 +352,7 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
 
         def write_dw(dst, accumulate):
             _ck(lib.dmp_stem_conv_wgrad(dy.data_ptr(), x.data_ptr(), layout, dst.data_ptr(), N, cin, H, W, conv.out_channels,
-                                        kh, kw, s, p, 1 if accumulate else 0, sp), "stem conv wgrad")
+                                        kh, kw, s, p, 1 if accumulate else 0, _sp()), "stem conv wgrad")
 
         return None, write_dw
     if kind == "igemm":
@@ -278,7 +372,7 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx):
 
         def write_dw(dst, accumulate):
             dwp = torch.zeros((cout, kh * kw * cin), device=x.device, dtype=torch.float32)
-            _ck(lib.dmp_conv_igemm_wgrad(dy.data_ptr(), x.data_ptr(), dwp.data_ptr(), N, H, W, cin, cout, kh, kw, conv.padding[0], sp),
+            _ck(lib.dmp_conv_igemm_wgrad(dy.data_ptr(), x.data_ptr(), dwp.data_ptr(), N, H, W, cin, cout, kh, kw, conv.padding[0], _sp()),
                 "conv igemm wgrad")
             g = dwp.view(cout, kh, kw, cin).permute(0, 3, 1, 2)
             if accumulate:
@@ -316,9 +410,35 @@ def _bn_workspace(bn, which: str, C: int, dev):
     return ws
 
 
-# Opt-in (DMP_BN_EPILOGUE_STATS=1).  bench/epilogue_stats_bench.py: with the present register->global GEMM epilogue the statistics
-# cost the producer 3-23 us per layer, about what the lighter BatchNorm pass saves; it pays once the epilogue is TMA-stored.
-_EPILOGUE_STATS = os.environ.get("DMP_BN_EPILOGUE_STATS", "0") == "1"
+# BatchNorm batch statistics from the producing convolution's epilogue (DMP_BN_EPILOGUE_STATS=0 disables): the GEMM reads its
+# staged bf16 output tile column-wise out of shared memory, the depthwise stencil reduces per block; the normalisation is then
+# one elementwise pass (dmp_bn_apply_sums) instead of the cooperative statistics -> grid barrier -> apply kernel.
+_EPILOGUE_STATS = os.environ.get("DMP_BN_EPILOGUE_STATS", "1") == "1"
+# Opt-in fusions (numerically verified, tests/test_gpu_fused_chain.py; measured slower than the separate kernels at batch 128 on
+# B200, profiles/README.md): DMP_FUSE_BN_CHAIN=1 runs expand -> bn1 -> relu -> depthwise -> bn2 -> relu as one chain in which
+# relu(bn1(.)) is applied while the stencil loads its input (the register-bound stencil pays more for the extra arithmetic than
+# the saved elementwise pass costs); DMP_FUSE_BN_BWD=1 lets the consumer's data-gradient kernel produce a BatchNorm's backward
+# reductions (the GEMM epilogue warps, one per scheduler, become the kernel's bound).
+_FUSE_CHAIN = os.environ.get("DMP_FUSE_BN_CHAIN", "0") == "1"
+_FUSE_BN_BWD = os.environ.get("DMP_FUSE_BN_BWD", "0") == "1"
+# Weight-gradient kernels run on a side stream (DMP_WGRAD_SIDE_STREAM=0 disables): the data-gradient chain is the critical
+# path of backward, every kernel of a batch-128 step is latency- rather than throughput-bound, and the weight gradient of a
+# layer depends on nothing that follows it -- so it overlaps with the next BatchNorm backward / data gradient.
+_WGRAD_SIDE = os.environ.get("DMP_WGRAD_SIDE_STREAM", "1") == "1"
+
+
+class _BnLink:
+    """Hand-over between an op that ends in act(BatchNorm(y_raw)) and the single convolution that consumes its output.
+
+    The consumer's data-gradient kernel can apply the ReLU mask and accumulate the BatchNorm backward's two reductions
+    (sum g, sum g*xhat) in its own epilogue; it then sets ``reduced`` and the producer's backward is a single elementwise pass.
+    Only valid when the activation has exactly one consumer (``consumers`` is counted at forward time and checked at backward
+    time); models declare that with ``conv_bn_act(..., single_consumer=True)``."""
+    __slots__ = ("y_raw", "mean", "invstd", "gamma", "beta", "relu", "bsums", "reduced", "consumers", "count")
+
+    def __init__(self):
+        self.y_raw = self.mean = self.invstd = self.gamma = self.beta = self.bsums = None
+        self.relu, self.reduced, self.consumers, self.count = False, False, 0, 0.0
 
 
 def _bn_epilogue_stats_ok(bn, sync, kind) -> bool:
@@ -330,10 +450,11 @@ def _bn_epilogue_stats_ok(bn, sync, kind) -> bool:
     return training and (bn.momentum is not None or not bn.track_running_stats)
 
 
-def _bn_sums_buffer(bn, C: int, dev):
-    """Per-layer, per-device {double sums[2C]; int ticket}: zero on creation, re-zeroed by dmp_bn_apply_sums after each use."""
+def _bn_sums_buffer(bn, C: int, dev, which: str = "sums"):
+    """Per-layer, per-device {double sums[2C]; int ticket}: zero on creation, re-zeroed by its consumer kernel after each use
+    (``sums``: forward batch sums, ``bsums``: backward reductions)."""
     store = bn.__dict__.setdefault("_dmp_ws", {})
-    key = (dev.index, "sums")
+    key = (dev.index, which)
     buf = store.get(key)
     need = int(_k().dmp_bn_sums_bytes(C)) // 8
     if buf is None or buf.numel() != need:
@@ -418,6 +539,31 @@ def _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu, need
     N, C, Ho, Wo = y_raw.shape
     M = N * Ho * Wo
     dres_t = None
+    link = getattr(ctx, "link_out", None)
+    if link is not None and link.reduced:
+        # the consumer's data-gradient kernel already masked the gradient and accumulated sum g / sum g*xhat: one elementwise pass
+        link.reduced = False
+        gw, gb = (bn.weight if needs_gamma else None), (bn.bias if needs_beta else None)
+        direct = all(p is None or (p.grad is not None and getattr(p, "_dmp_direct", False) and p.grad.dtype == torch.float32
+                                   and p.grad.is_contiguous()) for p in (gw, gb))
+        if direct:
+            dg_t, db_t, acc_flag = (gw.grad if gw is not None else None), (gb.grad if gb is not None else None), 1
+        else:
+            dg_t = torch.empty(C, device=y_raw.device, dtype=torch.float32) if gw is not None else None
+            db_t = torch.empty(C, device=y_raw.device, dtype=torch.float32) if gb is not None else None
+            acc_flag = 0
+        dy = dout if dout.is_contiguous(memory_format=torch.channels_last) else dout.contiguous(memory_format=torch.channels_last)
+        _ck(lib.dmp_bn_bwd_dx_sums(dy.data_ptr(), y_raw.data_ptr(), 1, mean.data_ptr(), invstd.data_ptr(), _native.ptr(gamma),
+                                   dy.data_ptr(), _native.ptr(dg_t), _native.ptr(db_t), acc_flag, M, C, link.bsums.data_ptr(), sp),
+            "bn bwd dx (producer-side sums)")
+        _note("bn:bwd_dx_from_sums")
+        if direct:
+            for p in (gw, gb):
+                if p is not None:
+                    for cb in grad_ready_callbacks:
+                        cb(p)
+            return dy, None, None, None
+        return dy, None, dg_t, db_t
     if ctx.bn_train and ctx.sync is None:
         # single cooperative launch: reductions -> grid barrier -> dx (+dres), dgamma/dbeta accumulated in place
         gw, gb = (bn.weight if needs_gamma else None), (bn.bias if needs_beta else None)
@@ -461,10 +607,10 @@ def _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu, need
                               1 if relu else 0, sp), "bn bwd dx")
 
         def write_dgamma(dst, accumulate):
-            _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), dst.data_ptr(), None, C, 1 if accumulate else 0, sp), "bn dgamma")
+            _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), dst.data_ptr(), None, C, 1 if accumulate else 0, _sp()), "bn dgamma")
 
         def write_dbeta(dst, accumulate):
-            _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), None, dst.data_ptr(), C, 1 if accumulate else 0, sp), "bn dbeta")
+            _ck(lib.dmp_bn_bwd_params(accum.data_ptr(), None, dst.data_ptr(), C, 1 if accumulate else 0, _sp()), "bn dbeta")
 
         dgamma = _deliver_grad(bn.weight, write_dgamma) if needs_gamma else None
         dbeta = _deliver_grad(bn.bias, write_dbeta) if needs_beta else None
@@ -487,10 +633,13 @@ class _ConvBNAct(torch.autograd.Function):
     """CUDA path. Inputs: x, conv weight, bn weight, bn bias, residual (the last three may be None)."""
 
     @staticmethod
-    def forward(ctx, x, w, gamma, beta, residual, conv, bn, relu, sync):
+    def forward(ctx, x, w, gamma, beta, residual, conv, bn, relu, sync, link_out=None, link_in=None):
         lib = _k()
         sp = _sp()
         kind = conv_kind(conv, x)
+        ctx.link_out, ctx.link_in = None, link_in
+        if link_in is not None:
+            link_in.consumers += 1
         if kind != "stem":
             x = _as_cl_bf16(x)
         if kind == "pw" and conv.stride != (1, 1):
@@ -513,6 +662,12 @@ class _ConvBNAct(torch.autograd.Function):
             ctx.bn_train = False
             return out
         out, mean, invstd, ctx.count, ctx.bn_train = _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync, sums)
+        if link_out is not None and ctx.bn_train and sync is None and residual is None:
+            # this op's output has a single consumer: let its data-gradient kernel produce the reductions of our backward
+            link_out.y_raw, link_out.mean, link_out.invstd, link_out.gamma, link_out.beta = y_raw, mean, invstd, gamma, beta
+            link_out.relu, link_out.count = relu, ctx.count
+            link_out.bsums = _bn_sums_buffer(bn, y_raw.shape[1], y_raw.device, "bsums")
+            ctx.link_out = link_out
         ctx.save_for_backward(x_saved, w, out if relu else None, y_raw, mean, invstd, gamma)
         return out
 
@@ -537,9 +692,9 @@ class _ConvBNAct(torch.autograd.Function):
             x, w, out, y_raw, mean, invstd, gamma = ctx.saved_tensors
             dy, dres, dgamma, dbeta = _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu,
                                                         ctx.needs_input_grad[2], ctx.needs_input_grad[3])
-        dx, write_dw = _conv_bwd_cuda(dy, x, w, conv, kind, ctx.x_needs_grad)
-        dw = _deliver_grad(conv.weight, write_dw) if ctx.needs_input_grad[1] else None
-        return dx, dw, dgamma, dbeta, dres, None, None, None, None
+        dx, write_dw = _conv_bwd_cuda(dy, x, w, conv, kind, ctx.x_needs_grad, ctx.link_in)
+        dw = _deliver_grad(conv.weight, write_dw, (dy, x)) if ctx.needs_input_grad[1] else None
+        return dx, dw, dgamma, dbeta, dres, None, None, None, None, None, None
 
 
 class _BNAct(torch.autograd.Function):
@@ -575,8 +730,11 @@ def _conv_bn_act_reference(x, conv, bn, relu, residual):
 
 
 def conv_bn_act(x: torch.Tensor, conv: nn.Conv2d, bn: Optional[nn.Module] = None, relu: bool = False,
-                residual: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """``act(bn(conv(x)) + residual)`` with optional pieces.  ``bn`` may be BatchNorm2d or our SyncBatchNorm."""
+                residual: Optional[torch.Tensor] = None, single_consumer: bool = False) -> torch.Tensor:
+    """``act(bn(conv(x)) + residual)`` with optional pieces.  ``bn`` may be BatchNorm2d or our SyncBatchNorm.
+
+    ``single_consumer=True`` is the caller's promise that the returned activation feeds exactly one further ``conv_bn_act``
+    (and nothing else): that convolution's data-gradient kernel then also produces this BatchNorm's backward reductions."""
     if not _use_kernels(x):
         _note("conv_bn_act:reference")
         return _conv_bn_act_reference(x, conv, bn, relu, residual)
@@ -585,7 +743,166 @@ def conv_bn_act(x: torch.Tensor, conv: nn.Conv2d, bn: Optional[nn.Module] = None
         sync = None
     gamma = bn.weight if bn is not None else None
     beta = bn.bias if bn is not None else None
-    return _ConvBNAct.apply(x, conv.weight, gamma, beta, residual, conv, bn, relu, sync)
+    link_in = getattr(x, "_dmp_bn_link", None) if torch.is_grad_enabled() else None
+    link_out = _BnLink() if (single_consumer and bn is not None and residual is None and _FUSE_BN_BWD and torch.is_grad_enabled()) else None
+    out = _ConvBNAct.apply(x, conv.weight, gamma, beta, residual, conv, bn, relu, sync, link_out, link_in)
+    if link_out is not None and link_out.y_raw is not None:
+        out._dmp_bn_link = link_out
+    return out
+
+
+# ----------------------------------------------------------------------------------------------------
+# expand 1x1 -> bn1 -> relu -> depthwise 3x3 -> bn2 -> relu  as one chain (the first two thirds of the reference's Block,
+# /root/reference/code/distributed_training/model/mobilenetv2.py:32-33)
+# ----------------------------------------------------------------------------------------------------
+def _param_grad_targets(params, C, dev):
+    """(tensors to hand to a kernel that writes per-channel parameter gradients, accumulate flag, direct?) for BatchNorm
+    weight/bias: straight into ``param.grad`` when that is a flat-arena view, else fresh buffers."""
+    direct = all(p is None or (p.grad is not None and getattr(p, "_dmp_direct", False) and p.grad.dtype == torch.float32
+                               and p.grad.is_contiguous()) for p in params)
+    if direct:
+        return [p.grad if p is not None else None for p in params], 1, True
+    return [torch.empty(C, device=dev, dtype=torch.float32) if p is not None else None for p in params], 0, False
+
+
+class _PwRawStats(torch.autograd.Function):
+    """y_raw = conv1x1(x), with the BatchNorm batch sums of y_raw accumulated by the GEMM epilogue into ``sums``.
+    The normalisation itself happens inside the consumer (``_DwBnInBn``) while it loads y_raw."""
+
+    @staticmethod
+    def forward(ctx, x, w, conv, sums):
+        x = _as_cl_bf16(x)
+        ctx.conv = conv
+        ctx.x_needs_grad = ctx.needs_input_grad[0]
+        y_raw, x_saved = _conv_fwd_cuda(x, w, conv, "pw", sums)
+        ctx.save_for_backward(x_saved, w)
+        return y_raw
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = _as_cl_bf16(dy)
+        dx, write_dw = _conv_bwd_cuda(dy, x, w, ctx.conv, "pw", ctx.x_needs_grad)
+        dw = _deliver_grad(ctx.conv.weight, write_dw, (dy, x)) if ctx.needs_input_grad[1] else None
+        return dx, dw, None, None
+
+
+class _DwBnInBn(torch.autograd.Function):
+    """a2 = relu(bn2(depthwise(relu(bn1(y1_raw))))) given the RAW expand output y1_raw and bn1's batch sums.
+
+    Forward: ONE stencil kernel normalises y1_raw on load, convolves, accumulates bn2's batch sums and publishes bn1's
+    statistics; one elementwise kernel applies bn2.  relu(bn1(y1_raw)) never exists in memory.
+    Backward: bn2 backward (one elementwise pass when the consumer's data-gradient kernel produced its reductions, else the
+    cooperative kernel) -> depthwise weight gradient with the activation re-created on load -> depthwise data gradient fused
+    with bn1's ReLU mask and reductions -> bn1's elementwise dx pass."""
+
+    @staticmethod
+    def forward(ctx, y1, g1, b1, w2, g2, b2, bn1, bn2, conv2, sums1, link_out):
+        lib = _k()
+        sp = _sp()
+        N, C, H, W = y1.shape
+        dev = y1.device
+        s = conv2.stride[0]
+        Ho, Wo = (H + 2 - 3) // s + 1, (W + 2 - 3) // s + 1
+        y2 = _cl_empty(N, C, Ho, Wo, dev)
+        mean1 = torch.empty(C, device=dev, dtype=torch.float32)
+        invstd1 = torch.empty(C, device=dev, dtype=torch.float32)
+        sums2 = _bn_sums_buffer(bn2, C, dev)
+        t1 = bn1.track_running_stats and bn1.running_mean is not None
+        _ck(lib.dmp_dwconv3x3_fwd_bnin_colstats(y1.data_ptr(), weight_bf16(w2).data_ptr(), y2.data_ptr(), N, H, W, C, s,
+                                                sums1.data_ptr(), _native.ptr(g1), _native.ptr(b1), float(bn1.eps),
+                                                float(bn1.momentum or 0.1), _native.ptr(bn1.running_mean if t1 else None),
+                                                _native.ptr(bn1.running_var if t1 else None),
+                                                _native.ptr(bn1.num_batches_tracked if t1 else None), mean1.data_ptr(),
+                                                invstd1.data_ptr(), sums2.data_ptr(), sp), "dwconv fwd (bn1 on load) + bn2 sums")
+        _note("conv_dw:stencil+bn_in+bnstats")
+        a2, mean2, invstd2, count2, _ = _bn_forward_cuda(y2, g2, b2, None, bn2, True, None, sums2)
+        ctx.bn1, ctx.bn2, ctx.conv2 = bn1, bn2, conv2
+        ctx.link_out = None
+        if link_out is not None:
+            link_out.y_raw, link_out.mean, link_out.invstd, link_out.gamma, link_out.beta = y2, mean2, invstd2, g2, b2
+            link_out.relu, link_out.count = True, count2
+            link_out.bsums = _bn_sums_buffer(bn2, C, dev, "bsums")
+            ctx.link_out = link_out
+        ctx.save_for_backward(y1, y2, mean1, invstd1, mean2, invstd2, g1, b1, w2, g2, b2)
+        return a2
+
+    @staticmethod
+    def backward(ctx, da2):
+        lib = _k()
+        sp = _sp()
+        y1, y2, mean1, invstd1, mean2, invstd2, g1, b1, w2, g2, b2 = ctx.saved_tensors
+        bn1, bn2, conv2 = ctx.bn1, ctx.bn2, ctx.conv2
+        N, C, H, W = y1.shape
+        _, _, Ho, Wo = y2.shape
+        s = conv2.stride[0]
+        dev = y1.device
+        da2 = _as_cl_bf16(da2)
+        # ---- bn2 backward -> dy2 (gradient of the depthwise convolution's raw output)
+        ctx.bn_train, ctx.sync, ctx.has_res, ctx.count = True, None, False, float(N * Ho * Wo)
+        dy2, _, dg2, db2 = _bn_backward_cuda(ctx, da2, None, y2, mean2, invstd2, g2, bn2, True, ctx.needs_input_grad[4],
+                                             ctx.needs_input_grad[5])
+        # ---- depthwise weight gradient; its input relu(bn1(y1)) is re-created while loading y1
+        def write_dw(dst, accumulate):
+            _ck(lib.dmp_dwconv3x3_wgrad_bnin(dy2.data_ptr(), y1.data_ptr(), dst.data_ptr(), N, H, W, C, s, 1 if accumulate else 0,
+                                             mean1.data_ptr(), invstd1.data_ptr(), _native.ptr(g1), _native.ptr(b1), _sp()),
+                "dwconv wgrad (bn1 on load)")
+
+        dw2 = _deliver_grad(conv2.weight, write_dw, (dy2, y1)) if ctx.needs_input_grad[3] else None
+        # ---- depthwise data gradient fused with bn1's ReLU mask and backward reductions, then bn1's elementwise dx pass
+        bs1 = _bn_sums_buffer(bn1, C, dev, "bsums")
+        g = _cl_empty(N, C, H, W, dev)
+        _ck(lib.dmp_dwconv3x3_dgrad_bnbwd(dy2.data_ptr(), weight_bf16(w2).data_ptr(), g.data_ptr(), N, H, W, C, s, y1.data_ptr(),
+                                          mean1.data_ptr(), invstd1.data_ptr(), _native.ptr(g1), _native.ptr(b1), bs1.data_ptr(), sp),
+            "dwconv dgrad + bn1 bwd reductions")
+        p1 = (bn1.weight if ctx.needs_input_grad[1] else None, bn1.bias if ctx.needs_input_grad[2] else None)
+        (dg1_t, db1_t), acc_flag, direct = _param_grad_targets(p1, C, dev)
+        _ck(lib.dmp_bn_bwd_dx_sums(g.data_ptr(), y1.data_ptr(), 1, mean1.data_ptr(), invstd1.data_ptr(), _native.ptr(g1), g.data_ptr(),
+                                   _native.ptr(dg1_t), _native.ptr(db1_t), acc_flag, N * H * W, C, bs1.data_ptr(), sp), "bn1 bwd dx")
+        _note("bn:bwd_dx_from_sums")
+        if direct:
+            for p in p1:
+                if p is not None:
+                    for cb in grad_ready_callbacks:
+                        cb(p)
+            dg1_t = db1_t = None
+        return g, dg1_t, db1_t, dw2, dg2, db2, None, None, None, None, None
+
+
+def _chain_ok(x, conv1, bn1, conv2, bn2) -> bool:
+    if not (_FUSE_CHAIN and _EPILOGUE_STATS and _use_kernels(x) and torch.is_grad_enabled()):
+        return False
+    if bn1 is None or bn2 is None or not (bn1.training and bn2.training):
+        return False
+    for bn in (bn1, bn2):
+        if getattr(bn, "_dmp_sync", None) is not None or bn.momentum is None or not isinstance(bn, nn.BatchNorm2d):
+            return False
+    if conv_kind(conv1, x) != "pw" or conv1.stride != (1, 1):
+        return False
+    C = conv2.in_channels
+    if not (conv2.kernel_size == (3, 3) and conv2.groups == C == conv2.out_channels and conv2.padding == (1, 1)
+            and conv2.stride in ((1, 1), (2, 2)) and conv2.bias is None and C % 16 == 0 and conv1.out_channels == C):
+        return False
+    if conv2.stride == (2, 2) and (x.shape[2] % 2 or x.shape[3] % 2):
+        return False
+    return True
+
+
+def expand_dw_bn_act(x: torch.Tensor, conv1: nn.Conv2d, bn1, conv2: nn.Conv2d, bn2, single_consumer: bool = False) -> torch.Tensor:
+    """``relu(bn2(conv2(relu(bn1(conv1(x))))))`` for a 1x1 expand followed by a depthwise 3x3 (train mode).  On the kernel
+    path the intermediate activation between bn1 and the depthwise convolution is never materialised; everywhere else (CPU,
+    eval mode, SyncBatchNorm, unsupported shapes) this is two ``conv_bn_act`` calls."""
+    if not _chain_ok(x, conv1, bn1, conv2, bn2):
+        out = conv_bn_act(x, conv1, bn1, relu=True, single_consumer=True)
+        return conv_bn_act(out, conv2, bn2, relu=True, single_consumer=single_consumer)
+    dev = x.device
+    sums1 = _bn_sums_buffer(bn1, conv1.out_channels, dev)
+    y1 = _PwRawStats.apply(x, conv1.weight, conv1, sums1)
+    link_out = _BnLink() if (single_consumer and _FUSE_BN_BWD) else None
+    a2 = _DwBnInBn.apply(y1, bn1.weight, bn1.bias, conv2.weight, bn2.weight, bn2.bias, bn1, bn2, conv2, sums1, link_out)
+    if link_out is not None:
+        a2._dmp_bn_link = link_out
+    return a2
 
 
 class _IdentityConv:
@@ -696,7 +1013,7 @@ class _Linear(torch.autograd.Function):
 
             def write_dw(dst, accumulate):
                 _ck(lib.dmp_linear_small_bwd(dy2.data_ptr(), x2.data_ptr(), w.data_ptr(), 0, None, dst.data_ptr(), None, B, Nf, K,
-                                             1 if accumulate else 0, sp), "linear dw")
+                                             1 if accumulate else 0, _sp()), "linear dw")
 
             def write_db(dst, accumulate):
                 if accumulate:
@@ -716,7 +1033,7 @@ class _Linear(torch.autograd.Function):
             def write_dw(dst, accumulate):
                 if not accumulate:
                     dst.zero_()
-                _ck(lib.dmp_gemm_bf16(2, dy2.data_ptr(), Nf, x2.data_ptr(), K, dst.data_ptr(), K, Nf, K, B, None, 2, 0, sp),
+                _ck(lib.dmp_gemm_bf16(2, dy2.data_ptr(), Nf, x2.data_ptr(), K, dst.data_ptr(), K, Nf, K, B, None, 2, 0, _sp()),
                     "linear wgrad gemm")
 
             def write_db(dst, accumulate):

@@ -138,6 +138,11 @@ class TorchDistBackend:
         return ALIGN_ELEMS
 
     def launch(self, bucket: "Bucket"):
+        if bucket.flat.is_cuda:  # gradients may have been written on the op layer's side stream as well
+            cur = torch.cuda.current_stream(bucket.flat.device)
+            for st in OF.side_streams().gradient_streams(bucket.flat.device):
+                if st.cuda_stream != cur.cuda_stream:
+                    cur.wait_stream(st)
         bucket.flat.div_(self.world_size)
         bucket.work = dist.all_reduce(bucket.flat, group=self.group, async_op=True)
 
@@ -214,6 +219,10 @@ class PeerBackend:
         ev = torch.cuda.Event()
         ev.record(cur)
         self.stream.wait_event(ev)
+        # the bucket's gradients were written on the stream backward runs on AND on the op layer's weight-gradient side stream
+        for st in OF.side_streams().gradient_streams(self.device):
+            if st.cuda_stream != cur.cuda_stream:
+                self.stream.wait_stream(st)
         self._launched_any = True
         fused = bucket.fused
         W = self.world_size

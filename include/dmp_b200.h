@@ -36,6 +36,12 @@ int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* B, long 
  * (double): the 1x1 convolution hands its BatchNorm the batch statistics, see dmp_bn_apply_sums. */
 int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd, int M, int N,
                            int K, double* stats, dmp_stream_t stream);
+/* NN data-gradient GEMM of a 1x1 convolution whose input was act(BatchNorm(y_raw)) (R/model/mobilenetv2.py:33-34): stores the
+ * ReLU-masked gradient G and accumulates {sum G, sum G*xhat} per column into stats[2N] -- the BatchNorm backward's reductions
+ * come out of the producer of its incoming gradient; dmp_bn_bwd_dx_sums finishes the job in one elementwise pass. */
+int dmp_gemm_bf16_dgrad_bnbwd(const void* A, long long lda, const void* B, long long ldb, void* G, long long ldd, int M, int N, int K,
+                              const void* y_raw, long long ld_y, const float* mean, const float* invstd, const float* gamma,
+                              const float* beta, int relu, double* stats, dmp_stream_t stream);
 int dmp_gemm_ref_f32out(int layout, const void* A, long long lda, const void* B, long long ldb, float* D, long long ldd,
                         int M, int N, int K, const float* bias, int accumulate, dmp_stream_t stream); /* CUDA-core oracle */
 
@@ -98,6 +104,10 @@ int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int dtype, co
  * One array per GPU shared by all calls: each call clears what it uses; calls that can overlap on a GPU race.  The first call
  * on a device resolves the array's address (cudaGetSymbolAddress) -- make it at start-up, before any stream capture.
  * Calls no cudaMalloc/cudaFree. */
+/* BatchNorm backward from reductions that already exist (sums = {sum g, sum g*xhat} + ticket, g already ReLU-masked): one
+ * elementwise pass, dx may alias g; block 0 writes dgamma/dbeta, the last block clears the sums. */
+int dmp_bn_bwd_dx_sums(const void* g, const void* x, int dtype, const float* mean, const float* invstd, const float* gamma, void* dx,
+                       float* dgamma, float* dbeta, int accumulate_params, long long M, int C, double* sums, dmp_stream_t stream);
 int dmp_bn_stats_finalize_noalloc(const void* x, int dtype, long long M, int C, const float* gamma, const float* beta,
                                   float* running_mean, float* running_var, float momentum, float eps, float* mean,
                                   float* invstd, float* scale, float* shift, dmp_stream_t stream);
@@ -110,6 +120,19 @@ int dmp_dwconv3x3_fwd_colstats(const void* x, const void* w, int w_dtype, void* 
                                double* stats, dmp_stream_t stream);
 int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void* dx, int N, int H, int W, int C, int stride,
                         dmp_stream_t stream);
+/* expand -> bn1 -> relu -> depthwise -> bn2 chain (R/model/mobilenetv2.py:32-33) without ever writing relu(bn1(.)) to memory:
+ * the forward normalises the RAW expand output while loading it (coefficients from the producer's batch sums, which it also
+ * publishes and clears), the weight gradient re-creates the activation the same way, and the data gradient applies the ReLU
+ * mask and accumulates bn1's backward reductions {sum g, sum g*xhat}.  bf16 weights [C,1,3,3], bf16 NHWC activations. */
+int dmp_dwconv3x3_fwd_bnin_colstats(const void* x_raw, const void* w_bf16, void* y, int N, int H, int W, int C, int stride,
+                                    double* in_sums, const float* gamma, const float* beta, float eps, float momentum,
+                                    float* running_mean, float* running_var, long long* num_batches_tracked, float* mean_out,
+                                    float* invstd_out, double* out_stats, dmp_stream_t stream);
+int dmp_dwconv3x3_dgrad_bnbwd(const void* dy, const void* w_bf16, void* g, int N, int H, int W, int C, int stride, const void* y_raw,
+                              const float* mean, const float* invstd, const float* gamma, const float* beta, double* bwd_sums,
+                              dmp_stream_t stream);
+int dmp_dwconv3x3_wgrad_bnin(const void* dy, const void* x_raw, float* dw, int N, int H, int W, int C, int stride, int accumulate,
+                             const float* mean, const float* invstd, const float* gamma, const float* beta, dmp_stream_t stream);
 int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int stride, int accumulate,
                         dmp_stream_t stream);
 
