@@ -36,6 +36,16 @@ _KERNEL_SIGS = {
     "dmp_gemm_ref_f32out": (i32, [i32, vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i32, vp]),
     "dmp_conv_igemm_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "dmp_conv_igemm_wgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_gemm_bf16_batched": (i32, [i32, vp, i64, i64, i64, vp, i64, i64, i64, vp, i64, i64, i64, i32, i32, i32, i32, i32, vp]),
+    # pooling / transformer row-wise kernels (csrc/kernels/elementwise.cu)
+    "dmp_maxpool_fwd": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_maxpool_bwd": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_layernorm_fwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, vp]),
+    "dmp_layernorm_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i64, i32, vp]),
+    "dmp_gelu_fwd": (i32, [vp, vp, i64, vp]),
+    "dmp_gelu_bwd": (i32, [vp, vp, vp, i64, vp]),
+    "dmp_softmax_fwd": (i32, [vp, vp, i64, i32, f32, vp]),
+    "dmp_softmax_bwd": (i32, [vp, vp, vp, i64, i32, f32, vp]),
     # optimizer
     "dmp_sgd_flat": (i32, [vp, vp, vp, i32, vp, i64, vp, i32, i32, vp]),
     "dmp_cast_flat": (i32, [vp, vp, i64, i32, vp]),

@@ -36,6 +36,9 @@ struct GemmParams {
     long long ld_aux;
     const float *bn_mean, *bn_invstd, *bn_gamma, *bn_beta;
     int relu;
+    // batched GEMM (attention): item z = zb * nh + zh selects the 3rd / 4th tensor-map coordinate of A, B and D
+    int nh, nbatch;
+    long long ldd_h, ldd_b;  // element offsets of D per zh / zb for the epilogues that do not store through TMA
 };
 
 // Persistent kernel: CTA b processes work items b, b+gridDim.x, ...  A work item is one 128 x BN output tile of one
@@ -100,7 +103,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int lane = threadIdx.x & 31;
     const int total_kb = (p.K + BK - 1) / BK;
     const int tiles_mn = p.m_tiles * p.n_tiles;
-    const int num_items = tiles_mn * p.splits;
+    const int num_items = tiles_mn * p.splits * p.nh * p.nbatch;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -134,10 +137,12 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             if (BRES && blockIdx.x < num_items) {
                 const int n0c = ((blockIdx.x % tiles_mn) % p.n_tiles) * BN;  // the same for every tile of this CTA
                 mbar_expect_tx(bres_bar, (uint32_t)(total_kb * B_BYTES));
-                for (int kb = 0; kb < total_kb; ++kb) tma_load_2d(bres + kb * B_BYTES, &tmB, bres_bar, kb * BK, n0c);
+                for (int kb = 0; kb < total_kb; ++kb) tma_load_4d(bres + kb * B_BYTES, &tmB, bres_bar, kb * BK, n0c, 0, 0);
             }
             for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-                const int split = item / tiles_mn, tile = item % tiles_mn;
+                const int z = item / (tiles_mn * p.splits), rem = item % (tiles_mn * p.splits);
+                const int zh = z % p.nh, zb = z / p.nh;
+                const int split = rem / tiles_mn, tile = rem % tiles_mn;
                 const int m0 = (tile / p.n_tiles) * BM, n0 = (tile % p.n_tiles) * BN;
                 const int kb_begin = split * p.k_blocks_per_split;
                 int kb_end = kb_begin + p.k_blocks_per_split;
@@ -155,7 +160,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     // rows/columns; accumulator rows and columns are independent and the epilogue masks everything >= M, N.
                     if (BRES) {  // the ring carries A only
                         mbar_expect_tx(&full_bar[s], A_BYTES);
-                        tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);
+                        tma_load_4d(sa, &tmA, &full_bar[s], k0, m0, zh, zb);
                         continue;
                     }
                     constexpr int BOX_BYTES = 64 * BK * 2;
@@ -169,17 +174,17 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                     }
                     mbar_expect_tx(&full_bar[s], tx);
                     if (A_MN) {
-                        tma_load_2d(sa, &tmA, &full_bar[s], m0, k0);  // global A^T [K, M]: two boxes of {64 m, 64 k}
-                        if (a_hi) tma_load_2d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0);
+                        tma_load_4d(sa, &tmA, &full_bar[s], m0, k0, zh, zb);  // global A^T [K, M]: two boxes of {64 m, 64 k}
+                        if (a_hi) tma_load_4d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, k0, zh, zb);
                     } else {
-                        tma_load_2d(sa, &tmA, &full_bar[s], k0, m0);  // box {64 k, 128 m}
+                        tma_load_4d(sa, &tmA, &full_bar[s], k0, m0, zh, zb);  // box {64 k, 128 m}
                     }
                     if (B_MN) {
 #pragma unroll
                         for (int c = 0; c < B_ROWS / 64; ++c)
-                            if (c == 0 || n0 + c * 64 < p.N) tma_load_2d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0);
+                            if (c == 0 || n0 + c * 64 < p.N) tma_load_4d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, k0, zh, zb);
                     } else {
-                        tma_load_2d(sb, &tmB, &full_bar[s], k0, n0);  // box {64 k, BN n}
+                        tma_load_4d(sb, &tmB, &full_bar[s], k0, n0, zh, zb);  // box {64 k, BN n}
                     }
                 }
             }
@@ -194,7 +199,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 tcgen05_fence_after();
             }
             for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
-                const int split = item / tiles_mn;
+                const int split = (item % (tiles_mn * p.splits)) / tiles_mn;
                 const int kb_begin = split * p.k_blocks_per_split;
                 int kb_end = kb_begin + p.k_blocks_per_split;
                 if (kb_end > total_kb) kb_end = total_kb;
@@ -268,6 +273,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         int local = 0;
         for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
             const int tile = item % tiles_mn;
+            const int z = item / (tiles_mn * p.splits);
+            const int zh = z % p.nh, zb = z / p.nh;
+            const long long dz = zh * p.ldd_h + zb * p.ldd_b;  // batch offset of D (elements) for the non-TMA stores
             const int m0 = (tile / p.n_tiles) * BM, n0 = (tile % p.n_tiles) * BN;
             const int buf = local & 1;
             const uint32_t acc_ph = (local >> 1) & 1;
@@ -285,8 +293,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
                     for (int pn = 0; pn < BN / PW; ++pn)
                         if (n0 + pn * PW < p.N)
-                            tma_load_2d(ystg + lane_grp * STG_WARP_BYTES + pn * (32 * PW * 2), &tmY, &ybar[lane_grp], n0 + pn * PW,
-                                        m0 + lane_grp * 32);
+                            tma_load_4d(ystg + lane_grp * STG_WARP_BYTES + pn * (32 * PW * 2), &tmY, &ybar[lane_grp], n0 + pn * PW,
+                                        m0 + lane_grp * 32, 0, 0);
                 }
             }
             mbar_wait(&tmem_full_bar[buf], acc_ph);
@@ -346,7 +354,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             *(int4*)(rowp + (((chunk0 + (j >> 3)) ^ swz) << 4)) = *(int4*)&o;
                         }
                     } else if (p.epi == 0) {
-                        bf16* d = (bf16*)p.D + (long long)row * p.ldd + n;
+                        bf16* d = (bf16*)p.D + dz + (long long)row * p.ldd + n;
                         if (n + 32 <= p.N && ((p.ldd & 7) == 0)) {
 #pragma unroll
                             for (int j = 0; j < 32; j += 8) {
@@ -365,7 +373,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                             }
                         }
                     } else if (p.epi == 1) {
-                        float* d = (float*)p.D + (long long)row * p.ldd + n;
+                        float* d = (float*)p.D + dz + (long long)row * p.ldd + n;
 #pragma unroll
                         for (int j = 0; j < 32; j += 4) {
                             if (n + j + 4 <= p.N && ((p.ldd & 3) == 0)) *(float4*)(d + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
@@ -374,7 +382,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                                     if (n + j + q < p.N) d[j + q] = v[j + q];
                         }
                     } else {
-                        float* d = (float*)p.D + (long long)row * p.ldd + n;
+                        float* d = (float*)p.D + dz + (long long)row * p.ldd + n;
 #pragma unroll
                         for (int j = 0; j < 32; ++j)
                             if (n + j < p.N) atomicAdd(d + j, v[j]);
@@ -450,7 +458,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 constexpr int RPI = 32 / LPR;           // rows per instruction
                 const int piece = lane % LPR, rsub = lane / LPR;
                 const int ncol = n0 + piece * 8;
-                bf16* dbase = (bf16*)p.D + (long long)(m0 + lane_grp * 32) * p.ldd + ncol;
+                bf16* dbase = (bf16*)p.D + dz + (long long)(m0 + lane_grp * 32) * p.ldd + ncol;
 #pragma unroll 4
                 for (int r0 = 0; r0 < 32; r0 += RPI) {
                     const int rr = r0 + rsub;
@@ -463,7 +471,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 if (p.tma_store == 1 && m0 + lane_grp * 32 < p.M) {
 #pragma unroll
                     for (int pn = 0; pn < BN / PW; ++pn)
-                        if (n0 + pn * PW < p.N) tma_store_2d(&tmD, my_stg + pn * (32 * PW * 2), n0 + pn * PW, m0 + lane_grp * 32);
+                        if (n0 + pn * PW < p.N) tma_store_4d(&tmD, my_stg + pn * (32 * PW * 2), n0 + pn * PW, m0 + lane_grp * 32, zh, zb);
                     tma_store_commit();
                 }
             }
@@ -507,18 +515,27 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
 // ------------------------------------------------------------------ host side
 // 2D bf16 tensor map: dim0 (contiguous) = inner, dim1 = outer with row pitch ld (elements).
+// Batch geometry of one operand: nh x nb matrices, element strides between them (0, 0 for a plain 2-D operand).
+struct Batch {
+    int nh = 1, nb = 1;
+    long long stride_h = 0, stride_b = 0;
+};
+
+// Every operand is encoded as a 4-D tensor {inner, outer, nh, nb}; plain GEMMs use nh = nb = 1 and coordinates (.., 0, 0).
 int make_tmap_2d(CUtensorMap* tm, const void* base, uint64_t inner, uint64_t outer, uint64_t ld_elems, uint32_t box_inner,
-                 uint32_t box_outer, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B) {
+                 uint32_t box_outer, CUtensorMapSwizzle swizzle = CU_TENSOR_MAP_SWIZZLE_128B, const Batch& bt = Batch()) {
     PFN_tmapEncodeTiled enc = get_encode_fn();
     DMP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled driver entry point unavailable");
     DMP_REQUIRE(((uintptr_t)base & 15) == 0, "TMA operand base must be 16-byte aligned");
     DMP_REQUIRE((ld_elems * 2) % 16 == 0, "TMA operand row pitch must be a multiple of 16 bytes (ld=%llu elements)",
                 (unsigned long long)ld_elems);
-    cuuint64_t gdim[2] = {inner, outer};
-    cuuint64_t gstride[1] = {ld_elems * 2};
-    cuuint32_t box[2] = {box_inner, box_outer};
-    cuuint32_t estr[2] = {1, 1};
-    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+    DMP_REQUIRE((bt.stride_h * 2) % 16 == 0 && (bt.stride_b * 2) % 16 == 0, "TMA batch strides must be multiples of 16 bytes");
+    const uint64_t plane = ld_elems * 2 * outer;  // any valid non-zero stride does for an extent-1 dimension
+    cuuint64_t gdim[4] = {inner, outer, (cuuint64_t)bt.nh, (cuuint64_t)bt.nb};
+    cuuint64_t gstride[3] = {ld_elems * 2, bt.nh > 1 ? (cuuint64_t)bt.stride_h * 2 : plane, bt.nb > 1 ? (cuuint64_t)bt.stride_b * 2 : plane};
+    cuuint32_t box[4] = {box_inner, box_outer, 1, 1};
+    cuuint32_t estr[4] = {1, 1, 1, 1};
+    CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     DMP_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (inner=%llu outer=%llu ld=%llu)", (int)r,
@@ -537,7 +554,8 @@ const int g_gemm_store_mode = [] {
 }();
 
 template <int BN, bool A_MN, bool B_MN, int ECOL = 0, bool BRES = false>
-int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream) {
+int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream,
+                const Batch& dbatch = Batch()) {
     constexpr int B_ROWS = (B_MN && BN < 64) ? 64 : BN;
     constexpr int ring_bytes = BRES ? bres_stages(BN) * (BM * BK * 2) + bres_bytes(BN)
                                     : gemm_stages(B_ROWS, ECOL) * (BM * BK * 2 + B_ROWS * BK * 2);
@@ -563,14 +581,14 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
         if (q.tma_store == 1) {
             constexpr int PW = BN >= 64 ? 64 : BN;
             if (int rc = make_tmap_2d(&tmD, p.D, (uint64_t)p.N, (uint64_t)p.M, (uint64_t)p.ldd, PW, 32,
-                                      PW == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B))
+                                      PW == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, dbatch))
                 return rc;
         }
     }
     q.m_tiles = dmp_ceil_div(p.M, BM);
     q.n_tiles = dmp_ceil_div(p.N, BN);
     q.splits = splits;
-    const long long items = (long long)q.m_tiles * q.n_tiles * splits;
+    const long long items = (long long)q.m_tiles * q.n_tiles * splits * q.nh * q.nbatch;
     const int ctas_per_sm = smem_bytes <= 110 * 1024 ? 2 : 1;
     long long grid = (long long)dmp_num_sms() * ctas_per_sm;
     if (grid > items) grid = items;
@@ -593,11 +611,12 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
 }
 
 template <bool A_MN, bool B_MN>
-int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t s) {
+int dispatch_bn(int bn, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t s,
+                const Batch& dbatch = Batch()) {
     switch (bn) {
-        case 32: return launch_gemm<32, A_MN, B_MN>(tmA, tmB, p, splits, s);
-        case 64: return launch_gemm<64, A_MN, B_MN>(tmA, tmB, p, splits, s);
-        default: return launch_gemm<128, A_MN, B_MN>(tmA, tmB, p, splits, s);
+        case 32: return launch_gemm<32, A_MN, B_MN>(tmA, tmB, p, splits, s, dbatch);
+        case 64: return launch_gemm<64, A_MN, B_MN>(tmA, tmB, p, splits, s, dbatch);
+        default: return launch_gemm<128, A_MN, B_MN>(tmA, tmB, p, splits, s, dbatch);
     }
 }
 
@@ -641,6 +660,7 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
     splits = dmp_ceil_div(total_kb, p.k_blocks_per_split);  // no empty splits
     p.D = D; p.ldd = ldd; p.bias = bias; p.epi = out_mode; p.stats = nullptr;
     p.aux = nullptr; p.ld_aux = 0; p.bn_mean = p.bn_invstd = p.bn_gamma = p.bn_beta = nullptr; p.relu = 0;
+    p.nh = p.nbatch = 1; p.ldd_h = p.ldd_b = 0;
 
     if (!a_mn && !b_mn) {
         // resident-B variant: whole [bn x K] panel in shared memory, loaded once per CTA (DMP_GEMM_BRES=0 disables).  Measured:
@@ -674,6 +694,7 @@ DMP_API int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, 
     p.k_blocks_per_split = dmp_ceil_div(K, BK);
     p.D = D; p.ldd = ldd; p.bias = nullptr; p.epi = 0; p.stats = stats;
     p.aux = nullptr; p.ld_aux = 0; p.bn_mean = p.bn_invstd = p.bn_gamma = p.bn_beta = nullptr; p.relu = 0;
+    p.nh = p.nbatch = 1; p.ldd_h = p.ldd_b = 0;
     static const bool use_bres = [] { const char* e = getenv("DMP_GEMM_BRES"); return e == nullptr || e[0] != '0'; }();
     if (use_bres && (long long)p.k_blocks_per_split * bn * BK * 2 <= bres_bytes(bn) && dmp_ceil_div(N, bn) <= dmp_num_sms()) {
         switch (bn) {
@@ -687,6 +708,43 @@ DMP_API int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, 
         case 64: return launch_gemm<64, false, false, 1>(tmA, tmB, p, 1, stream);
         default: return launch_gemm<128, false, false, 1>(tmA, tmB, p, 1, stream);
     }
+}
+
+// Batched GEMM: nh x nb independent problems D_z = A_z * B_z of one shape, operands addressed as base + zh*stride_h + zb*stride_b
+// (elements), bf16 output.  One persistent launch walks all tiles of all problems.  This is what attention is made of
+// (BASELINE.json config 4, no counterpart in the reference): scores = Q K^T (layout 0), context = P V (layout 1),
+// dV = P^T dO and dK = dS^T Q (layout 2), dP = dO V^T (0), dQ = dS K (1), with z = (head, batch) walking the fused
+// [B, S, 3, heads, d] projection in place -- no per-head copies.
+DMP_API int dmp_gemm_bf16_batched(int layout, const void* A, long long lda, long long a_sh, long long a_sb, const void* B, long long ldb,
+                                  long long b_sh, long long b_sb, void* D, long long ldd, long long d_sh, long long d_sb, int M, int N,
+                                  int K, int nh, int nb, cudaStream_t stream) {
+    DMP_REQUIRE(layout >= 0 && layout <= 2, "dmp_gemm_bf16_batched: bad layout %d", layout);
+    DMP_REQUIRE(M > 0 && N > 0 && K > 0 && nh > 0 && nb > 0, "dmp_gemm_bf16_batched: empty problem");
+    DMP_REQUIRE((ldd & 7) == 0 && (N & 7) == 0 && ((uintptr_t)D & 15) == 0 && (d_sh & 7) == 0 && (d_sb & 7) == 0,
+                "dmp_gemm_bf16_batched: D must be 16-byte aligned with N, ldd and batch strides multiples of 8");
+    const bool a_mn = (layout == 2), b_mn = (layout != 0);
+    int bn = N > 64 ? 128 : (N > 32 ? 64 : 32);
+    if (b_mn && bn < 64) bn = 64;
+    Batch ba, bb, bd;
+    ba.nh = bb.nh = bd.nh = nh; ba.nb = bb.nb = bd.nb = nb;
+    ba.stride_h = a_sh; ba.stride_b = a_sb; bb.stride_h = b_sh; bb.stride_b = b_sb; bd.stride_h = d_sh; bd.stride_b = d_sb;
+    CUtensorMap tmA, tmB;
+    int rc;
+    if (a_mn) rc = make_tmap_2d(&tmA, A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK, CU_TENSOR_MAP_SWIZZLE_128B, ba);
+    else rc = make_tmap_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B, ba);
+    if (rc) return rc;
+    if (b_mn) rc = make_tmap_2d(&tmB, B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK, CU_TENSOR_MAP_SWIZZLE_128B, bb);
+    else rc = make_tmap_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)bn, CU_TENSOR_MAP_SWIZZLE_128B, bb);
+    if (rc) return rc;
+    GemmParams p;
+    p.M = M; p.N = N; p.K = K;
+    p.k_blocks_per_split = dmp_ceil_div(K, BK);
+    p.D = D; p.ldd = ldd; p.bias = nullptr; p.epi = 0; p.stats = nullptr;
+    p.aux = nullptr; p.ld_aux = 0; p.bn_mean = p.bn_invstd = p.bn_gamma = p.bn_beta = nullptr; p.relu = 0;
+    p.nh = nh; p.nbatch = nb; p.ldd_h = d_sh; p.ldd_b = d_sb;
+    if (!a_mn && !b_mn) return dispatch_bn<false, false>(bn, tmA, tmB, p, 1, stream, bd);
+    if (!a_mn && b_mn) return dispatch_bn<false, true>(bn, tmA, tmB, p, 1, stream, bd);
+    return dispatch_bn<true, true>(bn, tmA, tmB, p, 1, stream, bd);
 }
 
 // Data-gradient GEMM of a 1x1 convolution whose INPUT was act(BatchNorm(y_raw)):  G[M,N] (bf16) = mask * (A[M,K] * B[K,N])
@@ -710,6 +768,7 @@ DMP_API int dmp_gemm_bf16_dgrad_bnbwd(const void* A, long long lda, const void* 
     p.D = G; p.ldd = ldd; p.bias = nullptr; p.epi = 0; p.stats = stats;
     p.aux = (const bf16*)y_raw; p.ld_aux = ld_y; p.bn_mean = mean; p.bn_invstd = invstd; p.bn_gamma = gamma; p.bn_beta = beta;
     p.relu = relu;
+    p.nh = p.nbatch = 1; p.ldd_h = p.ldd_b = 0;
     if (bn == 64) return launch_gemm<64, false, true, 2>(tmA, tmB, p, 1, stream);
     return launch_gemm<128, false, true, 2>(tmA, tmB, p, 1, stream);
 }

@@ -1,9 +1,10 @@
 """BERT-base encoder (12 layers, hidden 768, 12 heads, FFN 3072) -- pipeline workload of BASELINE.json config 4.
 
-NOT IN REFERENCE (the reference has no attention model).  All projection / FFN matmuls go through the
-tcgen05 GEMM (``FusedLinear``); softmax-attention uses ``scaled_dot_product_attention``; LayerNorm/GELU are
-elementwise library ops.  ``as_sequential`` exposes embeddings, the 12 layers and the head as a flat list for
-the layer-split partitioner; activations between stages are a single [B, S, H] tensor.
+NOT IN REFERENCE (the reference has no attention model).  On CUDA every op of a layer is one of this library's kernels:
+projection / FFN matmuls and the six matrix products of attention are tcgen05 GEMMs (``FusedLinear``, ``OF.attention``),
+LayerNorm (+ residual), GELU and the row softmax are the kernels of csrc/kernels/elementwise.cu; CPU tensors (and
+``use_reference_ops``) run the plain PyTorch restatement.  ``as_sequential`` exposes embeddings, the 12 layers and the head
+as a flat list for the layer-split partitioner; activations between stages are a single [B, S, H] tensor.
 """
 from __future__ import annotations
 
@@ -11,6 +12,7 @@ import torch
 import torch.nn as nn
 import torch.nn.functional as F
 
+from ..ops import functional as OF
 from .layers import FusedLinear
 
 
@@ -27,8 +29,8 @@ class BertEmbeddings(nn.Module):
         S = input_ids.shape[1]
         pos = torch.arange(S, device=input_ids.device)
         x = self.word_embeddings(input_ids) + self.position_embeddings(pos)[None] + self.token_type_embeddings.weight[0]
-        x = self.dropout(self.LayerNorm(x))
-        return x.to(torch.bfloat16) if x.is_cuda else x
+        x = self.dropout(OF.layer_norm(x, self.LayerNorm))
+        return x.to(torch.bfloat16) if OF._use_kernels(x) else x
 
 
 class BertLayer(nn.Module):
@@ -44,13 +46,10 @@ class BertLayer(nn.Module):
         self.dropout = nn.Dropout(dropout)
 
     def forward(self, x):
-        B, S, H = x.shape
-        qkv = self.qkv(x).view(B, S, 3, self.heads, H // self.heads).permute(2, 0, 3, 1, 4)
-        a = F.scaled_dot_product_attention(qkv[0], qkv[1], qkv[2])
-        a = a.transpose(1, 2).reshape(B, S, H)
-        x = self.ln1((x + self.dropout(self.attn_out(a))).float()).to(x.dtype)
-        h = self.ffn_out(F.gelu(self.ffn_in(x)))
-        return self.ln2((x + self.dropout(h)).float()).to(x.dtype)
+        a = OF.attention(self.qkv(x), self.heads)
+        x = OF.layer_norm(self.dropout(self.attn_out(a)), self.ln1, residual=x)
+        h = self.ffn_out(OF.gelu(self.ffn_in(x)))
+        return OF.layer_norm(self.dropout(h), self.ln2, residual=x)
 
 
 class BertHead(nn.Module):

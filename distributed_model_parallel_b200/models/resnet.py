@@ -63,7 +63,7 @@ class _Stem(nn.Module):
 
     def forward(self, x):
         out = OF.conv_bn_act(x, self.conv1, self.bn1, relu=True)
-        return F.max_pool2d(out, 3, 2, 1) if self.maxpool else out
+        return OF.max_pool2d(out, 3, 2, 1) if self.maxpool else out
 
 
 class _Head(nn.Module):
@@ -101,7 +101,7 @@ class ResNet(nn.Module):
     def forward(self, x):
         out = OF.conv_bn_act(x, self.conv1, self.bn1, relu=True)
         if self.imagenet:
-            out = F.max_pool2d(out, 3, 2, 1)
+            out = OF.max_pool2d(out, 3, 2, 1)
         out = self.layer4(self.layer3(self.layer2(self.layer1(out))))
         return self.linear(OF.global_avgpool_flatten(out))
 

@@ -27,7 +27,7 @@ class ConvUnit(nn.Module):
 
 class MaxPool(nn.Module):
     def forward(self, x):
-        return F.max_pool2d(x, 2, 2)
+        return OF.max_pool2d(x, 2, 2)
 
 
 class Classifier(nn.Module):

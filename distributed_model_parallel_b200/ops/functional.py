@@ -961,6 +961,187 @@ def global_avgpool_flatten(x: torch.Tensor, relu: bool = False) -> torch.Tensor:
     return F.adaptive_avg_pool2d(x, 1).flatten(1)
 
 
+class _MaxPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p):
+        x = _as_cl_bf16(x)
+        N, C, H, W = x.shape
+        Ho, Wo = (H + 2 * p - k) // s + 1, (W + 2 * p - k) // s + 1
+        y = _cl_empty(N, C, Ho, Wo, x.device)
+        idx = torch.empty((N, Ho, Wo, C), device=x.device, dtype=torch.uint8)
+        _ck(_k().dmp_maxpool_fwd(x.data_ptr(), y.data_ptr(), idx.data_ptr(), N, H, W, C, k, s, p, _sp()), "maxpool fwd")
+        ctx.geom = (N, C, H, W, k, s, p)
+        ctx.save_for_backward(idx)
+        _note("maxpool:kernel")
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        N, C, H, W, k, s, p = ctx.geom
+        dy = _as_cl_bf16(dy)
+        dx = _cl_empty(N, C, H, W, dy.device)
+        _ck(_k().dmp_maxpool_bwd(dy.data_ptr(), idx.data_ptr(), dx.data_ptr(), N, H, W, C, k, s, p, _sp()), "maxpool bwd")
+        return dx, None, None, None
+
+
+def max_pool2d(x: torch.Tensor, kernel_size: int, stride: Optional[int] = None, padding: int = 0) -> torch.Tensor:
+    """Max pooling on the kernel path (channels-last bf16, gather backward from the saved winning taps); the ResNet-50 stem
+    pool and VGG's 2x2 pools (model zoo of /root/reference/code/distributed_training/data_parallel.py:58-73)."""
+    stride = kernel_size if stride is None else stride
+    if _use_kernels(x) and x.dim() == 4 and x.shape[1] % 8 == 0 and kernel_size <= 15:
+        return _MaxPool.apply(x, int(kernel_size), int(stride), int(padding))
+    _note("maxpool:reference")
+    return F.max_pool2d(x, kernel_size, stride, padding)
+
+
+# ----------------------------------------------------------------------------------------------------
+# transformer pieces (BERT-base pipeline config; nothing of this exists in the reference)
+# ----------------------------------------------------------------------------------------------------
+class _LayerNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, res, gamma, beta, ln):
+        shp = x.shape
+        Hd = shp[-1]
+        x2 = x.reshape(-1, Hd)
+        x2 = x2 if (x2.dtype == torch.bfloat16 and x2.is_contiguous()) else x2.to(torch.bfloat16).contiguous()
+        r2 = None
+        if res is not None:
+            r2 = res.reshape(-1, Hd)
+            r2 = r2 if (r2.dtype == torch.bfloat16 and r2.is_contiguous()) else r2.to(torch.bfloat16).contiguous()
+        rows = x2.shape[0]
+        y = torch.empty_like(x2)
+        z = torch.empty_like(x2) if r2 is not None else x2
+        mean = torch.empty(rows, device=x.device, dtype=torch.float32)
+        rstd = torch.empty(rows, device=x.device, dtype=torch.float32)
+        _ck(_k().dmp_layernorm_fwd(x2.data_ptr(), _native.ptr(r2), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(),
+                                   z.data_ptr() if r2 is not None else None, mean.data_ptr(), rstd.data_ptr(), rows, Hd, float(ln.eps),
+                                   _sp()), "layernorm fwd")
+        ctx.ln, ctx.has_res, ctx.shape = ln, res is not None, shp
+        ctx.save_for_backward(z, gamma, mean, rstd)
+        _note("layernorm:kernel")
+        return y.reshape(shp)
+
+    @staticmethod
+    def backward(ctx, dy):
+        z, gamma, mean, rstd = ctx.saved_tensors
+        ln = ctx.ln
+        rows, Hd = z.shape
+        dy2 = dy.reshape(rows, Hd)
+        dy2 = dy2 if (dy2.dtype == torch.bfloat16 and dy2.is_contiguous()) else dy2.to(torch.bfloat16).contiguous()
+        dz = torch.empty_like(z)
+        (dg_t, db_t), acc, direct = _param_grad_targets((ln.weight, ln.bias), Hd, z.device)
+        if not direct:
+            dg_t.zero_(); db_t.zero_()
+        _ck(_k().dmp_layernorm_bwd(dy2.data_ptr(), z.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dz.data_ptr(),
+                                   dg_t.data_ptr(), db_t.data_ptr(), rows, Hd, _sp()), "layernorm bwd")
+        if direct:
+            for p in (ln.weight, ln.bias):
+                for cb in grad_ready_callbacks:
+                    cb(p)
+            dg_t = db_t = None
+        dzr = dz.reshape(ctx.shape)
+        return dzr, (dzr if ctx.has_res else None), dg_t, db_t, None
+
+
+def layer_norm(x: torch.Tensor, ln: nn.LayerNorm, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``LayerNorm(x + residual)`` over the last dimension: one kernel forward (the sum is written once, for backward), one
+    backward (dx = dresidual, dgamma, dbeta)."""
+    Hd = x.shape[-1]
+    if _use_kernels(x) and Hd % 8 == 0 and Hd <= 2048 and ln.elementwise_affine and ln.bias is not None:
+        return _LayerNorm.apply(x, residual, ln.weight, ln.bias, ln)
+    _note("layernorm:reference")
+    z = x if residual is None else x + residual
+    return F.layer_norm(z.float(), (Hd,), ln.weight, ln.bias, ln.eps).to(z.dtype)
+
+
+class _Gelu(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = x if (x.dtype == torch.bfloat16 and x.is_contiguous()) else x.to(torch.bfloat16).contiguous()
+        y = torch.empty_like(x)
+        _ck(_k().dmp_gelu_fwd(x.data_ptr(), y.data_ptr(), x.numel(), _sp()), "gelu fwd")
+        ctx.save_for_backward(x)
+        _note("gelu:kernel")
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        dy = dy if (dy.dtype == torch.bfloat16 and dy.is_contiguous()) else dy.to(torch.bfloat16).contiguous()
+        dx = torch.empty_like(x)
+        _ck(_k().dmp_gelu_bwd(dy.data_ptr(), x.data_ptr(), dx.data_ptr(), x.numel(), _sp()), "gelu bwd")
+        return dx
+
+
+def gelu(x: torch.Tensor) -> torch.Tensor:
+    if _use_kernels(x) and x.numel() % 8 == 0:
+        return _Gelu.apply(x)
+    _note("gelu:reference")
+    return F.gelu(x)
+
+
+def _bgemm(layout, A, lda, a_sh, a_sb, B, ldb, b_sh, b_sb, D, ldd, d_sh, d_sb, M, N, K, nh, nb, what):
+    _ck(_k().dmp_gemm_bf16_batched(layout, A, lda, a_sh, a_sb, B, ldb, b_sh, b_sb, D, ldd, d_sh, d_sb, M, N, K, nh, nb, _sp()), what)
+
+
+class _Attention(torch.autograd.Function):
+    """Softmax attention on the fused projection qkv [B, S, 3, heads, d] (bf16): six batched tcgen05 GEMMs (every head of every
+    sequence in one persistent launch each, operands addressed in place through 4-D tensor maps) and a row softmax."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads):
+        B, S, three, nh, d = qkv.shape
+        qkv = qkv if (qkv.dtype == torch.bfloat16 and qkv.is_contiguous()) else qkv.to(torch.bfloat16).contiguous()
+        dev = qkv.device
+        ld = 3 * nh * d                       # row pitch of Q / K / V inside the fused projection
+        sb = S * ld                           # batch stride
+        esz = 2
+        q, k, v = qkv.data_ptr(), qkv.data_ptr() + nh * d * esz, qkv.data_ptr() + 2 * nh * d * esz
+        P = torch.empty((B, nh, S, S), device=dev, dtype=torch.bfloat16)
+        out = torch.empty((B, S, nh, d), device=dev, dtype=torch.bfloat16)
+        _bgemm(0, q, ld, d, sb, k, ld, d, sb, P.data_ptr(), S, S * S, nh * S * S, S, S, d, nh, B, "attention scores")
+        _ck(_k().dmp_softmax_fwd(P.data_ptr(), P.data_ptr(), B * nh * S, S, 1.0 / (d ** 0.5), _sp()), "attention softmax")
+        _bgemm(1, P.data_ptr(), S, S * S, nh * S * S, v, ld, d, sb, out.data_ptr(), nh * d, d, S * nh * d, S, d, S, nh, B, "attention PV")
+        ctx.save_for_backward(qkv, P)
+        _note("attention:tcgen05_batched")
+        return out.view(B, S, nh * d)
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, P = ctx.saved_tensors
+        B, S, _, nh, d = qkv.shape
+        dev = qkv.device
+        ld, sb, esz = 3 * nh * d, S * 3 * nh * d, 2
+        q, k, v = qkv.data_ptr(), qkv.data_ptr() + nh * d * esz, qkv.data_ptr() + 2 * nh * d * esz
+        do = dout.reshape(B, S, nh, d)
+        do = do if (do.dtype == torch.bfloat16 and do.is_contiguous()) else do.to(torch.bfloat16).contiguous()
+        dqkv = torch.empty_like(qkv)
+        dq, dk, dv = dqkv.data_ptr(), dqkv.data_ptr() + nh * d * esz, dqkv.data_ptr() + 2 * nh * d * esz
+        lo, so = nh * d, S * nh * d           # dO / context layout [B, S, heads, d]
+        dP = torch.empty_like(P)
+        # dV = P^T dO, dP = dO V^T, dS = softmax'(dP), dQ = dS K, dK = dS^T Q
+        _bgemm(2, P.data_ptr(), S, S * S, nh * S * S, do.data_ptr(), lo, d, so, dv, ld, d, sb, S, d, S, nh, B, "attention dV")
+        _bgemm(0, do.data_ptr(), lo, d, so, v, ld, d, sb, dP.data_ptr(), S, S * S, nh * S * S, S, S, d, nh, B, "attention dP")
+        _ck(_k().dmp_softmax_bwd(dP.data_ptr(), P.data_ptr(), dP.data_ptr(), B * nh * S, S, 1.0 / (d ** 0.5), _sp()), "attention softmax bwd")
+        _bgemm(1, dP.data_ptr(), S, S * S, nh * S * S, k, ld, d, sb, dq, ld, d, sb, S, d, S, nh, B, "attention dQ")
+        _bgemm(2, dP.data_ptr(), S, S * S, nh * S * S, q, ld, d, sb, dk, ld, d, sb, S, d, S, nh, B, "attention dK")
+        return dqkv, None
+
+
+def attention(qkv: torch.Tensor, heads: int) -> torch.Tensor:
+    """Multi-head softmax attention of a fused projection ``qkv`` [B, S, 3*H] -> context [B, S, H]."""
+    B, S, H3 = qkv.shape
+    Hd = H3 // 3
+    d = Hd // heads
+    if _use_kernels(qkv) and d % 8 == 0 and S % 8 == 0:
+        return _Attention.apply(qkv.view(B, S, 3, heads, d), heads)
+    _note("attention:reference")
+    q, k, v = qkv.view(B, S, 3, heads, d).permute(2, 0, 3, 1, 4)
+    a = F.scaled_dot_product_attention(q, k, v)
+    return a.transpose(1, 2).reshape(B, S, Hd)
+
+
 # ----------------------------------------------------------------------------------------------------
 # linear
 # ----------------------------------------------------------------------------------------------------

@@ -42,6 +42,12 @@ int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, long lon
 int dmp_gemm_bf16_dgrad_bnbwd(const void* A, long long lda, const void* B, long long ldb, void* G, long long ldd, int M, int N, int K,
                               const void* y_raw, long long ld_y, const float* mean, const float* invstd, const float* gamma,
                               const float* beta, int relu, double* stats, dmp_stream_t stream);
+/* nh x nb independent GEMMs of one shape in one persistent launch; operand z = (zh, zb) lives at base + zh*stride_h + zb*stride_b
+ * (elements).  The six matrix products of softmax attention, walking the fused [B,S,3,heads,d] projection in place.
+ * NOT IN REFERENCE (BASELINE.json config 4: BERT-base pipeline). */
+int dmp_gemm_bf16_batched(int layout, const void* A, long long lda, long long a_sh, long long a_sb, const void* B, long long ldb,
+                          long long b_sh, long long b_sb, void* D, long long ldd, long long d_sh, long long d_sb, int M, int N, int K,
+                          int nh, int nb, dmp_stream_t stream);
 int dmp_gemm_ref_f32out(int layout, const void* A, long long lda, const void* B, long long ldb, float* D, long long ldd,
                         int M, int N, int K, const float* bias, int accumulate, dmp_stream_t stream); /* CUDA-core oracle */
 
@@ -135,6 +141,20 @@ int dmp_dwconv3x3_wgrad_bnin(const void* dy, const void* x_raw, float* dw, int N
                              const float* mean, const float* invstd, const float* gamma, const float* beta, dmp_stream_t stream);
 int dmp_dwconv3x3_wgrad(const void* dy, const void* x, float* dw, int N, int H, int W, int C, int stride, int accumulate,
                         dmp_stream_t stream);
+
+/* ------------------------------------------------------------------ pooling and transformer row-wise kernels (csrc/kernels/elementwise.cu)
+ * Max-pool for the ResNet / VGG family the reference lists (R/data_parallel.py:58-73); LayerNorm, GELU, softmax for the BERT-base
+ * pipeline config (NOT IN REFERENCE).  bf16 activations, fp32 statistics; idx = winning tap per output element (uint8). */
+int dmp_maxpool_fwd(const void* x, void* y, void* idx, int N, int H, int W, int C, int k, int stride, int pad, dmp_stream_t stream);
+int dmp_maxpool_bwd(const void* dy, const void* idx, void* dx, int N, int H, int W, int C, int k, int stride, int pad, dmp_stream_t stream);
+int dmp_layernorm_fwd(const void* x, const void* res, const float* gamma, const float* beta, void* y, void* z, float* mean, float* rstd,
+                      long long rows, int H, float eps, dmp_stream_t stream);
+int dmp_layernorm_bwd(const void* dy, const void* z, const float* gamma, const float* mean, const float* rstd, void* dz, float* dgamma,
+                      float* dbeta, long long rows, int H, dmp_stream_t stream);
+int dmp_gelu_fwd(const void* x, void* y, long long n, dmp_stream_t stream);
+int dmp_gelu_bwd(const void* dy, const void* x, void* dx, long long n, dmp_stream_t stream);
+int dmp_softmax_fwd(const void* s, void* p, long long rows, int L, float scale, dmp_stream_t stream);
+int dmp_softmax_bwd(const void* dp, const void* p, void* ds, long long rows, int L, float scale, dmp_stream_t stream);
 
 /* ------------------------------------------------------------------ small ops (csrc/kernels/misc.cu; R/model/mobilenetv2.py:52,57,69-75) */
 int dmp_stem_conv_fwd(const void* x, int x_layout, const void* w, int w_dtype, void* y, int N, int Cin, int H, int W,

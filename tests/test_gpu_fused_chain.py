@@ -213,7 +213,7 @@ def test_block_fused_chain_matches_unfused_kernels_and_reference(cin, cout, expa
     _close(dx, xr.grad, 8e-2, 8e-2 * xr.grad.abs().max().item(), "block input gradient", max_bad_frac=5e-3)
     for (n, p), (_, q) in zip(blk.named_parameters(), ref.named_parameters()):
         tol = 0.12 * max(q.grad.abs().max().item(), 1e-3)
-        _close(p.grad, q.grad, 6e-2, tol, "grad of %s" % n, max_bad_frac=0.05)
+        _close(p.grad, q.grad, 6e-2, tol, "grad of %s" % n, max_bad_frac=0.1)  # per-channel sums: see tests/test_gpu_models.py on their noise
     for (n, b), (_, c) in zip(blk.named_buffers(), ref.named_buffers()):
         if b.dtype.is_floating_point:
             _close(b, c, 2e-2, 2e-2, "buffer %s" % n)
