@@ -36,6 +36,9 @@ _KERNEL_SIGS = {
     "dmp_gemm_ref_f32out": (i32, [i32, vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i32, vp]),
     "dmp_conv_igemm_fwd": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "dmp_conv_igemm_wgrad": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_conv_igemm_fwd_strided": (i32, [vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_conv_igemm_dgrad_s2": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
+    "dmp_conv_igemm_wgrad_strided": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "dmp_gemm_bf16_batched": (i32, [i32, vp, i64, i64, i64, vp, i64, i64, i64, vp, i64, i64, i64, i32, i32, i32, i32, i32, vp]),
     # pooling / transformer row-wise kernels (csrc/kernels/elementwise.cu)
     "dmp_maxpool_fwd": (i32, [vp, vp, vp, i32, i32, i32, i32, i32, i32, i32, vp]),

@@ -31,6 +31,15 @@ struct ConvParams {
     void* D;
     long long ldd;
     const float* bias;
+    // generalisation to strided convolutions and their data gradient: an item belongs to a class c (forward: one class; stride-2
+    // data gradient: the four output-pixel parities), a class has its own tap list -- (weight tap index, patch offset dh, dw) --
+    // and writes output pixel (a * oscale + ph[c], b * oscale + pw[c]) of an OH x OW image for patch pixel (a, b)
+    int astride;                 // element stride of the A-operand boxes (forward of a strided convolution: its stride; else 1)
+    int ncls, oscale, OH, OW;
+    int cls_ntaps[4], cls_ph[4], cls_pw[4];
+    signed char cls_tap[4][49], cls_dh[4][49], cls_dw[4][49];
+    int kcrs;                    // wgrad: write dW as [Cout][Cin][KH][KW] (the parameter's own layout) instead of [Cout][tap][Cin]
+    int wstride;                 // wgrad: stride of the convolution (x boxes are read with this element stride)
 };
 
 // ------------------------------------------------------------------ forward / stride-1 data gradient
@@ -53,8 +62,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int cchunks = p.Cin / BK;
-    const int total_kb = p.KH * p.KW * cchunks;
-    const int num_items = p.m_tiles * p.n_tiles;
+    const int tiles_mn = p.m_tiles * p.n_tiles;
+    const int num_items = tiles_mn * p.ncls;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
@@ -79,19 +88,23 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         if (lane == 0) {
             int it = 0;
             for (int item = blockIdx.x; item < num_items; item += gridDim.x) {
-                const int mt = item / p.n_tiles, n0 = (item % p.n_tiles) * BN;
+                const int cls = item / tiles_mn, rem = item % tiles_mn;
+                const int mt = rem / p.n_tiles, n0 = (rem % p.n_tiles) * BN;
                 const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, tn = mt / (p.tiles_w * p.tiles_h);
+                const int total_kb = p.cls_ntaps[cls] * cchunks;
                 for (int kb = 0; kb < total_kb; ++kb, ++it) {
                     const int s = it % STAGES;
                     const uint32_t ph = (it / STAGES) & 1;
                     mbar_wait(&empty_bar[s], ph ^ 1);
                     uint8_t* sa = smem + s * STAGE_BYTES;
                     uint8_t* sb = sa + A_BYTES;
-                    const int tap = kb / cchunks, cc = kb % cchunks;
-                    const int kh = tap / p.KW, kw = tap % p.KW;
+                    const int ti = kb / cchunks, cc = kb % cchunks;
+                    const int tap = p.cls_tap[cls][ti];
                     mbar_expect_tx(&full_bar[s], STAGE_BYTES);
-                    // one shifted pixel patch x 64 channels; negative / past-the-edge coordinates are zero-filled = padding
-                    tma_load_4d(sa, &tmA, &full_bar[s], cc * BK, tw * p.BW + kw - p.pad, th * p.BH + kh - p.pad, tn * p.BNI);
+                    // one shifted pixel patch x 64 channels (every astride-th pixel); negative / past-the-edge coordinates are
+                    // zero-filled by the TMA unit = the convolution's padding
+                    tma_load_4d(sa, &tmA, &full_bar[s], cc * BK, tw * p.BW * p.astride + p.cls_dw[cls][ti],
+                                th * p.BH * p.astride + p.cls_dh[cls][ti], tn * p.BNI);
                     tma_load_2d(sb, &tmB, &full_bar[s], tap * p.Cin + cc * BK, n0);
                 }
             }
@@ -101,6 +114,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             constexpr uint32_t idesc = make_idesc(BN, 0, 0);
             int it = 0, local = 0;
             for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
+                const int total_kb = p.cls_ntaps[item / tiles_mn] * cchunks;
                 const int buf = local & 1;
                 const uint32_t acc_ph = (local >> 1) & 1;
                 mbar_wait(&tmem_empty_bar[buf], acc_ph ^ 1);
@@ -126,7 +140,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         const int lane_grp = warp & 3;
         int local = 0;
         for (int item = blockIdx.x; item < num_items; item += gridDim.x, ++local) {
-            const int mt = item / p.n_tiles, n0 = (item % p.n_tiles) * BN;
+            const int cls = item / tiles_mn, rem = item % tiles_mn;
+            const int mt = rem / p.n_tiles, n0 = (rem % p.n_tiles) * BN;
             const int tw = mt % p.tiles_w, th = (mt / p.tiles_w) % p.tiles_h, tn = mt / (p.tiles_w * p.tiles_h);
             const int buf = local & 1;
             const uint32_t acc_ph = (local >> 1) & 1;
@@ -135,7 +150,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
             const int wi = r % p.BW, hi = (r / p.BW) % p.BH, ni = r / (p.BW * p.BH);
             const int n = tn * p.BNI + ni, ho = th * p.BH + hi, wo = tw * p.BW + wi;
             const bool valid = n < p.Nimg && ho < p.Ho && wo < p.Wo;
-            const long long row = ((long long)n * p.Ho + ho) * p.Wo + wo;
+            const long long row = ((long long)n * p.OH + ho * p.oscale + p.cls_ph[cls]) * p.OW + wo * p.oscale + p.cls_pw[cls];
             mbar_wait(&tmem_full_bar[buf], acc_ph);
             tcgen05_fence_after();
             const uint32_t taddr_row = tmem_base + buf * ACC_COLS + ((uint32_t)(lane_grp * 32) << 16);
@@ -248,8 +263,8 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                     tma_load_4d(sa + A_BYTES / 2, &tmA, &full_bar[s], m0 + 64, tw * p.BW, th * p.BH, tn * p.BNI);
 #pragma unroll
                     for (int c = 0; c < BN / 64; ++c)
-                        tma_load_4d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, tw * p.BW + kw - p.pad,
-                                    th * p.BH + kh - p.pad, tn * p.BNI);
+                        tma_load_4d(sb + c * (64 * BK * 2), &tmB, &full_bar[s], n0 + c * 64, tw * p.BW * p.wstride + kw - p.pad,
+                                    th * p.BH * p.wstride + kh - p.pad, tn * p.BNI);
                 }
             }
         }
@@ -303,10 +318,17 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 tmem_ld_32(taddr_row + c0, rr);
                 tmem_ld_wait();
                 if (row < p.Cout) {
-                    float* d = (float*)p.D + (long long)row * p.ldd + (long long)tap * p.Cin + n0 + c0;
+                    if (p.kcrs) {  // straight into the parameter's [Cout][Cin][KH][KW] gradient: no repacking pass afterwards
+                        float* d = (float*)p.D + (long long)row * p.ldd + (long long)(n0 + c0) * taps + tap;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (n0 + c0 + j < p.Cin) atomicAdd(d + j, __uint_as_float(rr[j]));
+                        for (int j = 0; j < 32; ++j)
+                            if (n0 + c0 + j < p.Cin) atomicAdd(d + (long long)j * taps, __uint_as_float(rr[j]));
+                    } else {
+                        float* d = (float*)p.D + (long long)row * p.ldd + (long long)tap * p.Cin + n0 + c0;
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (n0 + c0 + j < p.Cin) atomicAdd(d + j, __uint_as_float(rr[j]));
+                    }
                 }
             }
             tcgen05_fence_before();
@@ -329,14 +351,16 @@ int next_pow2(int v) {
 }
 
 // 4-D bf16 map over a channels-last activation [N, H, W, C] with box {64, bw, bh, bni}
-int make_tmap_act(CUtensorMap* tm, const void* base, int N, int H, int W, int C, int bw, int bh, int bni) {
+// estride > 1: the box takes every estride-th pixel along W and H (bw x bh pixels land in shared memory either way)
+int make_tmap_act(CUtensorMap* tm, const void* base, int N, int H, int W, int C, int bw, int bh, int bni, int estride = 1) {
     PFN_tmapEncodeTiled enc = get_encode_fn();
     DMP_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled driver entry point unavailable");
     DMP_REQUIRE(((uintptr_t)base & 15) == 0 && (C % 8) == 0, "conv operand must be 16-byte aligned with C %% 8 == 0");
+    DMP_REQUIRE(bw * estride <= 256 && bh * estride <= 256, "conv patch %dx%d with stride %d exceeds the TMA box limit", bw, bh, estride);
     cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
     cuuint64_t gstride[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
-    cuuint32_t box[4] = {64, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bni};
-    cuuint32_t estr[4] = {1, 1, 1, 1};
+    cuuint32_t box[4] = {64, (cuuint32_t)(bw * estride), (cuuint32_t)(bh * estride), (cuuint32_t)bni};
+    cuuint32_t estr[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
     CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), gdim, gstride, box, estr,
                      CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                      CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -376,26 +400,11 @@ int set_smem(K kern, int bytes) {
 
 }  // namespace
 
-// y[N,H,W,Cout] = conv(x[N,H,W,Cin], wp) with stride 1 and padding `pad` such that the output keeps H x W
-// (KH = KW = 2*pad+1).  wp: bf16 [Cout, KH*KW*Cin] (weight permuted to [Cout][kh][kw][Cin]).  Cin % 64 == 0, Cout % 8 == 0.
-// The stride-1 data gradient is the same call with x := dy, wp := [Cin, KH*KW*Cout] holding the flipped, transposed filter.
-DMP_API int dmp_conv_igemm_fwd(const void* x, const void* wp, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
-                               int KH, int KW, int pad, cudaStream_t stream) {
-    DMP_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "dmp_conv_igemm_fwd: needs Cin %% 64 == 0 and Cout %% 8 == 0 (Cin=%d Cout=%d)", Cin, Cout);
-    DMP_REQUIRE(KH == 2 * pad + 1 && KW == 2 * pad + 1, "dmp_conv_igemm_fwd: only 'same' stride-1 convolutions (K = 2*pad+1)");
-    ConvParams p;
-    memset(&p, 0, sizeof(p));
-    p.Nimg = N; p.Ho = H; p.Wo = W; p.Cin = Cin; p.Cout = Cout; p.KH = KH; p.KW = KW; p.pad = pad;
-    patch_shape(H, W, 128, &p.BW, &p.BH, &p.BNI);
-    p.tiles_w = dmp_ceil_div(W, p.BW); p.tiles_h = dmp_ceil_div(H, p.BH); p.tiles_n = dmp_ceil_div(N, p.BNI);
-    p.m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
-    const int bn = Cout > 64 ? 128 : (Cout > 32 ? 64 : 32);
-    p.n_tiles = dmp_ceil_div(Cout, bn);
-    p.D = y; p.ldd = Cout; p.bias = bias;
-    CUtensorMap tmA, tmB;
-    if (int rc = make_tmap_act(&tmA, x, N, H, W, Cin, p.BW, p.BH, p.BNI)) return rc;
-    if (int rc = make_tmap_w(&tmB, wp, Cout, (long long)KH * KW * Cin, bn)) return rc;
-    const long long items = (long long)p.m_tiles * p.n_tiles;
+namespace {
+
+template <int BN_unused = 0>
+int launch_conv_igemm(const CUtensorMap& tmA, const CUtensorMap& tmB, ConvParams& p, int bn, cudaStream_t stream) {
+    const long long items = (long long)p.m_tiles * p.n_tiles * p.ncls;
     const int smem_bytes = STAGES * (BM * BK * 2 + bn * BK * 2) + 1024 + 256;
     long long grid = (long long)dmp_num_sms() * (smem_bytes <= 110 * 1024 ? 2 : 1);
     if (grid > items) grid = items;
@@ -414,21 +423,108 @@ DMP_API int dmp_conv_igemm_fwd(const void* x, const void* wp, const float* bias,
     return 0;
 }
 
-// dwp[Cout, KH*KW*Cin] (fp32, [Cout][kh][kw][Cin]) += sum over pixels of dy[p, co] * x[p shifted by the tap, ci].
-// dy: [N,H,W,Cout], x: [N,H,W,Cin] bf16 channels-last, stride 1, 'same' padding.  dwp must hold the addend (zeros to overwrite).
-DMP_API int dmp_conv_igemm_wgrad(const void* dy, const void* x, float* dwp, int N, int H, int W, int Cin, int Cout, int KH, int KW,
-                                 int pad, cudaStream_t stream) {
-    DMP_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "dmp_conv_igemm_wgrad: channel counts must be multiples of 8");
-    DMP_REQUIRE(KH == 2 * pad + 1 && KW == 2 * pad + 1, "dmp_conv_igemm_wgrad: only 'same' stride-1 convolutions");
+}  // namespace
+
+// y[N,Ho,Wo,Cout] = conv(x[N,H,W,Cin], wp), KH x KW taps, padding `pad`, stride `stride` (1 or 2): Ho = (H + 2 pad - KH) / stride + 1.
+// wp: bf16 [Cout, KH*KW*Cin] (weight permuted to [Cout][kh][kw][Cin]).  Cin % 64 == 0, Cout % 8 == 0, KH*KW <= 49.
+// With stride 2 the A-operand boxes take every second pixel (TMA element strides): still no im2col buffer.
+DMP_API int dmp_conv_igemm_fwd_strided(const void* x, const void* wp, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
+                                       int KH, int KW, int pad, int stride, cudaStream_t stream) {
+    DMP_REQUIRE(Cin % 64 == 0 && Cout % 8 == 0, "dmp_conv_igemm_fwd: needs Cin %% 64 == 0 and Cout %% 8 == 0 (Cin=%d Cout=%d)", Cin, Cout);
+    DMP_REQUIRE(stride >= 1 && stride <= 4 && KH * KW <= 49 && pad >= 0, "dmp_conv_igemm_fwd: unsupported geometry (k=%dx%d stride %d)", KH, KW, stride);
+    const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+    DMP_REQUIRE(Ho > 0 && Wo > 0, "dmp_conv_igemm_fwd: empty output");
     ConvParams p;
     memset(&p, 0, sizeof(p));
-    p.Nimg = N; p.Ho = H; p.Wo = W; p.Cin = Cin; p.Cout = Cout; p.KH = KH; p.KW = KW; p.pad = pad;
-    patch_shape(H, W, 64, &p.BW, &p.BH, &p.BNI);
-    p.tiles_w = dmp_ceil_div(W, p.BW); p.tiles_h = dmp_ceil_div(H, p.BH); p.tiles_n = dmp_ceil_div(N, p.BNI);
+    p.Nimg = N; p.Ho = Ho; p.Wo = Wo; p.Cin = Cin; p.Cout = Cout; p.KH = KH; p.KW = KW; p.pad = pad;
+    p.astride = stride; p.ncls = 1; p.oscale = 1; p.OH = Ho; p.OW = Wo;
+    p.cls_ntaps[0] = KH * KW;
+    for (int kh = 0; kh < KH; ++kh)
+        for (int kw = 0; kw < KW; ++kw) {
+            const int t = kh * KW + kw;
+            p.cls_tap[0][t] = (signed char)t; p.cls_dh[0][t] = (signed char)(kh - pad); p.cls_dw[0][t] = (signed char)(kw - pad);
+        }
+    patch_shape(Ho, Wo, 128, &p.BW, &p.BH, &p.BNI);
+    p.tiles_w = dmp_ceil_div(Wo, p.BW); p.tiles_h = dmp_ceil_div(Ho, p.BH); p.tiles_n = dmp_ceil_div(N, p.BNI);
+    p.m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
+    const int bn = Cout > 64 ? 128 : (Cout > 32 ? 64 : 32);
+    p.n_tiles = dmp_ceil_div(Cout, bn);
+    p.D = y; p.ldd = Cout; p.bias = bias;
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap_act(&tmA, x, N, H, W, Cin, p.BW, p.BH, p.BNI, stride)) return rc;
+    if (int rc = make_tmap_w(&tmB, wp, Cout, (long long)KH * KW * Cin, bn)) return rc;
+    return launch_conv_igemm(tmA, tmB, p, bn, stream);
+}
+
+DMP_API int dmp_conv_igemm_fwd(const void* x, const void* wp, const float* bias, void* y, int N, int H, int W, int Cin, int Cout,
+                               int KH, int KW, int pad, cudaStream_t stream) {
+    DMP_REQUIRE(KH == 2 * pad + 1 && KW == 2 * pad + 1, "dmp_conv_igemm_fwd: only 'same' stride-1 convolutions (K = 2*pad+1)");
+    return dmp_conv_igemm_fwd_strided(x, wp, bias, y, N, H, W, Cin, Cout, KH, KW, pad, 1, stream);
+}
+
+// Data gradient of a stride-2 convolution: dx[N,H,W,Cin] from dy[N,H/2,W/2,Cout] (H, W even; Ho = H/2 requires KH = 2 pad + 1 or
+// 2 pad + 2).  The four output-pixel parities (h % 2, w % 2) are four stride-1 implicit GEMMs over dy, each with the subset of
+// taps whose (h + pad - kh) is even -- 1, 2, 2 and 4 taps for a 3x3 filter -- so no multiplication by an inserted zero is done.
+// wd: bf16 [Cin, KH*KW*Cout] = the weight permuted to [Cin][kh][kw][Cout].  Cout % 64 == 0, Cin % 8 == 0.
+DMP_API int dmp_conv_igemm_dgrad_s2(const void* dy, const void* wd, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                    int pad, cudaStream_t stream) {
+    DMP_REQUIRE(Cout % 64 == 0 && Cin % 8 == 0, "dmp_conv_igemm_dgrad_s2: needs Cout %% 64 == 0 and Cin %% 8 == 0");
+    DMP_REQUIRE(H % 2 == 0 && W % 2 == 0 && KH * KW <= 49, "dmp_conv_igemm_dgrad_s2: needs even H, W");
+    const int Ho = (H + 2 * pad - KH) / 2 + 1, Wo = (W + 2 * pad - KW) / 2 + 1;
+    DMP_REQUIRE(Ho == H / 2 && Wo == W / 2, "dmp_conv_igemm_dgrad_s2: output of the convolution must be H/2 x W/2");
+    ConvParams p;
+    memset(&p, 0, sizeof(p));
+    // "A operand" = dy with Cout channels; "output columns" = Cin
+    p.Nimg = N; p.Ho = Ho; p.Wo = Wo; p.Cin = Cout; p.Cout = Cin; p.KH = KH; p.KW = KW; p.pad = pad;
+    p.astride = 1; p.ncls = 4; p.oscale = 2; p.OH = H; p.OW = W;
+    for (int c = 0; c < 4; ++c) {
+        const int ph = c >> 1, pw = c & 1;
+        p.cls_ph[c] = ph; p.cls_pw[c] = pw;
+        int nt = 0;
+        for (int kh = 0; kh < KH; ++kh) {
+            if (((ph + pad - kh) % 2 + 2) % 2 != 0) continue;
+            for (int kw = 0; kw < KW; ++kw) {
+                if (((pw + pad - kw) % 2 + 2) % 2 != 0) continue;
+                p.cls_tap[c][nt] = (signed char)(kh * KW + kw);
+                // dx[2a+ph] takes dy[ho] with 2 ho + kh - pad = 2a + ph  ->  ho = a + (ph + pad - kh) / 2 (exact; may be negative)
+                const int nh = ph + pad - kh, nw = pw + pad - kw;
+                p.cls_dh[c][nt] = (signed char)(nh >= 0 ? nh / 2 : -((-nh) / 2));
+                p.cls_dw[c][nt] = (signed char)(nw >= 0 ? nw / 2 : -((-nw) / 2));
+                ++nt;
+            }
+        }
+        p.cls_ntaps[c] = nt;
+    }
+    patch_shape(Ho, Wo, 128, &p.BW, &p.BH, &p.BNI);
+    p.tiles_w = dmp_ceil_div(Wo, p.BW); p.tiles_h = dmp_ceil_div(Ho, p.BH); p.tiles_n = dmp_ceil_div(N, p.BNI);
+    p.m_tiles = p.tiles_w * p.tiles_h * p.tiles_n;
+    const int bn = Cin > 64 ? 128 : (Cin > 32 ? 64 : 32);
+    p.n_tiles = dmp_ceil_div(Cin, bn);
+    p.D = dx; p.ldd = Cin; p.bias = nullptr;
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap_act(&tmA, dy, N, Ho, Wo, Cout, p.BW, p.BH, p.BNI, 1)) return rc;
+    if (int rc = make_tmap_w(&tmB, wd, Cin, (long long)KH * KW * Cout, bn)) return rc;
+    return launch_conv_igemm(tmA, tmB, p, bn, stream);
+}
+
+// dW += sum over output pixels of dy[p, co] * x[p * stride (+) tap, ci].  dy: [N,Ho,Wo,Cout], x: [N,H,W,Cin] bf16 channels-last.
+// kcrs = 0: dw is fp32 [Cout][KH*KW][Cin]; kcrs = 1: dw is fp32 [Cout][Cin][KH][KW], the layout of the nn.Conv2d parameter, so the
+// kernel accumulates straight into param.grad.  dw must hold the addend (zeros to overwrite).
+DMP_API int dmp_conv_igemm_wgrad_strided(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                         int pad, int stride, int kcrs, cudaStream_t stream) {
+    DMP_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "dmp_conv_igemm_wgrad: channel counts must be multiples of 8");
+    DMP_REQUIRE(stride >= 1 && stride <= 4 && KH * KW <= 49, "dmp_conv_igemm_wgrad: unsupported geometry");
+    const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
+    ConvParams p;
+    memset(&p, 0, sizeof(p));
+    p.Nimg = N; p.Ho = Ho; p.Wo = Wo; p.Cin = Cin; p.Cout = Cout; p.KH = KH; p.KW = KW; p.pad = pad;
+    p.kcrs = kcrs; p.wstride = stride;
+    patch_shape(Ho, Wo, 64, &p.BW, &p.BH, &p.BNI);
+    p.tiles_w = dmp_ceil_div(Wo, p.BW); p.tiles_h = dmp_ceil_div(Ho, p.BH); p.tiles_n = dmp_ceil_div(N, p.BNI);
     const int bn = Cin > 64 ? 128 : 64;
     p.m_tiles = dmp_ceil_div(Cout, BM);
     p.n_tiles = dmp_ceil_div(Cin, bn);
-    p.D = dwp; p.ldd = (long long)KH * KW * Cin;
+    p.D = dw; p.ldd = (long long)KH * KW * Cin;
     const int total_patches = p.tiles_w * p.tiles_h * p.tiles_n;
     const int base_items = p.m_tiles * p.n_tiles * KH * KW;
     int splits = dmp_ceil_div(2 * dmp_num_sms(), base_items);
@@ -438,8 +534,8 @@ DMP_API int dmp_conv_igemm_wgrad(const void* dy, const void* x, float* dwp, int 
     p.patches_per_split = dmp_ceil_div(total_patches, splits);
     p.splits = dmp_ceil_div(total_patches, p.patches_per_split);
     CUtensorMap tmA, tmB;
-    if (int rc = make_tmap_act(&tmA, dy, N, H, W, Cout, p.BW, p.BH, p.BNI)) return rc;
-    if (int rc = make_tmap_act(&tmB, x, N, H, W, Cin, p.BW, p.BH, p.BNI)) return rc;
+    if (int rc = make_tmap_act(&tmA, dy, N, Ho, Wo, Cout, p.BW, p.BH, p.BNI, 1)) return rc;
+    if (int rc = make_tmap_act(&tmB, x, N, H, W, Cin, p.BW, p.BH, p.BNI, stride)) return rc;
     const long long items = (long long)base_items * p.splits;
     const int smem_bytes = STAGES * (BM * BK * 2 + bn * BK * 2) + 1024 + 256;
     long long grid = (long long)dmp_num_sms() * (smem_bytes <= 110 * 1024 ? 2 : 1);
@@ -454,4 +550,11 @@ DMP_API int dmp_conv_igemm_wgrad(const void* dy, const void* x, float* dwp, int 
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
+}
+
+// stride-1 'same' convolution, dwp in [Cout][kh][kw][Cin] order (kept for callers of the round-1 ABI)
+DMP_API int dmp_conv_igemm_wgrad(const void* dy, const void* x, float* dwp, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                 int pad, cudaStream_t stream) {
+    DMP_REQUIRE(KH == 2 * pad + 1 && KW == 2 * pad + 1, "dmp_conv_igemm_wgrad: only 'same' stride-1 convolutions");
+    return dmp_conv_igemm_wgrad_strided(dy, x, dwp, N, H, W, Cin, Cout, KH, KW, pad, 1, 0, stream);
 }

@@ -69,7 +69,8 @@ __global__ void stem_wgrad_kernel(const bf16* __restrict__ dy, const void* __res
                                   int stride, int pad, int Ho, int Wo) {
     const int T = Cin * KH * KW;
     const int G = Cout >> 3;
-    const int tap = threadIdx.x / G, cg = threadIdx.x % G;
+    const int tc = blockIdx.y * blockDim.x + threadIdx.x;  // (tap, 8 couts) pairs beyond one block go to further blockIdx.y slices
+    const int tap = tc / G, cg = tc % G;
     if (tap >= T) return;
     const int ci = tap / (KH * KW), kh = (tap / KW) % KH, kw = tap % KW;
     const long long npix = (long long)N * Ho * Wo;
@@ -308,7 +309,6 @@ DMP_API int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, flo
     DMP_REQUIRE(Cin >= 1 && Cin <= 4 && Cout % 8 == 0, "dmp_stem_conv_wgrad: needs Cin<=4 and Cout%%8==0");
     const int T = Cin * KH * KW;
     const int threads = T * (Cout / 8);
-    DMP_REQUIRE(threads <= 1024, "dmp_stem_conv_wgrad: taps*Cout/8 = %d exceeds 1024 threads", threads);
     const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
     if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)T * Cout, stream));
     if (KH == 3 && KW == 3 && (Cin == 3 || Cin == 1) && Cout % 32 == 0) {
@@ -326,8 +326,9 @@ DMP_API int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, flo
         DMP_COUNT_LAUNCH(1);
         return 0;
     }
-    const int block = ((threads + 31) / 32) * 32;
-    const int grid = dmp_num_sms() * 4;
+    const int slices = (threads + 511) / 512;  // <= 512 threads per block: the kernel needs ~100 registers per thread
+    const int block = (((threads + slices - 1) / slices + 31) / 32) * 32;
+    const dim3 grid(dmp_num_sms() * 4 / slices + 1, slices);
     stem_wgrad_kernel<<<grid, block, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, Cin, H, W, Cout, KH, KW, stride, pad,
                                                   Ho, Wo);
     DMP_LAUNCH_CHECK();

@@ -205,11 +205,15 @@ def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
     if (kh, kw) == (3, 3) and g == cin == cout and conv.padding == (1, 1) and conv.stride in ((1, 1), (2, 2)) \
             and cin % 8 == 0:
         return "dw"
-    if g == 1 and kh == kw and kh % 2 == 1 and kh > 1 and conv.stride == (1, 1) and conv.padding == (kh // 2, kh // 2) \
-            and cin % 64 == 0 and cout % 8 == 0:
-        return "igemm"
+    if g == 1 and kh == kw and kh % 2 == 1 and kh > 1 and conv.padding == (kh // 2, kh // 2) and cin % 64 == 0 and cout % 8 == 0 \
+            and kh * kw <= 49:
+        if conv.stride == (1, 1):
+            return "igemm"
+        # stride 2: TMA element strides forward / weight gradient, parity-class data gradient (needs even H, W and Cout % 64 == 0)
+        if conv.stride == (2, 2) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and cout % 64 == 0:
+            return "igemm"
     if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
-            and cin * kh * kw * cout * 4 <= 48 * 1024 and cin * kh * kw * (cout // 8) <= 1024:
+            and cin * kh * kw * cout * 4 <= 48 * 1024:
         return "stem"
     return "generic"
 
@@ -270,8 +274,9 @@ def _conv_fwd_cuda(x, w, conv, kind, stats=None):
         kh, kw = conv.kernel_size
         cout = conv.out_channels
         wp = weight_bf16(w).permute(0, 2, 3, 1).reshape(cout, kh * kw * cin).contiguous()  # [Cout][kh][kw][Cin]
-        y = _cl_empty(N, cout, H, W, x.device)
-        _ck(lib.dmp_conv_igemm_fwd(x.data_ptr(), wp.data_ptr(), None, y.data_ptr(), N, H, W, cin, cout, kh, kw, conv.padding[0], sp),
+        st, pd = conv.stride[0], conv.padding[0]
+        y = _cl_empty(N, cout, (H + 2 * pd - kh) // st + 1, (W + 2 * pd - kw) // st + 1, x.device)
+        _ck(lib.dmp_conv_igemm_fwd_strided(x.data_ptr(), wp.data_ptr(), None, y.data_ptr(), N, H, W, cin, cout, kh, kw, pd, st, sp),
             "conv igemm fwd")
         _note("conv_dense:tcgen05_igemm")
         return y, x
@@ -359,8 +364,15 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx, link_in=None):
         _, cin, H, W = x.shape
         kh, kw = conv.kernel_size
         cout = conv.out_channels
+        st = conv.stride[0]
         if need_dx:
-            if cout % 64 == 0:
+            if st == 2:
+                # four output-parity implicit GEMMs over dy, each with the taps that reach that parity (no inserted zeros)
+                wd = weight_bf16(w).permute(1, 2, 3, 0).reshape(cin, kh * kw * cout).contiguous()
+                dx = _cl_empty(N, cin, H, W, x.device)
+                _ck(lib.dmp_conv_igemm_dgrad_s2(dy.data_ptr(), wd.data_ptr(), dx.data_ptr(), N, H, W, cin, cout, kh, kw,
+                                                conv.padding[0], sp), "conv igemm dgrad (stride 2)")
+            elif cout % 64 == 0:
                 # dx = conv(dy, flipped filter with in/out channels swapped): the same implicit-GEMM kernel
                 wd = weight_bf16(w).permute(1, 2, 3, 0).flip(1, 2).reshape(cin, kh * kw * cout).contiguous()
                 dx = _cl_empty(N, cin, H, W, x.device)
@@ -371,14 +383,11 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx, link_in=None):
                                                          (0, 0), conv.groups, (True, False, False))[0]
 
         def write_dw(dst, accumulate):
-            dwp = torch.zeros((cout, kh * kw * cin), device=x.device, dtype=torch.float32)
-            _ck(lib.dmp_conv_igemm_wgrad(dy.data_ptr(), x.data_ptr(), dwp.data_ptr(), N, H, W, cin, cout, kh, kw, conv.padding[0], _sp()),
-                "conv igemm wgrad")
-            g = dwp.view(cout, kh, kw, cin).permute(0, 3, 1, 2)
-            if accumulate:
-                dst.add_(g)
-            else:
-                dst.copy_(g)
+            # the epilogue accumulates straight into the [Cout][Cin][KH][KW] gradient: no temporary, no permute, no add
+            if not accumulate:
+                dst.zero_()
+            _ck(lib.dmp_conv_igemm_wgrad_strided(dy.data_ptr(), x.data_ptr(), dst.data_ptr(), N, H, W, cin, cout, kh, kw,
+                                                 conv.padding[0], st, 1, _sp()), "conv igemm wgrad")
 
         return dx, write_dw
     # generic

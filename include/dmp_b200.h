@@ -60,6 +60,15 @@ int dmp_conv_igemm_fwd(const void* x, const void* wp, const float* bias, void* y
                        int KW, int pad, dmp_stream_t stream);
 int dmp_conv_igemm_wgrad(const void* dy, const void* x, float* dwp, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
                          dmp_stream_t stream);
+/* Strided (1 or 2) KxK forward with TMA element strides; stride-2 data gradient as four parity-class implicit GEMMs over dy (wd =
+ * weight permuted to [Cin][kh][kw][Cout]); weight gradient with strided x boxes, optionally (kcrs) accumulated straight into the
+ * [Cout][Cin][KH][KW] parameter gradient.  ResNet-18/50 down-sampling blocks. */
+int dmp_conv_igemm_fwd_strided(const void* x, const void* wp, const float* bias, void* y, int N, int H, int W, int Cin, int Cout, int KH,
+                               int KW, int pad, int stride, dmp_stream_t stream);
+int dmp_conv_igemm_dgrad_s2(const void* dy, const void* wd, void* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
+                            dmp_stream_t stream);
+int dmp_conv_igemm_wgrad_strided(const void* dy, const void* x, float* dw, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
+                                 int stride, int kcrs, dmp_stream_t stream);
 
 /* ------------------------------------------------------------------ optimizer (csrc/kernels/sgd.cu; R/data_parallel.py:90-91,111)
  * hp_dev = device {lr, momentum, weight_decay, grad_scale}. */

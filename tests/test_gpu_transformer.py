@@ -157,3 +157,31 @@ def test_batched_gemm_strided_operands(layout):
                                         M * nh * N, M, N, K, nh, nb, _sp()))
     torch.cuda.synchronize()
     _close(D.permute(0, 2, 1, 3), ref, 2e-2, 2e-2 * ref.abs().max().item(), "batched gemm layout %d" % layout)
+
+
+@pytest.mark.parametrize("N,H,Cin,Cout,k,stride", [(4, 16, 64, 128, 3, 2), (2, 32, 128, 256, 3, 2), (3, 8, 256, 512, 3, 2), (2, 14, 64, 64, 3, 2),
+                                                     (2, 16, 64, 64, 3, 1), (2, 12, 128, 64, 5, 1), (8, 64, 3, 64, 7, 2), (4, 32, 3, 64, 3, 1)])
+def test_dense_conv_paths_without_library_kernels(N, H, Cin, Cout, k, stride):
+    """Dense KxK convolutions of the ResNet / VGG family (stride 1 and 2, 7x7 stem) through the op layer: forward, data gradient
+    and weight gradient against F.conv2d in fp32, and no library convolution on the path."""
+    from distributed_model_parallel_b200.ops import functional as OF
+
+    torch.manual_seed(N + H + Cin + Cout + k)
+    conv = torch.nn.Conv2d(Cin, Cout, k, stride, k // 2, bias=False).cuda()
+    x = torch.randn(N, Cin, H, H, device="cuda")
+    stem = Cin <= 4
+    xk = x.clone().requires_grad_(not stem)
+    OF.path_counts.clear()
+    y = OF.conv_bn_act(xk if stem else xk.bfloat16().contiguous(memory_format=torch.channels_last), conv, None, relu=False)
+    assert "conv_generic:cudnn" not in OF.path_counts, dict(OF.path_counts)
+    xr = x.bfloat16().float().requires_grad_(True) if not stem else x.clone().requires_grad_(True)
+    wr = conv.weight.detach().bfloat16().float().requires_grad_(True) if not stem else conv.weight.detach().clone().requires_grad_(True)
+    yr = F.conv2d(xr, wr, None, stride, k // 2)
+    _close(y, yr, 2e-2, 2e-2 * yr.abs().max().item(), "conv forward")
+    dy = torch.randn_like(yr) * 0.5
+    y.backward(dy.to(y.dtype))
+    yr.backward(dy.bfloat16().float())
+    torch.cuda.synchronize()
+    _close(conv.weight.grad, wr.grad, 2e-2, 2e-2 * wr.grad.abs().max().item(), "conv weight gradient")
+    if not stem:
+        _close(xk.grad, xr.grad, 2e-2, 2e-2 * xr.grad.abs().max().item(), "conv data gradient")
