@@ -76,6 +76,10 @@ _KERNEL_SIGS = {
     "dmp_bn_bwd_fused": (i32, [vp, vp, vp, i32, vp, vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, vp, vp]),
     "dmp_bn_stats_finalize_noalloc": (i32, [vp, i32, i64, i32, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, vp]),
     "dmp_bn_noalloc_max_channels": (i32, []),
+    # SyncBatchNorm with the cross-GPU combine inside the kernel (csrc/comm/syncbn.cu)
+    "dmp_syncbn_ws_bytes": (i64, [i32]),
+    "dmp_syncbn_fwd": (i32, [vp, vp, vp, i64, i32, vp, vp, vp, vp, vp, f32, f32, vp, vp, vp, vp, i32, i32, vp, i32, vp]),
+    "dmp_syncbn_bwd": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, vp, vp, i32, i32, vp, vp]),
     # depthwise conv
     "dmp_dwconv3x3_fwd": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),
     "dmp_dwconv3x3_dgrad": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, vp]),

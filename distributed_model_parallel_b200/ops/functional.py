@@ -507,6 +507,25 @@ def _bn_forward_cuda(y_raw, gamma, beta, residual, bn, relu, sync, sums=None):
             return out, mean, invstd, float(M), True
         if rc != 1:
             _ck(rc, "bn fwd fused")
+    if training and sync is not None and sync.equal_batches and (bn.momentum is not None or not bn.track_running_stats):
+        # SyncBatchNorm in ONE launch: statistics -> grid barrier -> cross-GPU flag barrier + peer loads of all partial sums ->
+        # grid barrier -> normalise (+residual, +ReLU)
+        ws, total = sync.fused_workspace((bn._dmp_key, "f"), C, dev)
+        mean = torch.empty(C, device=dev, dtype=torch.float32)
+        invstd = torch.empty(C, device=dev, dtype=torch.float32)
+        out = torch.empty_like(y_raw)
+        track = bn.track_running_stats
+        rc = lib.dmp_syncbn_fwd(y_raw.data_ptr(), _native.ptr(residual), out.data_ptr(), M, C, _native.ptr(gamma), _native.ptr(beta),
+                                _native.ptr(bn.running_mean if track else None), _native.ptr(bn.running_var if track else None),
+                                _native.ptr(bn.num_batches_tracked if track else None), float(bn.momentum or 0.1), float(bn.eps),
+                                mean.data_ptr(), invstd.data_ptr(), ws.ptrs, sync._state.ptrs, sync.rank, sync.world_size,
+                                total.data_ptr(), 1 if relu else 0, sp)
+        if rc == 0:
+            sync.kernel_launches += 1
+            _note("bn:syncbn_fused1")
+            return out, mean, invstd, float(M) * sync.world_size, True
+        if rc != 1:
+            _ck(rc, "syncbn fwd fused")
     if training:
         accum = torch.empty(2 * C, device=dev, dtype=torch.float64)
         mean = torch.empty(C, device=dev, dtype=torch.float32)
@@ -602,6 +621,27 @@ def _bn_backward_cuda(ctx, dout, out, y_raw, mean, invstd, gamma, bn, relu, need
             return dy, dres_t, dg_t, db_t
         if rc != 1:
             _ck(rc, "bn bwd fused")
+    if ctx.bn_train and ctx.sync is not None and ctx.sync.equal_batches:
+        sync = ctx.sync
+        gw, gb = (bn.weight if needs_gamma else None), (bn.bias if needs_beta else None)
+        (dg_t, db_t), acc_flag, direct = _param_grad_targets((gw, gb), C, y_raw.device)
+        ws, total = sync.fused_workspace((bn._dmp_key, "b"), C, y_raw.device)
+        dy = torch.empty_like(y_raw)
+        dres_t = torch.empty_like(y_raw) if ctx.has_res else None
+        rc = lib.dmp_syncbn_bwd(dout.data_ptr(), _native.ptr(out if relu else None), y_raw.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+                                _native.ptr(gamma), dy.data_ptr(), _native.ptr(dres_t), _native.ptr(dg_t), _native.ptr(db_t), acc_flag,
+                                M, C, 1 if relu else 0, ws.ptrs, sync._state.ptrs, sync.rank, sync.world_size, total.data_ptr(), sp)
+        if rc == 0:
+            sync.kernel_launches += 1
+            if direct:
+                for p in (gw, gb):
+                    if p is not None:
+                        for cb in grad_ready_callbacks:
+                            cb(p)
+                return dy, dres_t, None, None
+            return dy, dres_t, dg_t, db_t
+        if rc != 1:
+            _ck(rc, "syncbn bwd fused")
     if ctx.bn_train:
         dy = torch.empty_like(y_raw)
         dres_t = torch.empty_like(y_raw) if ctx.has_res else None

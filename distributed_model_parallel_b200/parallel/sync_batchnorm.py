@@ -5,11 +5,13 @@ forward = local statistics -> cross-rank combine -> normalise; backward = local 
 cross-rank sum -> dx.  The reference only mentions it ("prepare for sync batch norm layers",
 /root/reference/Readme.md:151); BASELINE.json config 3 (ResNet-50 DDP) needs it.
 
-On CUDA the combine is NOT a library collective: the BN statistics kernel leaves per-channel double sums in a
-peer-visible slot and one small kernel (``dmp_allreduce_fused`` in fp64 one-shot mode) barriers with the peers and
-peer-loads every rank's partial sums -- ~2C doubles per layer, latency-bound, so it rides the compute stream
-between the statistics and the apply kernels of the fused ``conv_bn_act`` op.  CPU tensors (gloo tests) use
-``torch.distributed.all_reduce`` inside a small autograd Function.
+On CUDA the combine is NOT a library collective and not even a separate launch: the BatchNorm kernel accumulates its
+per-channel double sums in a peer-visible workspace, and between its statistics pass and its normalisation pass block 0
+barriers with the peers (flag pads in peer memory) and peer-loads every rank's partial sums (csrc/comm/syncbn.cu,
+``dmp_syncbn_fwd`` / ``dmp_syncbn_bwd``: ONE cooperative launch per layer and direction).  Shapes that cannot be launched
+cooperatively, and ragged batches (``equal_batches=False``), use the split path: statistics kernel -> small fp64 one-shot
+all-reduce kernel -> finalize -> apply.  CPU tensors (gloo tests) use ``torch.distributed.all_reduce`` inside a small
+autograd Function.
 """
 from __future__ import annotations
 
@@ -48,6 +50,23 @@ class SyncContext:
             buf = self._symm.alloc(n * 8)
             ent = (buf, torch.empty(n, dtype=torch.float64, device=device))
             self._slots[key] = ent
+        return ent
+
+    def fused_workspace(self, key, C, device):
+        """(peer-visible workspace, local totals buffer) of one (layer, direction) for the single-launch kernels; allocated
+        collectively on first use (every rank meets its layers in the same order)."""
+        ent = self._slots.get(("fused",) + tuple(key))
+        if ent is None:
+            if self._symm is None:
+                from .symm import ProcessSymmGroup
+                self._symm = ProcessSymmGroup(self.group, device)
+                self._state = self._symm.new_state()
+            buf = self._symm.alloc(int(_native.kernels().dmp_syncbn_ws_bytes(C)))
+            buf.local.view(torch.uint8).zero_()
+            torch.cuda.synchronize(device)
+            dist.barrier(group=self.group)  # nobody may start accumulating into a peer-read workspace before all are zeroed
+            ent = (buf, torch.empty(2 * C, dtype=torch.float64, device=device))
+            self._slots[("fused",) + tuple(key)] = ent
         return ent
 
     def all_reduce_sum(self, key, vec: torch.Tensor) -> torch.Tensor:

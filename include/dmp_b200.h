@@ -119,6 +119,19 @@ int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int dtype, co
  * One array per GPU shared by all calls: each call clears what it uses; calls that can overlap on a GPU race.  The first call
  * on a device resolves the array's address (cudaGetSymbolAddress) -- make it at start-up, before any stream capture.
  * Calls no cudaMalloc/cudaFree. */
+/* SyncBatchNorm, one cooperative launch per direction (csrc/comm/syncbn.cu): local sums -> grid barrier -> flag barrier with the
+ * peers + peer loads of every rank's partial sums -> grid barrier -> normalise / dx.  ws_ptrs[W] = every rank's peer-mapped
+ * workspace of dmp_syncbn_ws_bytes(C) (zeroed once), state_ptrs[W] = communicator states.  Return 1 = not launchable
+ * cooperatively (use dmp_bn_stats + dmp_allreduce_fused + dmp_bn_finalize + dmp_bn_apply).  (R/Readme.md:151; torch
+ * nn/modules/_functions.py:39-179 is the behaviour matched.) */
+long long dmp_syncbn_ws_bytes(int C);
+int dmp_syncbn_fwd(const void* x, const void* residual, void* y, long long M, int C, const float* gamma, const float* beta,
+                   float* running_mean, float* running_var, long long* num_batches_tracked, float momentum, float eps, float* mean,
+                   float* invstd, void* const* ws_ptrs, void* const* state_ptrs, int rank, int W, double* total, int relu,
+                   dmp_stream_t stream);
+int dmp_syncbn_bwd(const void* dy, const void* y, const void* x, const float* mean, const float* invstd, const float* gamma, void* dx,
+                   void* dres, float* dgamma, float* dbeta, int accumulate_params, long long M, int C, int relu, void* const* ws_ptrs,
+                   void* const* state_ptrs, int rank, int W, double* total, dmp_stream_t stream);
 /* BatchNorm backward from reductions that already exist (sums = {sum g, sum g*xhat} + ticket, g already ReLU-masked): one
  * elementwise pass, dx may alias g; block 0 writes dgamma/dbeta, the last block clears the sums. */
 int dmp_bn_bwd_dx_sums(const void* g, const void* x, int dtype, const float* mean, const float* invstd, const float* gamma, void* dx,

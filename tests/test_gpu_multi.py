@@ -333,21 +333,30 @@ def _w_ddp(rank, world, port, mode):
             x = torch.randn(32, 3, 16, 16, device="cuda") if not use_graph else torch.randn(32, 3, 32, 32, device="cuda")
             y = torch.randint(0, 10, (32,), device="cuda")
             a = s1(x, y).clone()
-            b = s2(x, y).clone() if not use_graph else a
+            b = s2(x, y).clone()  # the torch-DDP twin runs every mode (graph mode used to be compared with itself)
             torch.cuda.synchronize()
             losses.append((a[0].item(), b[0].item()))
+            if it == 1:
+                # distance between the two runs relative to the distance travelled from the common start, after TWO updates:
+                # on random data at this learning rate the trajectories are chaotic -- two runs of the very same configuration
+                # (fp32 atomics in another order) are 0.9 apart by this measure after six steps -- so later steps are compared
+                # through their losses only
+                num = sum(((p - q).float() ** 2).sum() for p, q in zip(ours.module.parameters(), ref.module.parameters())).sqrt()
+                den = sum(((q - b0).float() ** 2).sum() for q, b0 in zip(ref.module.parameters(), base.parameters())).sqrt()
+                rel = (num / den).item()
     ours.check_health()
-    # distance between the two runs relative to the distance travelled from the common start
-    num = sum(((p - q).float() ** 2).sum() for p, q in zip(ours.module.parameters(), ref.module.parameters())).sqrt()
-    den = sum(((q - b).float() ** 2).sum() for q, b in zip(ref.module.parameters(), base.parameters())).sqrt()
-    rel = (num / den).item()
+    if rank == 0:
+        print("ddp end-to-end [%s]: parameter distance / distance travelled = %.4f, losses %s" % (mode, rel, losses[-1]), flush=True)
     if mode == "reference_ops":   # fp32 library ops: only the summation order of the all-reduce differs
         assert rel < 1e-2, rel
-    elif mode == "kernels":       # bf16 kernels with atomics: looser
-        assert rel < 0.3, rel
-    if not use_graph:
-        for a, b in losses:
-            assert abs(a - b) < 0.05 * max(1.0, abs(b)), losses
+    elif mode == "kernels":       # bf16 kernels with fp32 atomics on both sides, small network
+        assert rel < 0.12, rel
+    else:
+        # full MobileNetV2, captured step against the eager torch-DDP twin: one bf16 gradient of this network has a cosine of
+        # ~0.96 with its fp32 value (tests/test_gpu_models.py), i.e. two bf16 evaluations differ by up to ~0.3 of their norm
+        assert rel < 0.4, rel
+    for i, (a, b) in enumerate(losses):
+        assert abs(a - b) < (0.03 if i < 3 else 0.15) * max(1.0, abs(b)), losses
     for p in list(ours.module.parameters())[:8]:
         pl = [torch.empty_like(p) for _ in range(world)]
         dist.all_gather(pl, p.detach().clone())
