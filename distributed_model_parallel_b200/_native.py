@@ -103,6 +103,7 @@ _KERNEL_SIGS = {
     "dmp_mc_xp_bind_map": (i32, [vp, vp, vp]),
     "dmp_mc_xp_destroy": (i32, [vp]),
     "dmp_allreduce_nvls": (i32, [vp, vp, i32, i32, i64, f32, i32, vp]),
+    "dmp_allreduce_nvls_sgd": (i32, [vp, vp, vp, vp, vp, vp, i32, vp, i32, i32, i64, f32, i32, vp]),
     # peer-memory collectives and plumbing (csrc/comm/collectives.cu)
     "dmp_comm_state_bytes": (C.c_longlong, []),
     "dmp_comm_max_ranks": (C.c_int, []),

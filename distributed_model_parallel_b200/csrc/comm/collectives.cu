@@ -248,6 +248,70 @@ allreduce_nvls_kernel(float* mc, PeerPtrs flags, uint32_t* epoch_mem, uint32_t* 
 }
 
 // ------------------------------------------------------------------------------------------------
+// NVLS all-reduce FUSED with SGD: gradients, fp32 masters and bf16 shadows of a bucket all live in multicast-bound buffers.
+// Rank r owns slice r: multimem.ld_reduce pulls the switch-side SUM of the W gradient copies (S/W bytes cross this GPU's link
+// instead of S(W-1)/W), the momentum update runs on the local master / momentum, and three multimem.st push the new fp32
+// parameters, their bf16 shadow and zeros for the gradient slice into EVERY copy (the switch replicates: 10 bytes per element
+// leave this GPU once instead of 6 bytes to each of W-1 peers).  Per GPU and element that is (4 + 10)/W bytes on the wire
+// against 10 (W-1)/W for the peer-load/peer-store two-shot kernel above.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(DMP_COMM_THREADS)
+allreduce_nvls_sgd_kernel(float* mc_grad, float* mc_master, bf16* mc_shadow, const float* __restrict__ master,
+                          float* __restrict__ momentum, const float* __restrict__ hp, int nesterov, PeerPtrs flags,
+                          uint32_t* epoch_mem, uint32_t* status, int rank, int W, long long n8, float scale) {
+    uint32_t epoch = epoch_mem[blockIdx.x];
+    __syncthreads();
+    if (!barrier_ranks(flags, rank, W, epoch + 1, status, false)) return;  // every rank's gradients are in place
+    const long long per = (n8 + W - 1) / W;
+    const long long lo = per * rank;
+    long long hi = lo + per;
+    if (hi > n8) hi = n8;
+    const float lr = hp[0], mu = hp[1], wd = hp[2];
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long v = lo + blockIdx.x * (long long)blockDim.x + threadIdx.x; v < hi; v += stride) {
+        float g[8], p[8], m[8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                         : "=f"(g[4 * h]), "=f"(g[4 * h + 1]), "=f"(g[4 * h + 2]), "=f"(g[4 * h + 3])
+                         : "l"((float4*)mc_grad + 2 * v + h)
+                         : "memory");
+            const float4 pv = *((const float4*)master + 2 * v + h);
+            const float4 mv = *((const float4*)momentum + 2 * v + h);
+            p[4 * h] = pv.x; p[4 * h + 1] = pv.y; p[4 * h + 2] = pv.z; p[4 * h + 3] = pv.w;
+            m[4 * h] = mv.x; m[4 * h + 1] = mv.y; m[4 * h + 2] = mv.z; m[4 * h + 3] = mv.w;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float d = g[j] * scale + wd * p[j];
+            m[j] = mu * m[j] + d;
+            p[j] -= lr * (nesterov ? (d + mu * m[j]) : m[j]);
+        }
+        uint32_t sh[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            bf162 b = __floats2bfloat162_rn(p[2 * j], p[2 * j + 1]);
+            sh[j] = *(uint32_t*)&b;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            *((float4*)momentum + 2 * v + h) = make_float4(m[4 * h], m[4 * h + 1], m[4 * h + 2], m[4 * h + 3]);
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"((float4*)mc_master + 2 * v + h),
+                         "f"(p[4 * h]), "f"(p[4 * h + 1]), "f"(p[4 * h + 2]), "f"(p[4 * h + 3])
+                         : "memory");
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%1,%1,%1};" ::"l"((float4*)mc_grad + 2 * v + h), "f"(0.f)
+                         : "memory");
+        }
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"((float4*)mc_shadow + v),
+                     "f"(__uint_as_float(sh[0])), "f"(__uint_as_float(sh[1])), "f"(__uint_as_float(sh[2])),
+                     "f"(__uint_as_float(sh[3]))
+                     : "memory");
+    }
+    if (!barrier_ranks(flags, rank, W, epoch + 2, status)) return;  // system-scope fence inside: the multicast stores are visible
+    if (threadIdx.x == 0) epoch_mem[blockIdx.x] = epoch + 2;
+}
+
+// ------------------------------------------------------------------------------------------------
 // broadcast: the source rank stores its buffer into every destination (peer stores, or one multimem.st
 // through an NVLS multicast mapping).  Optional fp32 -> bf16 cast into a second set of destinations.
 // With flags == null pointers (single-process DataParallel) ordering comes from stream events instead.
@@ -418,6 +482,30 @@ DMP_API int dmp_allreduce_nvls(void* mc, void* const* state, int rank, int W, lo
     uint32_t* status = epoch_mem + DMP_COMM_MAX_BLOCKS;
     const int grid = comm_grid(nvec / W, max_blocks);
     allreduce_nvls_kernel<<<grid, DMP_COMM_THREADS, 0, stream>>>((float*)mc, f, epoch_mem, status, rank, W, nvec, scale);
+    DMP_LAUNCH_CHECK();
+    DMP_COUNT_LAUNCH(1);
+    return 0;
+}
+
+// All-reduce (mean) + SGD through the switch: mc_grad / mc_master / mc_shadow are the multicast addresses of the bucket's gradient,
+// fp32 master and bf16 shadow buffers (every rank bound its copy), master / momentum the LOCAL unicast views of this rank's
+// master copy and its private momentum.  n: element count, a multiple of 8*W.  After the call every rank holds identical masters
+// and shadows and a zeroed gradient bucket.
+DMP_API int dmp_allreduce_nvls_sgd(void* mc_grad, void* mc_master, void* mc_shadow, const float* master, float* momentum,
+                                   const float* hp_dev, int nesterov, void* const* state, int rank, int W, long long n, float scale,
+                                   int max_blocks, cudaStream_t stream) {
+    DMP_REQUIRE(mc_grad && mc_master && mc_shadow && master && momentum && hp_dev, "dmp_allreduce_nvls_sgd: null buffer");
+    DMP_REQUIRE(W >= 2 && W <= DMP_MAX_RANKS && rank >= 0 && rank < W, "dmp_allreduce_nvls_sgd: bad rank / world size");
+    DMP_REQUIRE(n % (8 * (long long)W) == 0, "dmp_allreduce_nvls_sgd: element count must be a multiple of 8*W");
+    const long long n8 = n / 8;
+    if (n8 == 0) return 0;
+    PeerPtrs f = make_ptrs(state, W);
+    uint32_t* st = (uint32_t*)state[rank];
+    uint32_t* epoch_mem = st + FLAGS_WORDS;
+    uint32_t* status = epoch_mem + DMP_COMM_MAX_BLOCKS;
+    const int grid = comm_grid(n8 / W, max_blocks);
+    allreduce_nvls_sgd_kernel<<<grid, DMP_COMM_THREADS, 0, stream>>>((float*)mc_grad, (float*)mc_master, (bf16*)mc_shadow, master, momentum,
+                                                                      hp_dev, nesterov, f, epoch_mem, status, rank, W, n8, scale);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;

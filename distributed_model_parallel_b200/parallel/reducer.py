@@ -169,6 +169,7 @@ class PeerBackend:
 
     name = "peer-kernels"
     supports_fused = True
+    NVLS_FUSED_MIN_WORLD = 4
 
     def __init__(self, group=None, device=None, oneshot_max_bytes: Optional[int] = None, max_blocks: Optional[int] = None):
         from .symm import DTYPE_CODE, ProcessSymmGroup
@@ -192,15 +193,38 @@ class PeerBackend:
         self.nvls = os.environ.get("DMP_DDP_NVLS", "0") == "1" and self.world_size > 1
         self.nvls_min_bytes = int(os.environ.get("DMP_DDP_NVLS_MIN_BYTES", 8 << 20))
         self.nvls_launches = 0
+        # NVLS all-reduce FUSED with SGD (gradient bucket, fp32 master and bf16 shadow in multicast buffers; see
+        # allreduce_nvls_sgd_kernel).  DMP_DDP_NVLS_FUSED: "0" off, "1" on, "auto" (default) = on from NVLS_FUSED_MIN_WORLD ranks
+        # for buckets of at least DMP_DDP_NVLS_FUSED_MIN_BYTES -- the switch-side reduction moves (4+10)/W bytes per element over
+        # each GPU's link where the peer-load two-shot moves 10 (W-1)/W, which only pays once W is large enough
+        mode = os.environ.get("DMP_DDP_NVLS_FUSED", "auto")
+        self.nvls_fused = self.world_size > 1 and (mode == "1" or (mode == "auto" and self.world_size >= self.NVLS_FUSED_MIN_WORLD))
+        self.nvls_fused_min_bytes = int(os.environ.get("DMP_DDP_NVLS_FUSED_MIN_BYTES", 1 << 20))
+        self.nvls_fused_launches = 0
 
     def pad_multiple(self, dtype) -> int:
         esz = torch.empty((), dtype=dtype).element_size()
-        return max(ALIGN_ELEMS, (16 // esz) * max(1, self.world_size))
+        m = max(ALIGN_ELEMS, (16 // esz) * max(1, self.world_size))
+        if self.nvls_fused:
+            m = max(m, 8 * self.world_size)  # the NVLS fused kernel works on groups of 8 elements per rank slice
+        return m
+
+    def wants_nvls_fused(self, numel, dtype) -> bool:
+        return self.nvls_fused and dtype == torch.float32 and numel * 4 >= self.nvls_fused_min_bytes
 
     def alloc_flat(self, numel, dtype, device, symmetric=True):
         if self.symm is None or not symmetric:
             return torch.zeros(numel, dtype=dtype, device=device), None
         esz = torch.empty((), dtype=dtype).element_size()
+        if symmetric == "nvls_fused":  # a multicast buffer or nothing: the caller checked wants_nvls_fused on every rank alike
+            from .symm import ProcessMulticast
+            try:
+                mc = ProcessMulticast(numel * esz, self.group, self.device)
+                mc.local.zero_()
+                return mc.view(dtype, numel), mc
+            except RuntimeError:  # no multicast on this platform (every rank takes this branch together)
+                self.nvls_fused = False
+                symmetric = True
         if self.nvls and symmetric == "nvls_ok" and dtype == torch.float32 and numel * esz >= self.nvls_min_bytes:
             from .symm import ProcessMulticast
             try:
@@ -239,6 +263,14 @@ class PeerBackend:
             return
         algo = 0 if nbytes <= self.oneshot_max_bytes else 1
         scale = 1.0 / W
+        if fused is not None and fused.nvls is not None:
+            g_mc, m_mc, s_mc = fused.nvls
+            _native.check(lib.dmp_allreduce_nvls_sgd(g_mc, m_mc, s_mc, fused.master.data_ptr(), fused.momentum.data_ptr(),
+                                                     fused.hp.data_ptr(), 1 if fused.nesterov else 0, self.state.ptrs, self.rank, W,
+                                                     flat.numel(), scale, self.max_blocks, sp), "allreduce nvls + sgd")
+            self.nvls_fused_launches += 1
+            self.kernel_launches += 1
+            return
         if fused is None and hasattr(bucket.symm, "mc_ptr"):  # bucket lives in a multicast buffer: reduce inside the switch
             _native.check(lib.dmp_allreduce_nvls(bucket.symm.mc_ptr, self.state.ptrs, self.rank, W, flat.numel(), scale,
                                                  self.max_blocks, sp), "allreduce nvls")
@@ -284,6 +316,7 @@ class FusedSGDState:
     def __init__(self, master, momentum, shadow, hp, nesterov, master_symm=None, shadow_symm=None):
         self.master, self.momentum, self.shadow, self.hp, self.nesterov = master, momentum, shadow, hp, nesterov
         self.master_symm, self.shadow_symm = master_symm, shadow_symm
+        self.nvls = None  # (gradient, master, shadow) multicast addresses when the bucket is reduced inside the switch
 
 
 class Bucket:
@@ -384,7 +417,13 @@ class Reducer:
         bucket_of = [0] * len(self.params)
         for b, idxs in enumerate(assignment):
             # plain gradient buckets (no fused optimizer state to ship to peers) may live in an NVLS multicast buffer
-            bk = Bucket(b, idxs, [self.params[i] for i in idxs], self.backend, "nvls_ok" if self.fused_cfg is None else True)
+            mode = "nvls_ok" if self.fused_cfg is None else True
+            if self.fused_cfg is not None and hasattr(self.backend, "wants_nvls_fused"):
+                ps = [self.params[i] for i in idxs]
+                numel = sum((p.numel() + ALIGN_ELEMS - 1) // ALIGN_ELEMS * ALIGN_ELEMS for p in ps)
+                if bool(self.fused_cfg.get("bf16_shadow", True)) and self.backend.wants_nvls_fused(numel, ps[0].dtype):
+                    mode = "nvls_fused"
+            bk = Bucket(b, idxs, [self.params[i] for i in idxs], self.backend, mode)
             self.buckets.append(bk)
             for i in idxs:
                 bucket_of[i] = b
@@ -413,11 +452,13 @@ class Reducer:
         for bk in self.buckets:
             if bk.flat.dtype not in (torch.float32, torch.bfloat16):
                 raise RuntimeError("fused SGD supports fp32/bf16 gradient buckets")
-            master, msymm = self.backend.alloc_flat(bk.numel, torch.float32, dev, True)
+            via_switch = hasattr(bk.symm, "mc_ptr") and use_shadow  # the gradient bucket sits in a multicast buffer
+            amode = "nvls_fused" if via_switch else True
+            master, msymm = self.backend.alloc_flat(bk.numel, torch.float32, dev, amode)
             momentum = torch.zeros(bk.numel, dtype=torch.float32, device=dev)
             shadow = ssymm = None
             if use_shadow:
-                shadow, ssymm = self.backend.alloc_flat(bk.numel, torch.bfloat16, dev, True)
+                shadow, ssymm = self.backend.alloc_flat(bk.numel, torch.bfloat16, dev, amode)
             for p, off in zip(bk.params, bk.offsets):
                 if p.dtype != torch.float32:
                     raise RuntimeError("fused SGD expects fp32 master parameters (bf16 compute uses the shadow copy)")
@@ -429,6 +470,11 @@ class Reducer:
                     sv.copy_(mv)
                     p._dmp_shadow = sv
             bk.fused = FusedSGDState(master, momentum, shadow, self.hp, bool(cfg.get("nesterov", False)), msymm, ssymm)
+            if via_switch and hasattr(msymm, "mc_ptr") and hasattr(ssymm, "mc_ptr"):
+                bk.fused.nvls = (bk.symm.mc_ptr, msymm.mc_ptr, ssymm.mc_ptr)
+            elif via_switch:
+                raise RuntimeError("NVLS fused all-reduce: the master / shadow multicast buffers could not be created although the "
+                                   "gradient bucket's was")
 
     def sync_shadow(self):
         """Re-derive the bf16 shadows from the fp32 masters (after load_state_dict or manual edits)."""

@@ -230,6 +230,11 @@ int dmp_mc_xp_destroy(void* handle);
 /* In-place fp32 all-reduce through the NVSwitch: multimem.ld_reduce of the caller's 1/W slice, scale, multimem.st. */
 int dmp_allreduce_nvls(void* mc, void* const* state, int rank, int W, long long n, float scale, int max_blocks,
                        dmp_stream_t stream);
+/* All-reduce + SGD through the switch: multimem.ld_reduce of the owned slice, momentum update, multimem.st of fp32 master, bf16
+ * shadow and zeroed gradients into every copy.  (4 + 10)/W bytes per element on each GPU's link instead of 10 (W-1)/W. */
+int dmp_allreduce_nvls_sgd(void* mc_grad, void* mc_master, void* mc_shadow, const float* master, float* momentum, const float* hp_dev,
+                           int nesterov, void* const* state, int rank, int W, long long n, float scale, int max_blocks,
+                           dmp_stream_t stream);
 
 /* peer-memory plumbing */
 int dmp_symm_malloc(long long bytes, void** out);

@@ -315,6 +315,9 @@ def _w_ddp(rank, world, port, mode):
 
     torch.manual_seed(0)
     use_graph = mode == "graph"
+    if mode == "kernels_nvls":  # every bucket reduced and updated inside the switch (multimem.ld_reduce / multimem.st)
+        os.environ["DMP_DDP_NVLS_FUSED"] = "1"
+        os.environ["DMP_DDP_NVLS_FUSED_MIN_BYTES"] = "0"
     base = (MobileNetV2() if use_graph else _tiny_net()).cuda()
     sgd = dict(lr=0.05, momentum=0.9, weight_decay=1e-4)
     ctx = OF.use_reference_ops() if mode == "reference_ops" else contextlib.nullcontext()
@@ -346,11 +349,14 @@ def _w_ddp(rank, world, port, mode):
                 rel = (num / den).item()
     ours.check_health()
     if rank == 0:
-        print("ddp end-to-end [%s]: parameter distance / distance travelled = %.4f, losses %s" % (mode, rel, losses[-1]), flush=True)
+        print("ddp end-to-end [%s]: parameter distance / distance travelled = %.2e, losses %s, buckets %d, launches in the switch %s" % (
+            mode, rel, losses[-1], len(ours.reducer.buckets), getattr(ours.backend, "nvls_fused_launches", None)), flush=True)
     if mode == "reference_ops":   # fp32 library ops: only the summation order of the all-reduce differs
         assert rel < 1e-2, rel
-    elif mode == "kernels":       # bf16 kernels with fp32 atomics on both sides, small network
+    elif mode in ("kernels", "kernels_nvls"):  # bf16 kernels with fp32 atomics on both sides, small network
         assert rel < 0.12, rel
+        if mode == "kernels_nvls" and ours.backend.nvls_fused:  # (stays False where the platform has no multicast)
+            assert ours.backend.nvls_fused_launches > 0 and all(bk.fused.nvls is not None for bk in ours.reducer.buckets)
     else:
         # full MobileNetV2, captured step against the eager torch-DDP twin: one bf16 gradient of this network has a cosine of
         # ~0.96 with its fp32 value (tests/test_gpu_models.py), i.e. two bf16 evaluations differ by up to ~0.3 of their norm
@@ -365,7 +371,7 @@ def _w_ddp(rank, world, port, mode):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["reference_ops", "kernels", "graph"])
+@pytest.mark.parametrize("mode", ["reference_ops", "kernels", "kernels_nvls", "graph"])
 def test_ddp_peer_fused_end_to_end(mode):
     _spawn(_w_ddp, 2, mode)
 
