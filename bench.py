@@ -235,7 +235,18 @@ def measure_dataparallel(args, world, steps, warmup):
         for i in range(2):
             step(*host[i % 4]); step.read_stats()
         ms_e2e, _, _, _ = timed_steps(step, host, steps, 1, 0, read_stats=True, sample=False)
-    return {"value": gb / ms * 1e3, "ms_per_step": ms, "e2e_value": gb / ms_e2e * 1e3, "launches_per_step": step.launches_per_iteration}
+        res = {"value": gb / ms * 1e3, "ms_per_step": ms, "e2e_value": gb / ms_e2e * 1e3, "launches_per_step": step.launches_per_iteration,
+               "path": "thread per replica, persistent replicas" if getattr(dp, "_replica_set", None) is not None else "thread per replica"}
+        if world > 1 and not args.no_graph:
+            # the same DataParallel wrapper driven by one thread: every replica's forward + loss + backward is a CUDA graph
+            from distributed_model_parallel_b200.parallel.dp_engine import DataParallelStep
+            gstep = DataParallelStep(dp, opt)
+            for i in range(max(warmup, 3)):
+                gstep(*host[i % 4])
+            gms, _, _, _ = timed_steps(gstep, host, steps, 1, 0, read_stats=True, sample=False)
+            res["graph_per_replica_e2e_value"] = gb / gms * 1e3
+            res["graph_per_replica_ms_per_step"] = gms
+    return res
 
 
 def run_ours(args):
@@ -343,7 +354,7 @@ def run_ours(args):
                        "e2e": {"value": dpres.get("e2e_value"), "unit": "images/s",
                                "h2d_bytes_per_step": gb * (4 * 3 * input_shape(args.model)[1] * input_shape(args.model)[2] + 8),
                                "d2h_bytes_per_step": 12},
-                       "gpu_launches": int(dpres.get("launches_per_step", 0)) * args.steps, "error": dpres.get("error")}
+                       "gpu_launches": int(dpres.get("launches_per_step", 0)) * args.steps, "error": dpres.get("error"), "dp": dpres}
             else:
                 res["dp_value"] = dpres.get("value")
                 res["dp"] = dpres

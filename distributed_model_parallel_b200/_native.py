@@ -117,6 +117,8 @@ _KERNEL_SIGS = {
     "dmp_copy_peer": (C.c_int, [C.c_void_p, C.c_void_p, C.c_longlong, C.c_int, C.c_void_p]),
     "dmp_reduce_add_peer": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
+    "dmp_reduce_add_peer_z": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_longlong, C.c_float, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p]),
     "dmp_symm_malloc": (C.c_int, [C.c_longlong, C.POINTER(C.c_void_p)]),
     "dmp_symm_free": (C.c_int, [C.c_void_p]),
     "dmp_ipc_export": (C.c_int, [C.c_void_p, C.c_void_p]),

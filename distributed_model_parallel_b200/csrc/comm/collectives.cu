@@ -384,12 +384,15 @@ __global__ void __launch_bounds__(DMP_COMM_THREADS) copy16_kernel(const void* sr
 // ------------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(DMP_COMM_THREADS)
-reduce_add_peer_kernel(PeerPtrs src, int W, long long nvec, float scale, float* out_f32, SgdArgs sgd) {
+reduce_add_peer_kernel(PeerPtrs src, int W, long long nvec, float scale, float* out_f32, SgdArgs sgd, int zero_src) {
     constexpr int N = VecIO<T>::N;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long v = blockIdx.x * (long long)blockDim.x + threadIdx.x; v < nvec; v += stride) {
         float acc[N];
         reduce_vec<T>(src, W, v, acc);
+        if (zero_src) {  // the replicas' gradient arenas start the next iteration from zero (peer stores)
+            for (int r = 0; r < W; ++r) ((int4*)src.p[r])[v] = make_int4(0, 0, 0, 0);
+        }
 #pragma unroll
         for (int j = 0; j < N; ++j) acc[j] *= scale;
         if (sgd.master != nullptr) {
@@ -573,10 +576,19 @@ DMP_API int dmp_copy_peer(const void* src, void* dst, long long bytes, int max_b
     return 0;
 }
 
-// out = scale * sum_i src[i]  (fp32 out), or fused SGD on master/momentum/shadow when master != null.
+// out = scale * sum_i src[i]  (fp32 out), or fused SGD on master/momentum/shadow when master != null.  zero_src != 0 also zeroes
+// every source buffer after it has been read (persistent DataParallel replicas: their gradient arenas are accumulated into).
+DMP_API int dmp_reduce_add_peer_z(int dtype, void* const* src, int W, long long n, float scale, float* out_f32, float* master,
+                                  float* momentum, void* shadow, const float* hp_dev, int nesterov, int zero_src, int max_blocks,
+                                  cudaStream_t stream);
 DMP_API int dmp_reduce_add_peer(int dtype, void* const* src, int W, long long n, float scale, float* out_f32, float* master,
                                 float* momentum, void* shadow, const float* hp_dev, int nesterov, int max_blocks,
                                 cudaStream_t stream) {
+    return dmp_reduce_add_peer_z(dtype, src, W, n, scale, out_f32, master, momentum, shadow, hp_dev, nesterov, 0, max_blocks, stream);
+}
+DMP_API int dmp_reduce_add_peer_z(int dtype, void* const* src, int W, long long n, float scale, float* out_f32, float* master,
+                                  float* momentum, void* shadow, const float* hp_dev, int nesterov, int zero_src, int max_blocks,
+                                  cudaStream_t stream) {
     DMP_REQUIRE(W >= 1 && W <= DMP_MAX_RANKS, "dmp_reduce_add_peer: bad source count");
     DMP_REQUIRE(dtype == 0 || dtype == 1, "dmp_reduce_add_peer: dtype must be fp32 or bf16");
     const int esz = dtype == 0 ? 4 : 2;
@@ -587,8 +599,8 @@ DMP_API int dmp_reduce_add_peer(int dtype, void* const* src, int W, long long n,
     SgdArgs a;
     a.master = master; a.momentum = momentum; a.shadow = (bf16*)shadow; a.hp = hp_dev; a.nesterov = nesterov;
     const int grid = comm_grid(nvec, max_blocks);
-    if (dtype == 0) reduce_add_peer_kernel<float><<<grid, DMP_COMM_THREADS, 0, stream>>>(s, W, nvec, scale, out_f32, a);
-    else reduce_add_peer_kernel<bf16><<<grid, DMP_COMM_THREADS, 0, stream>>>(s, W, nvec, scale, out_f32, a);
+    if (dtype == 0) reduce_add_peer_kernel<float><<<grid, DMP_COMM_THREADS, 0, stream>>>(s, W, nvec, scale, out_f32, a, zero_src);
+    else reduce_add_peer_kernel<bf16><<<grid, DMP_COMM_THREADS, 0, stream>>>(s, W, nvec, scale, out_f32, a, zero_src);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;

@@ -148,6 +148,8 @@ class _SideStreams:
 
 
 _tls_side = threading.local()
+_all_side = []          # every manager ever created (one per thread that ran a backward with side-stream work)
+_all_side_lock = threading.Lock()
 
 
 def side_streams() -> _SideStreams:
@@ -155,7 +157,16 @@ def side_streams() -> _SideStreams:
     m = getattr(_tls_side, "m", None)
     if m is None:
         m = _tls_side.m = _SideStreams()
+        with _all_side_lock:
+            _all_side.append(m)
     return m
+
+
+def all_side_stream_managers():
+    """Every thread's side-stream manager: a caller that consumes gradients written by several autograd threads (DataParallel's
+    gradient reduction) joins them all first."""
+    with _all_side_lock:
+        return list(_all_side)
 
 
 def _deliver_grad(param: Optional[torch.Tensor], writer, side_inputs=()):

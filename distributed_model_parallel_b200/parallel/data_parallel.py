@@ -61,6 +61,7 @@ class DataParallel(nn.Module):
             self.module.to(self.devices[0])
         self._mc_arena = None
         self._mc_tried = False
+        self._replica_set = None
 
     def forward(self, *inputs: Any, **kwargs: Any) -> Any:
         with torch.autograd.profiler.record_function("DataParallel.forward"):
@@ -76,12 +77,34 @@ class DataParallel(nn.Module):
                 inputs, module_kwargs = ((),), ({},)
             if len(self.devices) == 1:
                 return self.module(*inputs[0], **module_kwargs[0])
+            rs = self._replica_set
+            if rs is not None and len(inputs) == len(self.devices):
+                # persistent replicas: parameters and buffers travel as two flat kernels, nothing is cloned or concatenated
+                with nvtx_range("dp.broadcast"):
+                    rs.broadcast()
+                with nvtx_range("dp.parallel_apply"):
+                    outputs = self.parallel_apply(rs.replicas, inputs, module_kwargs)
+                with nvtx_range("dp.gather"):
+                    out = self.gather(outputs, self.output_device)
+                if torch.is_grad_enabled():
+                    out = _map_tensors(out, lambda t: _ReduceAfterBackward.apply(t, rs) if t.requires_grad else t)
+                return out
             with nvtx_range("dp.replicate"):
                 replicas = self.replicate(self.module, self.devices[: len(inputs)])
             with nvtx_range("dp.parallel_apply"):
                 outputs = self.parallel_apply(replicas, inputs, module_kwargs)
             with nvtx_range("dp.gather"):
                 return self.gather(outputs, self.output_device)
+
+    def attach_optimizer(self, optimizer):
+        """Switches this wrapper to persistent replicas laid out like ``optimizer``'s flat arenas (``FlatFusedSGD``): the
+        per-forward replicate() / per-backward tensor-wise reduction become one broadcast kernel and one reduction kernel
+        (see ``parallel/dp_engine.py``).  Returns the ``ReplicaSet``.  Call again after re-creating the optimizer."""
+        from .dp_engine import ReplicaSet
+        if len(self.devices) < 2 or not all(d.type == "cuda" for d in self.devices):
+            return None
+        self._replica_set = ReplicaSet(self.module, self.devices, optimizer)
+        return self._replica_set
 
     def _multicast_arena(self):
         """NVLS multicast arena for the per-forward parameter/buffer broadcast (created once; None if unsupported or
@@ -115,6 +138,41 @@ class DataParallel(nn.Module):
 
     def gather(self, outputs, output_device):
         return gather(outputs, output_device, dim=self.dim)
+
+
+class _ReduceAfterBackward(torch.autograd.Function):
+    """Identity on the gathered output whose backward queues, once per backward pass, the reduction of the persistent
+    replicas' gradient arenas onto device 0 (it runs when the whole backward has been issued on every device)."""
+
+    @staticmethod
+    def forward(ctx, t, rs):
+        ctx.rs = rs
+        return t.view_as(t)
+
+    @staticmethod
+    def backward(ctx, g):
+        rs = ctx.rs
+        if not getattr(rs, "_reduce_queued", False):
+            rs._reduce_queued = True
+
+            def _cb():
+                rs._reduce_queued = False
+                rs.reduce_grads(fused_sgd=False)
+
+            torch.autograd.Variable._execution_engine.queue_callback(_cb)
+        return g, None
+
+
+def _map_tensors(obj, fn):
+    if isinstance(obj, torch.Tensor):
+        return fn(obj)
+    if isinstance(obj, tuple) and hasattr(obj, "_fields"):
+        return type(obj)(*(_map_tensors(o, fn) for o in obj))
+    if isinstance(obj, (list, tuple)):
+        return type(obj)(_map_tensors(o, fn) for o in obj)
+    if isinstance(obj, dict):
+        return type(obj)((k, _map_tensors(v, fn)) for k, v in obj.items())
+    return obj
 
 
 def data_parallel(module: nn.Module, inputs: Any, device_ids: Optional[Sequence] = None, output_device=None, dim: int = 0,

@@ -26,6 +26,12 @@ class TrainStep:
         self.optimizer = optimizer if optimizer is not None else getattr(model, "optimizer", None)
         if self.optimizer is None:
             raise ValueError("TrainStep needs an optimizer (or a DDP built with fused_sgd)")
+        # DataParallel over several GPUs: persistent replicas laid out like the optimizer's arenas (one broadcast / one reduce kernel)
+        if hasattr(model, "attach_optimizer") and getattr(model, "_replica_set", None) is None and hasattr(self.optimizer, "master"):
+            try:
+                model.attach_optimizer(self.optimizer)
+            except (TypeError, ValueError):
+                pass
         self.use_graph = use_graph and torch.cuda.is_available()
         self.warmup_iters = warmup_iters
         self.loss_fn = loss_fn

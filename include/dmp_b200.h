@@ -211,6 +211,9 @@ int dmp_copy_peer(const void* src, void* dst, long long bytes, int max_blocks, d
 int dmp_reduce_add_peer(int dtype, void* const* src, int W, long long n, float scale, float* out_f32, float* master,
                         float* momentum, void* shadow, const float* hp_dev, int nesterov, int max_blocks,
                         dmp_stream_t stream);
+/* Same, optionally zeroing every source after it was read (persistent DataParallel replicas accumulate into their arenas). */
+int dmp_reduce_add_peer_z(int dtype, void* const* src, int W, long long n, float scale, float* out_f32, float* master, float* momentum,
+                          void* shadow, const float* hp_dev, int nesterov, int zero_src, int max_blocks, dmp_stream_t stream);
 int dmp_comm_status(void* state_local, dmp_stream_t stream); /* 0 healthy, 1+peer: barrier with that peer timed out */
 
 /* NVLS multicast objects for one process driving several GPUs (csrc/comm/multicast.cu): per-device allocations bound to one

@@ -556,3 +556,55 @@ def test_multicast_broadcast_matches_source():
             for a, b in zip(ts, outs[k]):
                 assert b.device.index == k and torch.equal(a.cpu(), b.cpu())
         ts = [t + 1 for t in ts]
+
+
+# ------------------------------------------------------------------------------------------------ DataParallel with persistent replicas
+def test_dataparallel_persistent_replicas_and_graph_step():
+    """Three training steps of the same network three ways -- torch-shaped replicate() per forward, persistent replicas (one
+    broadcast kernel, one reduce kernel), and the one-thread graph-per-replica step -- must agree: same semantics (every replica
+    normalises its own chunk, gradients are summed onto device 0), same kernels."""
+    import copy
+    from distributed_model_parallel_b200.ops import functional as OF
+    from distributed_model_parallel_b200.optim import FlatFusedSGD
+    from distributed_model_parallel_b200.parallel import DataParallel
+    from distributed_model_parallel_b200.parallel.dp_engine import DataParallelStep
+
+    torch.manual_seed(0)
+    base = _tiny_net().cuda(0)
+    hp = dict(lr=0.05, momentum=0.9, weight_decay=1e-4)
+    g = torch.Generator().manual_seed(3)
+    batches = [(torch.randn(64, 3, 16, 16, generator=g).cuda(0), torch.randint(0, 10, (64,), generator=g).cuda(0)) for _ in range(3)]
+
+    def run(kind):
+        net = copy.deepcopy(base)
+        dp = DataParallel(net, device_ids=[0, 1])
+        opt = FlatFusedSGD(net.parameters(), **hp)
+        losses = []
+        if kind == "graph":
+            st = DataParallelStep(dp, opt)
+            for x, y in batches:
+                st(x, y)
+                losses.append(st.read_stats()[0])
+        else:
+            if kind == "persistent":
+                assert dp.attach_optimizer(opt) is not None
+            for x, y in batches:
+                loss = OF.cross_entropy(dp(x), y)
+                loss.backward()
+                opt.step()
+                losses.append(float(loss))
+            if kind == "persistent":
+                assert dp._replica_set.kernel_launches >= 3 * 3
+        torch.cuda.synchronize()
+        return losses, [p.detach().float().clone() for p in net.parameters()], [b.detach().float().clone() for b in net.buffers()]
+
+    l0, p0, b0 = run("replicate")
+    for kind in ("persistent", "graph"):
+        l1, p1, b1 = run(kind)
+        for a, b in zip(l0, l1):
+            assert abs(a - b) < 0.02 * max(1.0, abs(a)), (kind, l0, l1)
+        num = sum(((p - q) ** 2).sum() for p, q in zip(p0, p1)).sqrt().item()
+        den = sum((p ** 2).sum() for p in p0).sqrt().item()
+        assert num / den < 5e-3, (kind, num / den)
+        for a, b in zip(b0, b1):
+            assert torch.allclose(a, b, rtol=2e-2, atol=2e-2), kind
