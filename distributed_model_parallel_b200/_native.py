@@ -31,6 +31,8 @@ _KERNEL_SIGS = {
     "dmp_version": (i32, []),
     "dmp_device_cc": (i32, []),
     "dmp_l2_flush": (i32, [vp, i64, vp]),
+    "dmp_stream_fork": (i32, [vp, vp, vp, i32]),
+    "dmp_stream_join": (i32, [vp, vp]),
     # gemm
     "dmp_gemm_bf16": (i32, [i32, vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i32, i32, vp]),
     "dmp_gemm_ref_f32out": (i32, [i32, vp, i64, vp, i64, vp, i64, i32, i32, i32, vp, i32, vp]),

@@ -63,6 +63,53 @@ __global__ void stem_fwd_kernel(const void* __restrict__ x, int layout, const WT
     store8(y + (((long long)n * Ho + ho) * Wo + wo) * Cout + cg * 8, acc);
 }
 
+// 3x3 stems with a compile-time tap count: every tap is fetched unconditionally from a clamped address and zeroed by its
+// bounds predicate, so the T loads of a pixel are independent and in flight together.  (With the loads under their bounds
+// branches -- the generic kernel above -- each one waits for the previous: 27 serial L2 round trips per pixel.)
+template <int CIN, int KS, typename WT>
+__global__ void __launch_bounds__(256)
+stem_fwd_unrolled_kernel(const void* __restrict__ x, int layout, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H,
+                         int W, int Cout, int stride, int pad, int Ho, int Wo) {
+    extern __shared__ float sw[];  // [T][Cout]
+    constexpr int T = CIN * KS * KS;
+    for (int i = threadIdx.x; i < T * Cout; i += blockDim.x) {
+        const int co = i / T, tap = i % T;
+        sw[tap * Cout + co] = to_f32<WT>(w[i]);
+    }
+    __syncthreads();
+    const int G = Cout >> 3;
+    const long long idx = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    const long long total = (long long)N * Ho * Wo * G;
+    if (idx >= total) return;
+    const int cg = (int)(idx % G);
+    long long pix = idx / G;
+    const int wo = (int)(pix % Wo); pix /= Wo;
+    const int ho = (int)(pix % Ho);
+    const int n = (int)(pix / Ho);
+    float xv[T];
+#pragma unroll
+    for (int ci = 0; ci < CIN; ++ci)
+#pragma unroll
+        for (int kh = 0; kh < KS; ++kh)
+#pragma unroll
+            for (int kw = 0; kw < KS; ++kw) {
+                const int hi = ho * stride + kh - pad, wi = wo * stride + kw - pad;
+                const bool ok = (unsigned)hi < (unsigned)H && (unsigned)wi < (unsigned)W;
+                const float v = stem_x(x, layout, n, ci, min(max(hi, 0), H - 1), min(max(wi, 0), W - 1), CIN, H, W);
+                xv[(ci * KS + kh) * KS + kw] = ok ? v : 0.f;
+            }
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int t = 0; t < T; ++t) {
+        const float4 w0 = *(const float4*)(sw + t * Cout + cg * 8), w1 = *(const float4*)(sw + t * Cout + cg * 8 + 4);
+        acc[0] += xv[t] * w0.x; acc[1] += xv[t] * w0.y; acc[2] += xv[t] * w0.z; acc[3] += xv[t] * w0.w;
+        acc[4] += xv[t] * w1.x; acc[5] += xv[t] * w1.y; acc[6] += xv[t] * w1.z; acc[7] += xv[t] * w1.w;
+    }
+    store8(y + (((long long)n * Ho + ho) * Wo + wo) * Cout + cg * 8, acc);
+}
+
 // dw[co,tap] += sum_pix dy[pix,co] * x[pix (+) tap];  thread = (tap, 8 couts), block strides over pixels
 __global__ void stem_wgrad_kernel(const bf16* __restrict__ dy, const void* __restrict__ x, int layout,
                                   float* __restrict__ dw, int N, int Cin, int H, int W, int Cout, int KH, int KW,
@@ -111,56 +158,64 @@ __global__ void stem_wgrad_kernel(const bf16* __restrict__ dy, const void* __res
 }
 
 
-// 3x3 stems (27 or fewer taps): lane = pixel, warp = group of 4 output channels.  A thread keeps the whole [tap][4 couts]
-// slab of the weight gradient in registers (<= 108 accumulators) and walks pixels with a grid stride, so every load is
-// coalesced along the pixel axis (x) or shared by the block's warps through L1 (dy), and each loaded value feeds 4 (x) or
-// up to 27 (dy) FMAs.  The per-(tap, 8 couts) mapping above spends two loads on eight FMAs and took 180 us on the
-// MobileNetV2 stem; this one is bound by the 8 MB read of dy.
-template <int CIN, int KS>
+// 3x3 stems (27 or fewer taps): lane = pixel, warp = group of NCO output channels.  A thread keeps the whole [tap][NCO couts]
+// slab of the weight gradient in registers and walks pixels with a grid stride, so every load is coalesced along the pixel axis
+// (x) or shared by the block's warps through L1 (dy), and each loaded value feeds NCO (x) or up to 27 (dy) FMAs.
+// The taps of a pixel are fetched unconditionally from clamped addresses and zeroed by their bounds predicates: under their
+// bounds branches the 27 loads ran one after the other (186 us for the MobileNetV2 stem at batch 128 inside the step).
+template <int CIN, int KS, int NCO>
 __global__ void __launch_bounds__(256)
 stem_wgrad_reg_kernel(const bf16* __restrict__ dy, const void* __restrict__ x, int layout, float* __restrict__ dw, int N,
                       int H, int W, int Cout, int stride, int pad, int Ho, int Wo) {
     constexpr int T = CIN * KS * KS;
-    const int lane = threadIdx.x & 31, cog = blockIdx.y * 8 + (threadIdx.x >> 5);  // 8 warps = 32 couts per blockIdx.y
+    static_assert(NCO == 2 || NCO == 4, "NCO");
+    const int lane = threadIdx.x & 31, cog = blockIdx.y * 8 + (threadIdx.x >> 5);  // 8 warps = 8*NCO couts per blockIdx.y
     const long long npix = (long long)N * Ho * Wo;
-    float acc[T][4];
+    float acc[T][NCO];
 #pragma unroll
     for (int t = 0; t < T; ++t)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) acc[t][j] = 0.f;
+        for (int j = 0; j < NCO; ++j) acc[t][j] = 0.f;
     for (long long pix = (long long)blockIdx.x * 32 + lane; pix < npix; pix += (long long)gridDim.x * 32) {
-        long long r = pix;
-        const int wo = (int)(r % Wo); r /= Wo;
-        const int ho = (int)(r % Ho);
-        const int n = (int)(r / Ho);
-        const uint2 graw = *(const uint2*)(dy + pix * Cout + cog * 4);
-        float g[4];
-        g[0] = __uint_as_float(graw.x << 16); g[1] = __uint_as_float(graw.x & 0xffff0000u);
-        g[2] = __uint_as_float(graw.y << 16); g[3] = __uint_as_float(graw.y & 0xffff0000u);
+        const unsigned up = (unsigned)pix;  // npix < 2^31 is checked by the host
+        const int wo = (int)(up % (unsigned)Wo);
+        const unsigned r = up / (unsigned)Wo;
+        const int ho = (int)(r % (unsigned)Ho);
+        const int n = (int)(r / (unsigned)Ho);
+        float g[NCO];
+        if (NCO == 4) {
+            const uint2 graw = *(const uint2*)(dy + pix * Cout + cog * 4);
+            g[0] = __uint_as_float(graw.x << 16); g[1] = __uint_as_float(graw.x & 0xffff0000u);
+            g[2] = __uint_as_float(graw.y << 16); g[NCO - 1] = __uint_as_float(graw.y & 0xffff0000u);
+        } else {
+            const unsigned graw = *(const unsigned*)(dy + pix * Cout + cog * 2);
+            g[0] = __uint_as_float(graw << 16); g[1] = __uint_as_float(graw & 0xffff0000u);
+        }
+        float xv[T];
 #pragma unroll
         for (int ci = 0; ci < CIN; ++ci)
 #pragma unroll
-            for (int kh = 0; kh < KS; ++kh) {
-                const int hi = ho * stride + kh - pad;
+            for (int kh = 0; kh < KS; ++kh)
 #pragma unroll
                 for (int kw = 0; kw < KS; ++kw) {
-                    const int wi = wo * stride + kw - pad;
-                    float xv = 0.f;
-                    if (hi >= 0 && hi < H && wi >= 0 && wi < W) xv = stem_x(x, layout, n, ci, hi, wi, CIN, H, W);
-                    const int t = (ci * KS + kh) * KS + kw;
-#pragma unroll
-                    for (int j = 0; j < 4; ++j) acc[t][j] += g[j] * xv;
+                    const int hi = ho * stride + kh - pad, wi = wo * stride + kw - pad;
+                    const bool ok = (unsigned)hi < (unsigned)H && (unsigned)wi < (unsigned)W;
+                    const float v = stem_x(x, layout, n, ci, min(max(hi, 0), H - 1), min(max(wi, 0), W - 1), CIN, H, W);
+                    xv[(ci * KS + kh) * KS + kw] = ok ? v : 0.f;
                 }
-            }
+#pragma unroll
+        for (int t = 0; t < T; ++t)
+#pragma unroll
+            for (int j = 0; j < NCO; ++j) acc[t][j] += g[j] * xv[t];
     }
 #pragma unroll
     for (int t = 0; t < T; ++t)
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
+        for (int j = 0; j < NCO; ++j) {
             float v = acc[t][j];
 #pragma unroll
             for (int o = 16; o >= 1; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0) atomicAdd(&dw[(long long)(cog * 4 + j) * T + t], v);
+            if (lane == 0) atomicAdd(&dw[(long long)(cog * NCO + j) * T + t], v);
         }
 }
 
@@ -293,6 +348,17 @@ DMP_API int dmp_stem_conv_fwd(const void* x, int x_layout, const void* w, int w_
     DMP_REQUIRE(smem <= 48 * 1024, "dmp_stem_conv_fwd: filter too large for shared memory (%zu bytes)", smem);
     const long long total = (long long)N * Ho * Wo * (Cout / 8);
     const int grid = dmp_ceil_div(total, 256);
+    if (KH == 3 && KW == 3 && Cin == 3) {
+        if (w_dtype == 0)
+            stem_fwd_unrolled_kernel<3, 3, float><<<grid, 256, smem, stream>>>(x, x_layout, (const float*)w, (bf16*)y, N, H, W, Cout,
+                                                                              stride, pad, Ho, Wo);
+        else
+            stem_fwd_unrolled_kernel<3, 3, bf16><<<grid, 256, smem, stream>>>(x, x_layout, (const bf16*)w, (bf16*)y, N, H, W, Cout,
+                                                                             stride, pad, Ho, Wo);
+        DMP_LAUNCH_CHECK();
+        DMP_COUNT_LAUNCH(1);
+        return 0;
+    }
     if (w_dtype == 0)
         stem_fwd_kernel<float><<<grid, 256, smem, stream>>>(x, x_layout, (const float*)w, (bf16*)y, N, Cin, H, W, Cout, KH, KW,
                                                             stride, pad, Ho, Wo);
@@ -311,17 +377,20 @@ DMP_API int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, flo
     const int threads = T * (Cout / 8);
     const int Ho = (H + 2 * pad - KH) / stride + 1, Wo = (W + 2 * pad - KW) / stride + 1;
     if (!accumulate) DMP_CHECK_CUDA(cudaMemsetAsync(dw, 0, sizeof(float) * (size_t)T * Cout, stream));
-    if (KH == 3 && KW == 3 && (Cin == 3 || Cin == 1) && Cout % 32 == 0) {
+    if (KH == 3 && KW == 3 && (Cin == 3 || Cin == 1) && Cout % 16 == 0 && (long long)N * Ho * Wo < (1ll << 31)) {
+        // 2 couts per warp: 54 accumulators, two 256-thread blocks per SM; one block column per 16 couts, a whole number of
+        // waves of (blocks per SM) x SMs
         const long long npix = (long long)N * Ho * Wo;
-        long long gx = (npix + 32 * 8 - 1) / (32 * 8);  // >= 8 pixels per lane, else the final reduction dominates
-        const long long cap = (long long)dmp_num_sms() * 2 / (Cout / 32) + 1;
+        const int ny = Cout / 16;
+        long long gx = (npix + 32 * 4 - 1) / (32 * 4);  // >= 4 pixels per lane, else the final reduction dominates
+        const long long cap = (long long)dmp_num_sms() * 2 / ny;
         if (gx > cap) gx = cap;
         if (gx < 1) gx = 1;
-        const dim3 grid((unsigned)gx, (unsigned)(Cout / 32));
+        const dim3 grid((unsigned)gx, (unsigned)ny);
         if (Cin == 3)
-            stem_wgrad_reg_kernel<3, 3><<<grid, 256, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, H, W, Cout, stride, pad, Ho, Wo);
+            stem_wgrad_reg_kernel<3, 3, 2><<<grid, 256, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, H, W, Cout, stride, pad, Ho, Wo);
         else
-            stem_wgrad_reg_kernel<1, 3><<<grid, 256, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, H, W, Cout, stride, pad, Ho, Wo);
+            stem_wgrad_reg_kernel<1, 3, 2><<<grid, 256, 0, stream>>>((const bf16*)dy, x, x_layout, dw, N, H, W, Cout, stride, pad, Ho, Wo);
         DMP_LAUNCH_CHECK();
         DMP_COUNT_LAUNCH(1);
         return 0;

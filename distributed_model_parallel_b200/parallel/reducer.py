@@ -42,7 +42,43 @@ _native.register_runtime_sigs({
     "dmp_reducer_iterations": (C.c_longlong, [C.c_void_p]),
     "dmp_reducer_ready_order": (C.c_int, [C.c_void_p, C.POINTER(C.c_int32), C.c_int]),
     "dmp_reducer_unused_flags": (None, [C.c_void_p, C.POINTER(C.c_int32)]),
+    "dmp_reducer_set_plans": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int]),
+    "dmp_reducer_clear_plans": (None, [C.c_void_p]),
+    "dmp_reducer_grad_ready": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int32), C.c_int]),
+    "dmp_reducer_finish": (C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.c_int]),
+    "dmp_reducer_native_launches": (C.c_longlong, [C.c_void_p]),
+    "dmp_reducer_plan_bytes": (C.c_int, []),
+    "dmp_reducer_fns_bytes": (C.c_int, []),
 })
+
+PLAN_CALLER, PLAN_ALLREDUCE_FUSED, PLAN_NVLS, PLAN_NVLS_SGD, PLAN_SGD_FLAT, PLAN_NONE = range(6)
+
+
+class BucketPlan(C.Structure):
+    """Mirror of ``struct DmpBucketPlan`` (csrc/runtime/reducer.cpp): how the native hook launches one bucket."""
+    _fields_ = [("kind", C.c_int), ("algo", C.c_int), ("dtype", C.c_int), ("rank", C.c_int), ("world", C.c_int),
+                ("nesterov", C.c_int), ("zero_after", C.c_int), ("max_blocks", C.c_int), ("numel", C.c_longlong),
+                ("scale", C.c_float),
+                ("bufs", C.c_void_p), ("state", C.c_void_p), ("out", C.c_void_p), ("master", C.c_void_p),
+                ("momentum", C.c_void_p), ("shadow", C.c_void_p), ("hp", C.c_void_p), ("master_ptrs", C.c_void_p),
+                ("shadow_ptrs", C.c_void_p), ("mc_grad", C.c_void_p), ("mc_master", C.c_void_p), ("mc_shadow", C.c_void_p),
+                ("grad", C.c_void_p)]
+
+
+class LaunchFns(C.Structure):
+    """Mirror of ``struct DmpLaunchFns``: entry points of the kernel library (or test stubs) the native hook calls."""
+    _fields_ = [(n, C.c_void_p) for n in ("fork", "join", "allreduce_fused", "allreduce_nvls", "allreduce_nvls_sgd", "sgd_flat")]
+
+
+def kernel_launch_fns() -> LaunchFns:
+    """The real entry points, taken from libdmp_b200.so."""
+    lib = _native.kernels()
+    f = LaunchFns()
+    for field, sym in (("fork", "dmp_stream_fork"), ("join", "dmp_stream_join"), ("allreduce_fused", "dmp_allreduce_fused"),
+                       ("allreduce_nvls", "dmp_allreduce_nvls"), ("allreduce_nvls_sgd", "dmp_allreduce_nvls_sgd"),
+                       ("sgd_flat", "dmp_sgd_flat")):
+        setattr(f, field, C.cast(getattr(lib, sym), C.c_void_p).value)
+    return f
 
 DEFAULT_FIRST_BUCKET_BYTES = 1024 * 1024
 DEFAULT_BUCKET_CAP_MB = 25
@@ -68,8 +104,12 @@ def compute_bucket_assignment_by_size(sizes_bytes: Sequence[int], limits: Sequen
     return buckets
 
 
+_EMPTY: List[int] = []
+
+
 class NativeReducerState:
     """Thin RAII wrapper over the C++ reducer state machine."""
+    native_launch = False
 
     def __init__(self, bucket_of_param: Sequence[int], n_buckets: int):
         self.rt = _native.runtime()
@@ -106,6 +146,49 @@ class NativeReducerState:
 
     def num_launched(self) -> int:
         return self.rt.dmp_reducer_num_launched(self.h)
+
+    # ---- native launch path: the whole hook (mark -> launch decision -> stream fork -> collective) is one C++ call
+    def set_plans(self, fns: LaunchFns, plans: Sequence[BucketPlan], comm_stream: int, side_streams: Sequence[int]) -> bool:
+        """Installs one launch plan per bucket.  Returns True when every bucket launches natively."""
+        assert self.rt.dmp_reducer_plan_bytes() == C.sizeof(BucketPlan) and self.rt.dmp_reducer_fns_bytes() == C.sizeof(LaunchFns)
+        arr = (BucketPlan * len(plans))(*plans)
+        side = (C.c_void_p * max(1, len(side_streams)))(*[C.c_void_p(s) for s in side_streams])
+        self._keep = (fns, arr, side)
+        rc = self.rt.dmp_reducer_set_plans(self.h, C.addressof(fns), C.addressof(arr), len(plans), C.c_void_p(comm_stream),
+                                           C.addressof(side), len(side_streams))
+        if rc < 0:
+            raise RuntimeError("dmp_reducer_set_plans failed with code %d" % rc)
+        self.native_launch = rc == 1
+        return self.native_launch
+
+    def clear_plans(self):
+        self.rt.dmp_reducer_clear_plans(self.h)
+        self.native_launch = False
+
+    def grad_ready(self, p: int, unused: bool, cur_stream: int) -> List[int]:
+        """The autograd hook's one native call.  Returns the buckets the CALLER must launch (empty on the native path)."""
+        k = self.rt.dmp_reducer_grad_ready(self.h, p, 1 if unused else 0, C.c_void_p(cur_stream), self._out, self.nb)
+        if k == 0:
+            return _EMPTY
+        if k < 0:
+            if k == -1:
+                raise RuntimeError(
+                    "parameter %d was marked ready twice in one iteration (a parameter shared by several layers, or "
+                    "several forward passes before one backward, is not supported without static_graph)" % p)
+            if k <= -100:
+                _native.check(-100 - k, "bucket collective (native reducer path)")
+            raise RuntimeError("reducer grad_ready failed with code %d" % k)
+        return [self._out[i] for i in range(k)]
+
+    def finish(self, cur_stream: int) -> List[int]:
+        miss = (C.c_int32 * self.n)()
+        m = self.rt.dmp_reducer_finish(self.h, C.c_void_p(cur_stream), miss, self.n)
+        if m <= -100:
+            _native.check(-100 - m, "communication stream join (native reducer path)")
+        return [miss[i] for i in range(min(m, self.n))]
+
+    def native_launches(self) -> int:
+        return int(self.rt.dmp_reducer_native_launches(self.h))
 
     def __del__(self):
         try:
@@ -294,6 +377,56 @@ class PeerBackend:
                                                   self.max_blocks, sp), "allreduce+sgd")
         self.kernel_launches += 1
 
+    def native_plan(self, bucket: "Bucket") -> Optional[BucketPlan]:
+        """What ``launch`` would do for this bucket, as data: the C++ reducer then launches it without coming back here."""
+        def addr(x):
+            return None if x is None else (x if isinstance(x, int) else C.cast(x, C.c_void_p).value)
+
+        fused, W, flat = bucket.fused, self.world_size, bucket.flat
+        pl = BucketPlan()
+        pl.dtype, pl.rank, pl.world, pl.numel = self.DTYPE_CODE[flat.dtype], self.rank, W, flat.numel()
+        pl.scale, pl.max_blocks = 1.0 / W, self.max_blocks
+        pl.nesterov = 1 if (fused is not None and fused.nesterov) else 0
+        if fused is not None:
+            pl.master, pl.momentum, pl.hp = fused.master.data_ptr(), fused.momentum.data_ptr(), fused.hp.data_ptr()
+            pl.shadow = _native.ptr(fused.shadow) or None
+        if W == 1:
+            pl.kind = PLAN_SGD_FLAT if fused is not None else PLAN_NONE
+            pl.grad = flat.data_ptr()
+            return pl
+        pl.state = addr(self.state.ptrs)
+        if fused is not None and fused.nvls is not None:
+            pl.kind = PLAN_NVLS_SGD
+            pl.mc_grad, pl.mc_master, pl.mc_shadow = fused.nvls
+            return pl
+        if fused is None and hasattr(bucket.symm, "mc_ptr"):
+            pl.kind, pl.mc_grad = PLAN_NVLS, bucket.symm.mc_ptr
+            return pl
+        pl.kind = PLAN_ALLREDUCE_FUSED
+        pl.algo = 0 if flat.numel() * flat.element_size() <= self.oneshot_max_bytes else 1
+        pl.bufs = addr(bucket.symm.ptrs)
+        if fused is None:
+            if pl.algo == 0:
+                if bucket.scratch is None:
+                    bucket.scratch = torch.empty_like(flat)
+                pl.out = bucket.scratch.data_ptr()
+            pl.zero_after = 0
+        else:
+            pl.master_ptrs = addr(fused.master_symm.ptrs) if fused.master_symm is not None else None
+            pl.shadow_ptrs = addr(fused.shadow_symm.ptrs) if fused.shadow_symm is not None else None
+            pl.zero_after = 1
+        return pl
+
+    def account_native(self, plans: Sequence[BucketPlan]):
+        """Launch counters for one iteration the C++ reducer launched (every bucket exactly once)."""
+        for pl in plans:
+            if pl.kind != PLAN_NONE:
+                self.kernel_launches += 1
+            if pl.kind == PLAN_NVLS_SGD:
+                self.nvls_fused_launches += 1
+            elif pl.kind == PLAN_NVLS:
+                self.nvls_launches += 1
+
     def wait(self, bucket: "Bucket"):
         pass  # stream-ordered; joined once in end_iteration
 
@@ -383,8 +516,11 @@ class Reducer:
         self.fused_cfg = fused_sgd
         self.static_graph = static_graph
         self.require_sync = True
-        self.comm_hook: Optional[Callable] = None
+        self._comm_hook: Optional[Callable] = None
         self.comm_hook_state = None
+        self._plans: List[BucketPlan] = []
+        self._plans_dirty = True
+        self._side_seen = None
         self._hooks_installed = False
         self._in_backward = False
         self._callback_queued = False
@@ -397,6 +533,34 @@ class Reducer:
         order = list(range(len(params)))
         self._build_buckets(self._assign(order, reverse=True))
         self._install_hooks()
+
+    @property
+    def comm_hook(self):
+        return self._comm_hook
+
+    @comm_hook.setter
+    def comm_hook(self, hook):
+        self._comm_hook = hook
+        self._plans_dirty = True  # a communication hook takes the launches back to Python
+
+    def _install_plans(self, side=None):
+        """Hands the C++ reducer one launch plan per bucket (DMP_NATIVE_REDUCER=0 keeps every launch in Python).  Buckets a
+        communication hook or a torch.distributed back end reduces cannot be launched natively: the hook then returns their
+        ids instead."""
+        self._plans_dirty = False
+        self._plans = []
+        native_ok = (os.environ.get("DMP_NATIVE_REDUCER", "1") != "0" and self._comm_hook is None
+                     and hasattr(self.backend, "native_plan"))
+        if not native_ok:
+            self.native.clear_plans()
+            return
+        plans = [self.backend.native_plan(bk) for bk in self.buckets]
+        if any(pl is None for pl in plans):
+            self.native.clear_plans()
+            return
+        side = side or []
+        self._plans = plans
+        self.native.set_plans(kernel_launch_fns(), plans, self.backend.stream.cuda_stream, [s.cuda_stream for s in side])
 
     # -------------------------------------------------------------------------------- bucket layout
     def _assign(self, order: List[int], reverse: bool) -> List[List[int]]:
@@ -433,6 +597,7 @@ class Reducer:
             for k, i in enumerate(bk.param_indices):
                 self.slot_of[i] = (bk, k)
         self.native = NativeReducerState(bucket_of, len(self.buckets))
+        self._plans_dirty = True
         if self.fused_cfg is not None:
             self._attach_fused()
         if self.grad_as_view:
@@ -511,6 +676,8 @@ class Reducer:
 
     def prepare_for_backward(self, unused_indices: Sequence[int] = ()):
         """Called at the end of forward (when gradients will be synchronised by the coming backward)."""
+        if self._plans_dirty:
+            self._install_plans()
         self.native.prepare()
         self.backend.begin_iteration()
         self._in_backward = True
@@ -559,7 +726,18 @@ class Reducer:
             bk, k = self.slot_of[i]
             if bk.fused is None:
                 bk.views[k].zero_()
-        for b in self.native.mark_ready(i, unused):
+        if self.native.native_launch:
+            dev = self.backend.device
+            # weight gradients may still be in flight on this thread's side streams: the C++ side orders the communication
+            # stream after them (the list changes once, when the autograd thread creates its streams)
+            side = OF.side_streams().streams.get(dev.index)
+            if side is not self._side_seen:
+                self._side_seen = side
+                self.native.set_plans(kernel_launch_fns(), self._plans, self.backend.stream.cuda_stream,
+                                      [s.cuda_stream for s in (side or [])])
+            self.native.grad_ready(i, unused, torch.cuda.current_stream(dev).cuda_stream)  # launches what became launchable
+            return
+        for b in self.native.grad_ready(i, unused, 0):
             self._launch(self.buckets[b])
 
     def _launch(self, bk: Bucket):
@@ -574,7 +752,13 @@ class Reducer:
         if not self._in_backward:
             return
         self._in_backward = False
-        missing = self.native.finalize()
+        if self.native.native_launch:
+            missing = self.native.finish(torch.cuda.current_stream(self.backend.device).cuda_stream)
+            if not missing:
+                self.backend.account_native(self._plans)
+                self.stats["buckets_launched"] += len(self.buckets)
+        else:
+            missing = self.native.finalize()
         if missing:
             names = [self.param_names[i] for i in missing[:8]]
             raise RuntimeError(

@@ -25,6 +25,11 @@ void dmp_reset_launch_count(void);
 int dmp_version(void);
 int dmp_device_cc(void);                                              /* e.g. 100 for sm_100 */
 int dmp_l2_flush(void* buf, long long bytes, dmp_stream_t stream);    /* benchmark helper */
+/* Stream ordering for the native Reducer launch path (csrc/core.cu): comm waits for cur and for the side streams that are part
+ * of cur's capture (or for all of them outside a capture); cur waits for comm.  Counterpart of the event record / wait pairs
+ * c10d's Reducer issues around each bucket's all-reduce (T/nn/parallel/distributed.py:1183-1304). */
+int dmp_stream_fork(dmp_stream_t cur, dmp_stream_t comm, const dmp_stream_t* side, int n_side);
+int dmp_stream_join(dmp_stream_t cur, dmp_stream_t comm);
 
 /* ------------------------------------------------------------------ tcgen05 GEMM (csrc/kernels/gemm_tcgen05.cu)
  * bf16 x bf16 -> fp32 accumulate in TMEM.  layout 0: A[M,K] B[N,K] (1x1 conv / linear forward, R/model/mobilenetv2.py:17,21,55);
@@ -263,6 +268,18 @@ int dmp_reducer_num_launched(void* h);
 long long dmp_reducer_iterations(void* h);
 int dmp_reducer_ready_order(void* h, int32_t* out, int cap);
 void dmp_reducer_unused_flags(void* h, int32_t* out);
+/* Native launch path: per-bucket launch plans (struct DmpBucketPlan / DmpLaunchFns of csrc/runtime/reducer.cpp, mirrored by
+ * ctypes structures in parallel/reducer.py).  dmp_reducer_grad_ready is the whole autograd hook: mark, decide, order the
+ * communication stream, call the collective's entry point -- c10d's Reducer::autograd_hook -> mark_variable_ready ->
+ * all_reduce_bucket, which the reference README dissects (/root/reference/Readme.md:145-157). */
+int dmp_reducer_set_plans(void* h, const void* fns, const void* plans, int n_plans, dmp_stream_t comm, const dmp_stream_t* side,
+                          int n_side);
+void dmp_reducer_clear_plans(void* h);
+int dmp_reducer_grad_ready(void* h, int p, int unused, dmp_stream_t cur, int32_t* out_caller, int cap);
+int dmp_reducer_finish(void* h, dmp_stream_t cur, int32_t* out_missing, int cap);
+long long dmp_reducer_native_launches(void* h);
+int dmp_reducer_plan_bytes(void);
+int dmp_reducer_fns_bytes(void);
 int dmp_partition_balanced(int n, const double* cost, int W, int32_t* out_bounds);
 int dmp_schedule_generate(int kind, int W, int s, int M, int32_t* out, int cap);
 double dmp_schedule_simulate(int kind, int W, int M, double tf, double tb, int32_t* out_peak_inflight);

@@ -103,3 +103,75 @@ def test_comm_watchdog_polls_reports_once_and_stops():
     with healthy:
         time.sleep(0.1)
     assert healthy.polls >= 2 and healthy.fault is None and not healthy._thread.is_alive()
+
+
+def test_native_hook_launches_plans_in_bucket_order_with_stream_fork_and_join():
+    """The whole gradient-ready hook behind one C++ call (dmp_reducer_grad_ready): the kernel-library entry points are replaced
+    by recording stubs, so the launch order, the arguments taken from each bucket's plan and the fork/join of the communication
+    stream can be checked without a GPU."""
+    import ctypes as C
+
+    from distributed_model_parallel_b200.parallel.reducer import (PLAN_ALLREDUCE_FUSED, PLAN_CALLER, PLAN_NVLS_SGD, PLAN_SGD_FLAT,
+                                                                  BucketPlan, LaunchFns)
+
+    calls = []
+    vp, i32, i64, f32 = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+    FORK = C.CFUNCTYPE(i32, vp, vp, C.POINTER(vp), i32)
+    JOIN = C.CFUNCTYPE(i32, vp, vp)
+    ARF = C.CFUNCTYPE(i32, i32, i32, vp, vp, i32, i32, i64, f32, vp, vp, vp, vp, vp, i32, vp, vp, i32, i32, vp)
+    NVS = C.CFUNCTYPE(i32, vp, vp, vp, vp, vp, vp, i32, vp, i32, i32, i64, f32, i32, vp)
+    SGD = C.CFUNCTYPE(i32, vp, vp, vp, i32, vp, i64, vp, i32, i32, vp)
+    fail = {"on": False}
+    fork = FORK(lambda cur, comm, side, n: calls.append(("fork", cur, comm, [side[i] for i in range(n)])) or 0)
+    join = JOIN(lambda cur, comm: calls.append(("join", cur, comm)) or 0)
+    arf = ARF(lambda algo, dt, bufs, st, rank, W, n, scale, out, m, mom, sh, hp, nest, mp, sp_, za, mb, stream:
+              (calls.append(("allreduce_fused", algo, bufs, rank, W, n, round(scale, 4), m, za, stream)) or (7 if fail["on"] else 0)))
+    nvs = NVS(lambda g, m, s, master, mom, hp, nest, st, rank, W, n, scale, mb, stream: calls.append(("nvls_sgd", g, m, s, n, stream)) or 0)
+    sgd = SGD(lambda master, sh, grad, dt, mom, n, hp, nest, zero, stream: calls.append(("sgd_flat", master, grad, n, zero, stream)) or 0)
+    fns = LaunchFns()
+    for name, cb in (("fork", fork), ("join", join), ("allreduce_fused", arf), ("allreduce_nvls_sgd", nvs), ("sgd_flat", sgd)):
+        setattr(fns, name, C.cast(cb, C.c_void_p).value)
+
+    def plan(kind, **kw):
+        p = BucketPlan()
+        p.kind = kind
+        for k, v in kw.items():
+            setattr(p, k, v)
+        return p
+
+    r = NativeReducerState([0, 0, 1, 2], 3)
+    plans = [plan(PLAN_ALLREDUCE_FUSED, algo=1, bufs=0x1000, rank=1, world=4, numel=4096, scale=0.25, master=0x2000, zero_after=1),
+             plan(PLAN_NVLS_SGD, mc_grad=0x10, mc_master=0x20, mc_shadow=0x30, numel=64),
+             plan(PLAN_SGD_FLAT, master=0x40, grad=0x50, numel=8)]
+    assert r.set_plans(fns, plans, comm_stream=0xC0, side_streams=[0xA1, 0xA2]) is True
+    r.prepare()
+    assert r.grad_ready(3, False, 0xBEEF) == [] and calls == []      # bucket 2 complete, but buckets launch in order
+    assert r.grad_ready(2, False, 0xBEEF) == [] and calls == []
+    assert r.grad_ready(0, False, 0xBEEF) == [] and calls == []
+    assert r.grad_ready(1, False, 0xBEEF) == []                       # releases all three
+    assert [c[0] for c in calls] == ["fork", "allreduce_fused", "fork", "nvls_sgd", "fork", "sgd_flat"]
+    assert calls[0] == ("fork", 0xBEEF, 0xC0, [0xA1, 0xA2])
+    assert calls[1] == ("allreduce_fused", 1, 0x1000, 1, 4, 4096, 0.25, 0x2000, 1, 0xC0)    # launched ON the communication stream
+    assert calls[3] == ("nvls_sgd", 0x10, 0x20, 0x30, 64, 0xC0)
+    assert calls[5] == ("sgd_flat", 0x40, 0x50, 8, 1, 0xC0)
+    assert r.finish(0xBEEF) == [] and calls[-1] == ("join", 0xBEEF, 0xC0)
+    assert r.native_launches() == 3
+    # an iteration without launches does not join; a missing gradient is still reported
+    del calls[:]
+    r.prepare()
+    r.grad_ready(0, False, 1)
+    assert r.finish(1) == [1, 2, 3] and calls == []
+    # a failing entry point surfaces as an error from the hook
+    r.prepare()
+    fail["on"] = True
+    r.grad_ready(0, False, 1)
+    with pytest.raises(RuntimeError):
+        r.grad_ready(1, False, 1)
+    fail["on"] = False
+    # one caller-launched bucket (communication hook, torch.distributed back end) hands every launch back, in order
+    r2 = NativeReducerState([0, 1], 2)
+    assert r2.set_plans(fns, [plan(PLAN_ALLREDUCE_FUSED), plan(PLAN_CALLER)], 0xC0, []) is False
+    r2.prepare()
+    del calls[:]
+    assert r2.grad_ready(1, False, 0) == []
+    assert r2.grad_ready(0, False, 0) == [0, 1] and calls == []

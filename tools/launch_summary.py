@@ -1,13 +1,24 @@
 #!/usr/bin/env python
-"""Summarises an `ncu --metrics gpu__time_duration.sum --csv --log-file X` launch list: per-kernel count, total time, share.
+"""Summarises an `ncu --metrics gpu__time_duration.sum[,dram__bytes_read.sum,dram__bytes_write.sum] --csv --log-file X`
+launch list: per-kernel count, total time, share and (when the DRAM counters were collected) bytes moved and GB/s.
 
-    python tools/launch_summary.py gpurun_out/launches.csv [--steps N] > profiles/launches_summary.txt
+    python tools/launch_summary.py gpurun_out/launches.csv [--steps N] [--list] > profiles/launches_summary.txt
 
-The durations are per-launch device times under ncu (serialised, cold caches): compare SHARES, not absolutes."""
+The durations are per-launch device times under ncu (serialised, cold caches): compare SHARES, not absolutes.
+--list appends every launch in issue order (id, kernel, grid, block, us, MB read, MB written)."""
 import csv
 import re
 import sys
 from collections import defaultdict
+
+UNIT = {"ns": 1e-3, "nsecond": 1e-3, "us": 1.0, "usecond": 1.0, "ms": 1e3, "msecond": 1e3, "s": 1e6, "second": 1e6}
+BYTES = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def short(name):
+    name = re.sub(r"\(.*$", "", name)
+    name = re.sub(r"^void ", "", name)
+    return re.sub(r"\(anonymous namespace\)::", "", name)
 
 
 def main():
@@ -15,38 +26,56 @@ def main():
     steps = 1
     if "--steps" in sys.argv:
         steps = int(sys.argv[sys.argv.index("--steps") + 1])
-    rows = []
     with open(path, newline="") as f:
         lines = [ln for ln in f if not ln.startswith("==")]
-    rd = csv.reader(lines)
     header = None
-    for r in rd:
+    launches = {}
+    order = []
+    for r in csv.reader(lines):
         if header is None:
             if "Kernel Name" in r:
                 header = r
             continue
         if len(r) != len(header):
             continue
-        rows.append(dict(zip(header, r)))
-    tot = defaultdict(float)
-    cnt = defaultdict(int)
-    for r in rows:
-        if r.get("Metric Name") != "gpu__time_duration.sum":
+        d = dict(zip(header, r))
+        lid = d.get("ID")
+        if lid not in launches:
+            launches[lid] = {"name": short(d["Kernel Name"]), "grid": d.get("Grid Size", ""), "block": d.get("Block Size", ""),
+                             "us": 0.0, "rd": 0.0, "wr": 0.0}
+            order.append(lid)
+        m = d.get("Metric Name")
+        try:
+            v = float(d["Metric Value"].replace(",", ""))
+        except ValueError:
             continue
-        name = re.sub(r"\(.*$", "", r["Kernel Name"])
-        name = re.sub(r"^void ", "", name)
-        name = re.sub(r"\(anonymous namespace\)::", "", name)
-        v = float(r["Metric Value"].replace(",", ""))
-        unit = r.get("Metric Unit", "ns")
-        us = v / 1000.0 if unit in ("ns", "nsecond") else (v if unit in ("us", "usecond") else v * 1000.0)
-        tot[name] += us
-        cnt[name] += 1
+        u = d.get("Metric Unit", "")
+        if m == "gpu__time_duration.sum":
+            launches[lid]["us"] = v * UNIT.get(u, 1e-3)
+        elif m == "dram__bytes_read.sum":
+            launches[lid]["rd"] = v * BYTES.get(u, 1.0)
+        elif m == "dram__bytes_write.sum":
+            launches[lid]["wr"] = v * BYTES.get(u, 1.0)
+    tot, cnt, byt = defaultdict(float), defaultdict(int), defaultdict(float)
+    for l in launches.values():
+        tot[l["name"]] += l["us"]
+        cnt[l["name"]] += 1
+        byt[l["name"]] += l["rd"] + l["wr"]
     total = sum(tot.values())
     n = sum(cnt.values())
-    print("# window: %d launches, %.1f us total (%d step(s): %.1f us and %.0f launches per step)" % (n, total, steps, total / steps, n / steps))
-    print("%-86s %7s %10s %7s %8s" % ("kernel", "count", "total_us", "share", "us/launch"))
+    allb = sum(byt.values())
+    print("# window: %d launches, %.1f us total (%d step(s): %.1f us and %.0f launches per step), DRAM %.1f MB per step" % (
+        n, total, steps, total / max(steps, 1), n / max(steps, 1), allb / max(steps, 1) / 1e6))
+    print("%-78s %6s %10s %7s %9s %9s %8s" % ("kernel", "count", "total_us", "share", "us/launch", "DRAM_MB", "GB/s"))
     for k in sorted(tot, key=lambda k: -tot[k]):
-        print("%-86s %7d %10.1f %6.1f%% %8.1f" % (k[:86], cnt[k], tot[k], 100.0 * tot[k] / total, tot[k] / cnt[k]))
+        print("%-78s %6d %10.1f %6.1f%% %9.1f %9.1f %8.0f" % (k[:78], cnt[k], tot[k], 100.0 * tot[k] / max(total, 1e-9), tot[k] / cnt[k],
+                                                          byt[k] / 1e6, byt[k] / max(tot[k], 1e-9) / 1e3))
+    if "--list" in sys.argv:
+        print("\n# launches in issue order")
+        for lid in order:
+            l = launches[lid]
+            print("%5s %-70s %-16s %-14s %8.1f us %8.2f MB rd %8.2f MB wr" % (lid, l["name"][:70], l["grid"], l["block"], l["us"],
+                                                                             l["rd"] / 1e6, l["wr"] / 1e6))
 
 
 if __name__ == "__main__":
