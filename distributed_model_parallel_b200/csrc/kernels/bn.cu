@@ -13,6 +13,7 @@
 // (threads * VEC) is a multiple of C, therefore every thread sees the same VEC channels on every
 // iteration and keeps its partial sums / affine coefficients in registers.
 #include "../common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -672,6 +673,11 @@ int bn_coop_grid(K kernel, long long nvec, int C, int vec, size_t smem) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BN_THREADS, smem) != cudaSuccess || per_sm < 1) return -1;
     if (per_sm > 2) per_sm = 2;
     long long cap = (long long)dmp_num_sms() * per_sm;
+    // DMP_BN_COOP_MAX_BLOCKS: a cooperative grid needs all its blocks resident at once; next to a side-stream kernel that
+    // holds part of the SMs, a grid sized for the whole GPU waits at its barrier until that kernel has drained
+    // (0 = none; default two blocks on each of the two thirds of the SMs the side-stream weight-gradient kernels leave free)
+    static const int coop_cap = [] { const char* e = getenv("DMP_BN_COOP_MAX_BLOCKS"); return e ? atoi(e) : 2 * (dmp_num_sms() - dmp_num_sms() / 3); }();
+    if (coop_cap > 0 && cap > coop_cap) cap = coop_cap;
     // 8 16-byte vectors per thread.  Measured (bench/bn_phase_bench.py): fewer, fatter blocks are slower across the board
     // (16 per thread: +2..5 us per launch); thinner ones (4) gain ~1 us on narrow layers in isolation but cost wide layers
     // 2 us (every block ends with 2*C double atomics) and the whole step came out slower (5.05 vs 4.96 ms).

@@ -5,6 +5,7 @@
 // 8 contiguous channels (one 16-byte vector) of one output pixel, so every global access is a 128-bit
 // coalesced load/store and neighbouring pixels are served from L1/L2.
 #include "../common.cuh"
+#include <stdlib.h>
 
 namespace {
 
@@ -567,10 +568,16 @@ static int dw_wgrad_grid(int N, int Ho, int Wo, int C, int stride) {
     const int TWs = stride == 1 ? 4 : 2;
     const long long nitems = (long long)N * Ho * ((Wo + TWs - 1) / TWs);
     long long want = (nitems * P2 / 16 + (long long)warps_per_block * 4 - 1) / ((long long)warps_per_block * 4);  // ~4 items per lane pair
-    const long long cap = (long long)dmp_num_sms();  // 160-190 registers per thread: one 256-thread block per SM
+    long long cap = (long long)dmp_num_sms();  // 160-190 registers per thread: one 256-thread block per SM
+    // DMP_DW_WGRAD_MAX_BLOCKS (0 = none; default a third of the SMs): the kernel runs on a side stream next to the data-gradient
+    // chain, and a grid that takes every SM stalls the chain until it drains (see wgrad_max_ctas in gemm_tcgen05.cu)
+    static const int side_cap = [] { const char* e = getenv("DMP_DW_WGRAD_MAX_BLOCKS"); return e ? atoi(e) : dmp_num_sms() / 3; }();
+    if (side_cap > 0 && cap > side_cap) cap = side_cap;
     if (want > cap) want = cap;
     if (want < 1) want = 1;
-    return (int)(((want + q - 1) / q) * q);
+    long long g = (want / q) * q;  // largest multiple of q under the cap (at least q)
+    if (g < q) g = q;
+    return (int)g;
 }
 
 static int dw_check(const char* name, int N, int H, int W, int C, int stride) {

@@ -17,6 +17,8 @@
 // masked in the epilogue.
 #include "tcgen05_common.cuh"
 #include <atomic>
+#include <stdlib.h>
+
 
 namespace {
 
@@ -553,6 +555,20 @@ const int g_gemm_store_mode = [] {
     return (e != nullptr && e[0] >= '0' && e[0] <= '2') ? e[0] - '0' : 1;
 }();
 
+// DMP_WGRAD_MAX_CTAS: grid cap of the split-K weight-gradient GEMM (0 = none; default a third of the SMs).  Measured on the
+// captured MobileNetV2 step at batch 128 (profiles/sm_partition_sweep.txt): uncapped 4.28 ms, 96 CTAs 4.16, 64 4.10, 48 4.07;
+// with the depthwise weight gradient and the cooperative BatchNorm grids sized to match, 3.93 ms.  Neutral at batch 512.
+int wgrad_max_ctas() {
+    static const int v = [] { const char* e = getenv("DMP_WGRAD_MAX_CTAS"); return e ? atoi(e) : dmp_num_sms() / 3; }();
+    return v;
+}
+
+// DMP_GEMM_CHAIN_MAX_SMS: SMs the forward / data-gradient GEMMs size their persistent grid for (0 = all).
+int chain_max_sms() {
+    static const int v = [] { const char* e = getenv("DMP_GEMM_CHAIN_MAX_SMS"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
 template <int BN, bool A_MN, bool B_MN, int ECOL = 0, bool BRES = false>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int splits, cudaStream_t stream,
                 const Batch& dbatch = Batch()) {
@@ -592,6 +608,12 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     const int ctas_per_sm = smem_bytes <= 110 * 1024 ? 2 : 1;
     long long grid = (long long)dmp_num_sms() * ctas_per_sm;
     if (grid > items) grid = items;
+    // weight-gradient GEMMs run on a side stream next to the data-gradient chain: a grid that fills every SM (one CTA with
+    // ~200 KB of shared memory each) leaves the chain's kernels nowhere to run until it drains, so it may be capped
+    if (A_MN && p.epi == 2 && wgrad_max_ctas() > 0 && grid > wgrad_max_ctas()) grid = wgrad_max_ctas();
+    // ... and the chain's own GEMMs then take the SMs that are left (a statically scheduled CTA that has to wait for an SM
+    // delays all of its tiles)
+    if (!(A_MN && p.epi == 2) && chain_max_sms() > 0 && grid > (long long)chain_max_sms() * ctas_per_sm) grid = (long long)chain_max_sms() * ctas_per_sm;
     if (ECOL != 0 || BRES) {  // every tile of a CTA must have the same n0: the item stride has to be a multiple of n_tiles
         DMP_REQUIRE(splits == 1 && q.n_tiles <= grid, "gemm statistics epilogue: %d column tiles do not fit the grid", q.n_tiles);
         grid = grid / q.n_tiles * q.n_tiles;
