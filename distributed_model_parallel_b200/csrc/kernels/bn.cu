@@ -14,6 +14,7 @@
 // iteration and keeps its partial sums / affine coefficients in registers.
 #include "../common.cuh"
 #include <stdlib.h>
+#include <atomic>
 
 namespace {
 
@@ -393,9 +394,10 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T*
     __shared__ int s_last;
     const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
     const long long stride = (long long)gridDim.x * BN_THREADS;
-    const int ch0 = (int)((tid * VEC) % C);
+    const int ch0 = (int)(((unsigned)tid * (unsigned)VEC) % (unsigned)C);  // grid * BN_THREADS * VEC stays far below 2^31
     const double inv_count = 1.0 / count;
     float sc[VEC], sh[VEC];
+    bool odd = false;  // folds every loaded sum into the barrier predicate below
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
         const int c = ch0 + j;
@@ -406,28 +408,33 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T*
         const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
         sc[j] = g * is;
         sh[j] = b - (float)m * g * is;
+        odd |= !(sc[j] == sc[j]) && !(sh[j] == sh[j]) && (sc[j] == sh[j]);  // never true; depends on both loads
     }
-    if (blockIdx.x == 0) {
-        for (int c = threadIdx.x; c < C; c += BN_THREADS) {
-            const double m = sums[c] / count;
-            double var = sums[C + c] / count - m * m;
-            if (var < 0.0) var = 0.0;
-            mean_out[c] = (float)m;
-            invstd_out[c] = (float)(1.0 / sqrt(var + (double)eps));
-            if (running_mean != nullptr) {
-                const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
-                running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
-                running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
-            }
+    // One channel per thread over the first ceil(C / BN_THREADS) blocks publishes mean / invstd / running statistics (a single
+    // block looping over C channels of double divisions and square roots was the slowest block of every launch).
+    if (tid < C) {
+        const int c = (int)tid;
+        const double m = sums[c] * inv_count;
+        double var = sums[C + c] * inv_count - m * m;
+        if (var < 0.0) var = 0.0;
+        mean_out[c] = (float)m;
+        const double isd = 1.0 / sqrt(var + (double)eps);
+        invstd_out[c] = (float)isd;
+        odd |= !(isd == isd);
+        if (running_mean != nullptr) {
+            const double unbiased = count > 1.0 ? var * count / (count - 1.0) : var;
+            running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * (float)m;
+            running_var[c] = (1.f - momentum) * running_var[c] + momentum * (float)unbiased;
         }
-        if (threadIdx.x == 0 && num_batches_tracked != nullptr) *num_batches_tracked += 1;
+        if (c == 0 && num_batches_tracked != nullptr) *num_batches_tracked += 1;
     }
-    // everything this block needed from `sums` is in registers: take a ticket; the last block clears the buffer
-    __threadfence();
-    __syncthreads();
+    // Everything this block needs from `sums` has ARRIVED in registers once every thread has evaluated `odd` (the barrier
+    // predicate forces that use), so the ticket needs no memory fence: the last block to take one clears the buffer for the
+    // producer's next accumulation (CUDA-graph replay included), and a cleared value can no longer reach any thread.
+    const int any_odd = __syncthreads_or(odd ? 1 : 0);
     if (threadIdx.x == 0) {
         int* ticket = (int*)(sums + 2 * (long long)C);
-        s_last = (atomicAdd(ticket, 1) == (int)gridDim.x - 1);
+        s_last = (atomicAdd(ticket, 1 + any_odd) == (int)gridDim.x - 1);
     }
     __syncthreads();
     if (s_last) {
@@ -594,6 +601,141 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
     }
 }
 
+// Shared-memory-resident variant of bn_bwd_fused_kernel (bf16 tensors that fit on chip: 32 or 48 bytes per 8 elements, up to
+// ~190 KB per SM): dy, x (and y when the ReLU mask needs it) are fetched ONCE, with cp.async straight into shared memory -- every
+// load of a thread is in flight at the same time and costs no registers -- and both passes (reductions, then dx after the grid
+// barrier) read them back from there.  The two-pass kernel re-reads both tensors after the barrier and keeps only 8 loads per
+// thread in flight; for the layers of the 8x8 / 4x4 stages (1-10 MB) that second round trip was a third of the launch.
+// vpt = vectors per thread (runtime); shared memory: [vpt][NT][BN_THREADS] int4 followed by the reduction scratch.
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+}
+
+__global__ void __launch_bounds__(BN_THREADS)
+bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, const bf16* __restrict__ x,
+                       const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                       const float* __restrict__ beta, double count, bf16* __restrict__ dx, bf16* __restrict__ dres,
+                       float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate_params, long long nvec, int C, int relu,
+                       double* __restrict__ ws, int vpt) {
+    constexpr int VEC = 8;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cg::grid_group grid = cg::this_grid();
+    const bool mask_from_x = relu && (y == nullptr);
+    const bool need_y = relu && !mask_from_x;
+    const int NT = need_y ? 3 : 2;
+    int4* stash = (int4*)smem_raw;                                                      // [vpt][NT][BN_THREADS]
+    float* sm = (float*)(smem_raw + (size_t)vpt * NT * BN_THREADS * sizeof(int4));      // block_channel_reduce scratch
+    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long stride = (long long)gridDim.x * BN_THREADS;
+    for (int u = 0; u < vpt; ++u) {
+        const long long v = tid + u * stride;
+        if (v < nvec) {
+            int4* slot = stash + ((size_t)u * NT) * BN_THREADS + threadIdx.x;
+            cp_async16(slot, dy + v * 8);
+            cp_async16(slot + BN_THREADS, x + v * 8);
+            if (need_y) cp_async16(slot + 2 * BN_THREADS, y + v * 8);
+        }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    int* parity_p = (int*)(ws + 4 * (long long)NSETS * C);
+    const int parity = *parity_p;
+    double* accum = ws + (long long)parity * 2 * NSETS * C;
+    double* other = ws + (long long)(parity ^ 1) * 2 * NSETS * C;
+    const int ch0 = (int)(((unsigned)tid * (unsigned)VEC) % (unsigned)C);
+    float mu[VEC], is[VEC], gs[VEC], bs[VEC], acc[2 * VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        mu[j] = mean[ch0 + j];
+        is[j] = invstd[ch0 + j];
+        gs[j] = (gamma ? gamma[ch0 + j] : 1.f);
+        bs[j] = (beta ? beta[ch0 + j] : 0.f);
+        acc[j] = 0.f;
+        acc[VEC + j] = 0.f;
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");  // each thread reads back only what it fetched itself
+    for (int u = 0; u < vpt; ++u) {
+        if (tid + u * stride < nvec) {
+            const int4* slot = stash + ((size_t)u * NT) * BN_THREADS + threadIdx.x;
+            float g[VEC], xv[VEC];
+            Vec<bf16>::unpack(slot[0], g);
+            Vec<bf16>::unpack(slot[BN_THREADS], xv);
+            if (relu) {
+                if (mask_from_x) {
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) g[j] = ((xv[j] - mu[j]) * is[j] * gs[j] + bs[j]) > 0.f ? g[j] : 0.f;
+                } else {
+                    float yv[VEC];
+                    Vec<bf16>::unpack(slot[2 * BN_THREADS], yv);
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                acc[j] += g[j];
+                acc[VEC + j] += g[j] * (xv[j] - mu[j]) * is[j];
+            }
+        }
+    }
+    block_channel_reduce<VEC, 2>(acc, ch0, C, accum + (long long)(blockIdx.x % NSETS) * 2 * C, sm);
+    grid.sync();
+    const double inv_count = 1.0 / count;
+    float a[VEC], b[VEC], c[VEC];
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+        double s1 = 0.0, s2 = 0.0;
+#pragma unroll
+        for (int k = 0; k < NSETS; ++k) {
+            s1 += accum[(long long)k * 2 * C + ch0 + j];
+            s2 += accum[(long long)k * 2 * C + C + ch0 + j];
+        }
+        a[j] = gs[j] * is[j];
+        b[j] = (float)(s1 * inv_count);
+        c[j] = (float)(s2 * inv_count);
+    }
+    if (tid < C) {  // one channel per thread over the first blocks
+        const int ch = (int)tid;
+        double s1 = 0.0, s2 = 0.0;
+        for (int k = 0; k < NSETS; ++k) {
+            s1 += accum[(long long)k * 2 * C + ch];
+            s2 += accum[(long long)k * 2 * C + C + ch];
+        }
+        const float db = (float)s1, dg = (float)s2;
+        if (dgamma) dgamma[ch] = accumulate_params ? dgamma[ch] + dg : dg;
+        if (dbeta) dbeta[ch] = accumulate_params ? dbeta[ch] + db : db;
+        if (ch == 0) *parity_p = parity ^ 1;
+    }
+    for (long long i = tid; i < 2 * (long long)NSETS * C; i += stride) other[i] = 0.0;
+    for (int u = 0; u < vpt; ++u) {
+        const long long v = tid + u * stride;
+        if (v < nvec) {
+            const int4* slot = stash + ((size_t)u * NT) * BN_THREADS + threadIdx.x;
+            float g[VEC], xv[VEC];
+            Vec<bf16>::unpack(slot[0], g);
+            Vec<bf16>::unpack(slot[BN_THREADS], xv);
+            if (relu) {
+                if (mask_from_x) {
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) g[j] = ((xv[j] - mu[j]) * is[j] * gs[j] + bs[j]) > 0.f ? g[j] : 0.f;
+                } else {
+                    float yv[VEC];
+                    Vec<bf16>::unpack(slot[2 * BN_THREADS], yv);
+#pragma unroll
+                    for (int j = 0; j < VEC; ++j) g[j] = yv[j] > 0.f ? g[j] : 0.f;
+                }
+            }
+            if (dres != nullptr) Vec<bf16>::store(dres, v, g);
+#pragma unroll
+            for (int j = 0; j < VEC; ++j) {
+                const float xh = (xv[j] - mu[j]) * is[j];
+                g[j] = a[j] * (g[j] - b[j] - xh * c[j]);
+            }
+            Vec<bf16>::store(dx, v, g);
+        }
+    }
+}
+
 // BatchNorm backward when the two reductions already exist: g is the incoming gradient with the ReLU mask applied, and
 // sums = {sum g, sum g * xhat} (double[2C] + int ticket) were accumulated by the kernel that produced g (the data-gradient
 // kernel of the consuming convolution: dmp_gemm_bf16_dgrad_bnbwd / dmp_dwconv3x3_dgrad_bnbwd).  One elementwise pass:
@@ -690,18 +832,82 @@ int bn_coop_grid(K kernel, long long nvec, int C, int vec, size_t smem) {
     return (int)g;
 }
 
-int bn_grid(long long nvec, int C, int vec) {
+int bn_grid(long long nvec, int C, int vec, int vecs_per_thread = 8) {
     // smallest multiple q of blocks such that (blocks * BN_THREADS * vec) % C == 0
     long long per_block = (long long)BN_THREADS * vec;
     long long a = C, b = per_block;
     while (b) { long long t = a % b; a = b; b = t; }
     int q = (int)(C / a);
-    long long want = (nvec + BN_THREADS * 8 - 1) / (BN_THREADS * 8);
+    long long want = (nvec + BN_THREADS * vecs_per_thread - 1) / (BN_THREADS * vecs_per_thread);
     long long cap = (long long)dmp_num_sms() * 2;  // fewer, longer-lived blocks: each pays 2*C double atomics at its end
     if (want > cap) want = cap;
     if (want < 1) want = 1;
     long long g = ((want + q - 1) / q) * q;
     return (int)g;
+}
+
+// Shared-memory-resident BatchNorm backward (bn_bwd_resident_kernel).  Returns 0 when launched, 1 when the tensor does not fit
+// on chip (the caller uses the two-pass kernel), negative on a CUDA error.  DMP_BN_BWD_RESIDENT=0 disables.
+int bn_coop_sms() {  // SMs a cooperative BatchNorm grid is sized for (see DMP_BN_COOP_MAX_BLOCKS in bn_coop_grid)
+    static const int cap = [] { const char* e = getenv("DMP_BN_COOP_MAX_BLOCKS"); return e ? atoi(e) : 2 * (dmp_num_sms() - dmp_num_sms() / 3); }();
+    const int sms = dmp_num_sms();
+    return (cap > 0 && cap / 2 < sms) ? (cap / 2 > 0 ? cap / 2 : 1) : sms;
+}
+
+int bn_bwd_try_resident(const void* dy, const void* y, const void* x, const float* mean, const float* invstd, const float* gamma,
+                        const float* beta, double count, void* dx, void* dres, float* dgamma, float* dbeta, int accumulate_params,
+                        long long nvec, int C, int relu, double* ws, cudaStream_t stream) {
+    static const bool enabled = [] { const char* e = getenv("DMP_BN_BWD_RESIDENT"); return e == nullptr || e[0] != '0'; }();
+    if (!enabled) return 1;
+    // Measured inside a graph (bench/chain_bench.py, B200): 9.0 -> 7.0 us up to ~2 MB per tensor (8192 x 64 ... 2048 x 320),
+    // no change at 6 MB (8192 x 384: 15 us either way, bound by the arithmetic of 16 resident warps per SM), slightly slower
+    // for few rows of many channels (2048 x 960).  Larger tensors keep the two-pass kernel.
+    if (nvec * 16 > (3ll << 20)) return 1;
+    const int NT = (relu && y != nullptr) ? 3 : 2;
+    const size_t scratch = (size_t)BN_THREADS * 2 * 8 * sizeof(float);
+    const size_t per_vec = (size_t)NT * BN_THREADS * sizeof(int4);
+    // alignment: the grid must be a multiple of q so that every thread keeps its channels across its vectors
+    long long per_block = (long long)BN_THREADS * 8;
+    long long a = C, b = per_block;
+    while (b) { long long t = a % b; a = b; b = t; }
+    const int q = (int)(C / a);
+    const int sms = bn_coop_sms();
+    static std::atomic<unsigned long long> configured{0};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!(configured.load(std::memory_order_acquire) & (1ull << (dev & 63)))) {
+        DMP_CHECK_CUDA(cudaFuncSetAttribute(bn_bwd_resident_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        configured.fetch_or(1ull << (dev & 63), std::memory_order_release);
+    }
+    // two blocks per SM with up to ~96 KB each, else one block with up to 200 KB
+    for (int per_sm = 2; per_sm >= 1; --per_sm) {
+        const size_t budget = per_sm == 2 ? 100 * 1024 : 200 * 1024;
+        const int vpt_max = (int)((budget - scratch) / per_vec);
+        long long cap = (long long)sms * per_sm;
+        long long g = (cap / q) * q;
+        if (g < q) continue;
+        // as few vectors per thread as the grid allows, but at least 4 (fewer, fatter blocks: each ends with 2*C atomics)
+        long long vpt = (nvec + g * BN_THREADS - 1) / (g * BN_THREADS);
+        if (vpt > vpt_max) continue;
+        if (vpt < 4) {
+            long long want = (nvec + BN_THREADS * 4 - 1) / (BN_THREADS * 4);
+            g = (want / q) * q;
+            if (g < q) g = q;
+            vpt = (nvec + g * BN_THREADS - 1) / (g * BN_THREADS);
+            if (vpt > vpt_max) continue;
+        }
+        const size_t smem = (size_t)vpt * per_vec + scratch;
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bn_bwd_resident_kernel, BN_THREADS, smem) != cudaSuccess || occ < 1) continue;
+        if ((long long)occ * dmp_num_sms() < g) continue;
+        int vpt_i = (int)vpt;
+        void* args[] = {(void*)&dy, (void*)&y, (void*)&x, (void*)&mean, (void*)&invstd, (void*)&gamma, (void*)&beta, (void*)&count,
+                        (void*)&dx, (void*)&dres, (void*)&dgamma, (void*)&dbeta, (void*)&accumulate_params, (void*)&nvec, (void*)&C,
+                        (void*)&relu, (void*)&ws, (void*)&vpt_i};
+        DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_resident_kernel, dim3((unsigned)g), dim3(BN_THREADS), args, smem, stream));
+        return 0;
+    }
+    return 1;
 }
 
 int bn_check(const char* name, long long M, int C, int dtype) {
@@ -850,7 +1056,8 @@ DMP_API int dmp_bn_apply_sums(const void* x, int dtype, const void* residual, vo
     DMP_REQUIRE(sums && mean && invstd, "dmp_bn_apply_sums: null sums/mean/invstd");
     const int vec = dtype == 1 ? 8 : 4;
     const long long nvec = M * C / vec;
-    const int grid = bn_grid(nvec, C, vec);
+    // no reduction at the end of a block here, so thin blocks: 4 vectors per thread are one batch of loads in flight
+    const int grid = bn_grid(nvec, C, vec, 4);
     if (dtype == 1)
         bn_apply_sums_kernel<bf16><<<grid, BN_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)residual, (bf16*)y, nvec, C, (double)M,
                                                                     gamma, beta, running_mean, running_var, num_batches_tracked,
@@ -898,6 +1105,13 @@ DMP_API int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int d
                     (void*)&dres, (void*)&dgamma, (void*)&dbeta, (void*)&accumulate_params, (void*)&nvec, (void*)&C, (void*)&relu,
                     (void*)&ws};
     if (dtype == 1) {
+        if (int rc = bn_bwd_try_resident(dy, y, x, mean, invstd, gamma, beta, count, dx, dres, dgamma, dbeta, accumulate_params, nvec, C,
+                                         relu, ws, stream)) {
+            if (rc < 0) return rc;
+        } else {
+            DMP_COUNT_LAUNCH(1);
+            return 0;
+        }
         const int grid = bn_coop_grid(bn_bwd_fused_kernel<bf16>, nvec, C, vec, smem);
         if (grid < 0) return 1;
         DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_fused_kernel<bf16>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
