@@ -24,6 +24,8 @@ ap.add_argument("--sync-bn", action="store_true")
 ap.add_argument("--schedule", default="1f1b")
 ap.add_argument("--microbatches", type=int, default=8)
 ap.add_argument("--seq-len", type=int, default=128)
+ap.add_argument("--image", type=int, default=0, help="square image side (default 32, 224 for resnet50)")
+ap.add_argument("--partition", default="graph_time", choices=["graph_time", "params"])
 args = ap.parse_args()
 
 from distributed_model_parallel_b200.models import build_model
@@ -32,6 +34,8 @@ from distributed_model_parallel_b200.optim import FlatFusedSGD
 
 
 def shape():
+    if args.image:
+        return (3, args.image, args.image), (1000 if args.model == "resnet50" else 10)
     if args.model == "resnet50":
         return (3, 224, 224), 1000
     if args.model == "bert_base":
@@ -125,10 +129,16 @@ if args.mode == "ddp":
                           "global_batch": args.batch_per_gpu * world, "ms_per_step": ms, "images_per_s": args.batch_per_gpu * world / ms * 1e3,
                           "paths": dict(OF.path_counts) if args.impl == "ours" else None}))
 else:
-    from distributed_model_parallel_b200.parallel.pipeline import PipelineStage, layer_costs, split_sequential
+    from distributed_model_parallel_b200.parallel.pipeline import PipelineStage, layer_costs, measured_boundaries, split_sequential
     full = build_model(args.model, num_classes=nc)
     seq = full.as_sequential()
-    stages = split_sequential(seq, world, layer_costs(seq, "params"))
+    gb = args.batch_per_gpu * world
+    mbs = 1 if args.schedule == "naive" else args.microbatches
+    if args.partition == "params":
+        stages = split_sequential(seq, world, layer_costs(seq, "params"))
+    else:
+        sample = batch(max(1, gb // mbs), "cpu")[0] if rank == 0 else None
+        stages = split_sequential(seq, world, boundaries=measured_boundaries(seq, world, sample, dev, rank))
     module = stages[rank].to(dev)
     params = list(module.parameters())
     opt = FlatFusedSGD(params, **sgd) if params else None

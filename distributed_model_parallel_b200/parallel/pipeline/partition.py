@@ -49,8 +49,8 @@ def layer_costs(seq: nn.Sequential, mode: str = "params", sample: Optional[torch
         if sample is None:
             raise ValueError("mode='time' needs a sample input")
         costs, x = [], sample
-        for l in layers:
-            xin = x.detach().requires_grad_(x.is_floating_point())
+        for li, l in enumerate(layers):
+            xin = x.detach().requires_grad_(x.is_floating_point() and li > 0)  # the network input itself needs no gradient
             best = float("inf")
             for _ in range(repeats):
                 if x.is_cuda:
@@ -67,7 +67,76 @@ def layer_costs(seq: nn.Sequential, mode: str = "params", sample: Optional[torch
         for l in layers:
             l.zero_grad(set_to_none=True)
         return costs
+    if mode == "graph_time":
+        # What a layer costs INSIDE a captured stage: forward + backward of the layer replayed from a CUDA graph and timed with
+        # events.  Eager timing (mode "time") mostly counts kernel launches -- the host cannot issue them as fast as a B200
+        # retires them -- while the pipeline stages replay graphs, where only device time is left.
+        if sample is None or not sample.is_cuda:
+            raise ValueError("mode='graph_time' needs a CUDA sample input")
+        costs, x = [], sample
+        side = torch.cuda.Stream(device=sample.device)
+        for li, l in enumerate(layers):
+            xin = x.detach().clone().requires_grad_(x.is_floating_point() and li > 0)  # the network input needs no gradient
+            side.wait_stream(torch.cuda.current_stream(sample.device))
+            with torch.cuda.stream(side):
+                for _ in range(2):  # eager warm-up: lazy initialisation must not land in the capture
+                    y = l(xin)
+                    if y.requires_grad:
+                        torch.autograd.backward(y, torch.ones_like(y))
+            torch.cuda.current_stream(sample.device).wait_stream(side)
+            torch.cuda.synchronize(sample.device)
+            try:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=side):
+                    y = l(xin)
+                    if y.requires_grad:
+                        torch.autograd.backward(y, torch.ones_like(y))
+                g.replay()
+                torch.cuda.synchronize(sample.device)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                for _ in range(repeats):
+                    g.replay()
+                e1.record()
+                torch.cuda.synchronize(sample.device)
+                costs.append(e0.elapsed_time(e1) / repeats * 1e-3)
+                del g
+            except Exception:  # a layer that cannot be captured: eager device time
+                torch.cuda.synchronize(sample.device)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                y = l(xin)
+                if y.requires_grad:
+                    torch.autograd.backward(y, torch.ones_like(y))
+                e1.record()
+                torch.cuda.synchronize(sample.device)
+                costs.append(e0.elapsed_time(e1) * 1e-3)
+            x = y.detach()
+        for l in layers:
+            l.zero_grad(set_to_none=True)
+        return costs
     raise ValueError("unknown cost mode %r" % mode)
+
+
+def measured_boundaries(seq: nn.Sequential, num_stages: int, sample: torch.Tensor, device, rank: int, group=None,
+                        mode: str = "graph_time") -> List[int]:
+    """Stage boundaries from per-layer costs measured on ``device`` by rank 0 (the whole model visits that GPU once, layer
+    by layer) and broadcast, so every stage adopts the same cut.  ``sample``: one MICRO-batch of stage-0 input."""
+    import torch.distributed as dist
+
+    b = torch.zeros(num_stages + 1, dtype=torch.int64, device=device)
+    if rank == 0:
+        seq.to(device)
+        buffers = [t.detach().clone() for t in seq.buffers()]  # train-mode passes must not leak into BatchNorm statistics
+        costs = layer_costs(seq, mode, sample=sample.to(device))
+        with torch.no_grad():
+            for t, v in zip(seq.buffers(), buffers):
+                t.copy_(v)
+        seq.to("cpu")
+        b.copy_(torch.tensor(partition_balanced(costs, num_stages), dtype=torch.int64))
+    if dist.is_available() and dist.is_initialized():
+        dist.broadcast(b, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+    return [int(v) for v in b.tolist()]
 
 
 def split_sequential(seq: nn.Sequential, num_stages: int, costs: Optional[Sequence[float]] = None,

@@ -20,7 +20,8 @@ from ..data import prepare_dataloader
 from ..models import build_model
 from ..ops import functional as OF
 from ..optim import FlatFusedSGD
-from ..parallel.pipeline import PipelineStage, layer_costs, partition_balanced, reference_split, split_sequential
+from ..parallel.pipeline import (PipelineStage, layer_costs, measured_boundaries, partition_balanced, reference_split,
+                                 split_sequential)
 from ..utils import AverageMeter, EpochLogger, TrainConfig, accuracy, get_lr, save_pipeline_shard, stage_key_map
 from .common import CosineWithWarmup, limit
 
@@ -36,17 +37,10 @@ def _boundaries(seq, world_size: int, cfg: TrainConfig, device, rank: int):
     mode = getattr(cfg, "partition", None) or ("time" if device.type == "cuda" else "params")
     if mode != "time":
         return partition_balanced(layer_costs(seq, mode), world_size)
-    b = torch.zeros(world_size + 1, dtype=torch.int64, device=device)
-    if rank == 0:
-        from ..data.datasets import sample_batch
-        mb = max(1, cfg.batch_size // max(1, cfg.microbatches))
-        x = sample_batch(cfg, mb).to(device)
-        seq.to(device)
-        costs = layer_costs(seq, "time", sample=x)
-        seq.to("cpu")
-        b.copy_(torch.tensor(partition_balanced(costs, world_size), dtype=torch.int64))
-    dist.broadcast(b, src=0)
-    return [int(v) for v in b.tolist()]
+    from ..data.datasets import sample_batch
+    mb = max(1, cfg.batch_size // max(1, cfg.microbatches))
+    x = sample_batch(cfg, mb) if rank == 0 else None
+    return measured_boundaries(seq, world_size, x, device, rank)
 
 
 def worker(rank: int, world_size: int, cfg: TrainConfig, init_pg: bool = True):
