@@ -46,8 +46,10 @@ def timed(fn, iters):
 try:  # NVLS multicast buffer (switch-side reduction); absent on platforms without multicast support
     from distributed_model_parallel_b200.parallel.symm import ProcessMulticast
     mcbuf = ProcessMulticast(args.max_mb * 1024 * 1024)
+    mc_master = ProcessMulticast(args.max_mb * 1024 * 1024)      # fused variant: fp32 master and bf16 shadow live in multicast
+    mc_shadow = ProcessMulticast(args.max_mb * 1024 * 1024 // 2)  # buffers too (multimem.st writes every rank's copy)
 except Exception as e:  # noqa: BLE001
-    mcbuf = None
+    mcbuf = mc_master = mc_shadow = None
     if rank == 0:
         print("# NVLS multicast unavailable: %s" % str(e)[:200], flush=True)
 
@@ -60,7 +62,7 @@ if sizes[-1] != args.max_mb:
     sizes.append(args.max_mb)
 for mb in sizes:
     n = mb * 1024 * 1024 // 4  # fp32 gradients
-    n = n // (4 * world) * (4 * world)
+    n = n // (8 * world) * (8 * world)
     S = n * 4
     buf = g.alloc(S); grad = buf.view(torch.float32, n); grad.normal_()
     out = torch.empty_like(grad)
@@ -81,6 +83,11 @@ for mb in sizes:
     if mcbuf is not None:
         mcbuf.view(torch.float32, n).normal_()
         res["nvls_s"] = timed(lambda: _native.check(lib.dmp_allreduce_nvls(mcbuf.mc_ptr, state.ptrs, rank, world, n, 1.0 / world, 0, sp)), iters)
+        if n % (8 * world) == 0:
+            mc_master.view(torch.float32, n).normal_()
+            res["nvls_fused_sgd_s"] = timed(lambda: _native.check(lib.dmp_allreduce_nvls_sgd(
+                mcbuf.mc_ptr, mc_master.mc_ptr, mc_shadow.mc_ptr, mc_master.view(torch.float32, n).data_ptr(), mom.data_ptr(), hp.data_ptr(), 0,
+                state.ptrs, rank, world, n, 1.0 / world, 0, sp)), iters)
     # NCCL + separate fused SGD kernel = what the fused variants replace
     res["nccl_plus_sgd_s"] = timed(lambda: (dist.all_reduce(ref), lib.dmp_sgd_flat(master.data_ptr(), shadow.data_ptr(), ref.data_ptr(), 0, mom.data_ptr(), n, hp.data_ptr(), 0, 1, sp)), iters)
     f = 2.0 * (world - 1) / world

@@ -244,8 +244,8 @@ class TorchDistBackend:
 class PeerBackend:
     """Bucket all-reduce with our peer-memory kernels on a dedicated high-priority stream.
 
-    One-shot for buckets up to ``oneshot_max_bytes`` (env ``DMP_ONESHOT_MAX_BYTES``, default 512 KiB),
-    two-shot above.  With a ``FusedSGDState`` attached to the bucket the same kernel applies the 1/W scale,
+    One-shot for buckets up to ``oneshot_max_bytes`` (env ``DMP_ONESHOT_MAX_BYTES``; default by rank count: 8 MiB at 2 ranks,
+    4 MiB up to 4, 2 MiB beyond, from the measured crossovers), two-shot above.  With a ``FusedSGDState`` attached to the bucket the same kernel applies the 1/W scale,
     the bf16->fp32 cast and the SGD-momentum update, writes the new parameters (fp32 master + bf16 shadow)
     and zeroes the gradient bucket for the next iteration.
     """
@@ -265,7 +265,10 @@ class PeerBackend:
         self.device = torch.device(device) if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.symm = ProcessSymmGroup(self.group, self.device) if self.world_size > 1 else None
         self.state = self.symm.new_state() if self.symm is not None else None
-        self.oneshot_max_bytes = int(os.environ.get("DMP_ONESHOT_MAX_BYTES", oneshot_max_bytes or 512 * 1024))
+        # one-shot (every rank reads every peer's whole bucket) against two-shot (reduce-scatter + all-gather): the crossover
+        # moves down with the rank count -- 4..16 MB at 2 ranks, 1..4 MB at 8 (profiles/allreduce_sweep_*gpu.json)
+        table = 8 << 20 if self.world_size <= 2 else (4 << 20 if self.world_size <= 4 else 2 << 20)
+        self.oneshot_max_bytes = int(os.environ.get("DMP_ONESHOT_MAX_BYTES", oneshot_max_bytes or table))
         self.max_blocks = int(os.environ.get("DMP_COMM_MAX_BLOCKS", max_blocks or 0))
         self.stream = torch.cuda.Stream(device=self.device, priority=-1)
         self._launched_any = False

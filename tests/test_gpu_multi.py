@@ -376,6 +376,14 @@ def test_ddp_peer_fused_end_to_end(mode):
     _spawn(_w_ddp, 2, mode)
 
 
+@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4+ GPUs")
+@pytest.mark.parametrize("mode", ["kernels", "kernels_nvls"])
+def test_ddp_peer_fused_all_gpus(mode):
+    """The same end-to-end comparison on every GPU of the box (4 or 8 ranks): peer-load one-shot / two-shot kernels, and every
+    bucket reduced and updated inside the switch (multimem.ld_reduce / multimem.st)."""
+    _spawn(_w_ddp, min(8, torch.cuda.device_count()), mode)
+
+
 # ------------------------------------------------------------------------------------------------ single-process DP
 def test_dp_collectives_two_devices():
     from distributed_model_parallel_b200.parallel import comm
