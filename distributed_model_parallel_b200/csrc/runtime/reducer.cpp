@@ -207,7 +207,8 @@ struct DmpLaunchFns {
                     int zero_grad, rt_stream stream);
 };
 
-enum { PLAN_CALLER = 0, PLAN_ALLREDUCE_FUSED = 1, PLAN_NVLS = 2, PLAN_NVLS_SGD = 3, PLAN_SGD_FLAT = 4, PLAN_NONE = 5 };
+enum { PLAN_CALLER = 0, PLAN_ALLREDUCE_FUSED = 1, PLAN_NVLS = 2, PLAN_NVLS_SGD = 3, PLAN_SGD_FLAT = 4, PLAN_NONE = 5,
+       PLAN_NVLS_THEN_SGD = 6 };  // switch-side all-reduce, then the flat SGD kernel on this rank's copy (large buckets)
 
 struct DmpBucketPlan {
     int kind;
@@ -253,9 +254,10 @@ RT_API int dmp_reducer_set_plans(void* h, const DmpLaunchFns* fns, const DmpBuck
     e.native = true;
     for (const auto& p : e.plans) {
         if (p.kind == PLAN_CALLER) e.native = false;
-        if (p.kind < PLAN_CALLER || p.kind > PLAN_NONE) return -2;
+        if (p.kind < PLAN_CALLER || p.kind > PLAN_NVLS_THEN_SGD) return -2;
         if ((p.kind == PLAN_ALLREDUCE_FUSED && !fns->allreduce_fused) || (p.kind == PLAN_NVLS && !fns->allreduce_nvls) ||
-            (p.kind == PLAN_NVLS_SGD && !fns->allreduce_nvls_sgd) || (p.kind == PLAN_SGD_FLAT && !fns->sgd_flat))
+            (p.kind == PLAN_NVLS_SGD && !fns->allreduce_nvls_sgd) || (p.kind == PLAN_SGD_FLAT && !fns->sgd_flat) ||
+            (p.kind == PLAN_NVLS_THEN_SGD && (!fns->allreduce_nvls || !fns->sgd_flat)))
             return -3;
     }
     if (e.native && (!fns->fork || !fns->join)) return -3;
@@ -294,6 +296,13 @@ static int launch_plan(Engine* e, const DmpBucketPlan& p, rt_stream cur) {
             break;
         case PLAN_SGD_FLAT:
             rc = e->fns.sgd_flat(p.master, p.shadow, p.grad, p.dtype, p.momentum, p.numel, p.hp, p.nesterov, 1, e->comm);
+            break;
+        case PLAN_NVLS_THEN_SGD:
+            rc = e->fns.allreduce_nvls(p.mc_grad, p.state, p.rank, p.world, p.numel, p.scale, p.max_blocks, e->comm);
+            if (rc == 0) {
+                e->native_launches++;
+                rc = e->fns.sgd_flat(p.master, p.shadow, p.grad, p.dtype, p.momentum, p.numel, p.hp, p.nesterov, 1, e->comm);
+            }
             break;
         default:
             rc = -20;

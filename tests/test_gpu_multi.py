@@ -315,9 +315,11 @@ def _w_ddp(rank, world, port, mode):
 
     torch.manual_seed(0)
     use_graph = mode == "graph"
-    if mode == "kernels_nvls":  # every bucket reduced and updated inside the switch (multimem.ld_reduce / multimem.st)
+    if mode in ("kernels_nvls", "kernels_nvls_split"):  # every bucket reduced inside the switch (multimem.ld_reduce / multimem.st)
         os.environ["DMP_DDP_NVLS_FUSED"] = "1"
         os.environ["DMP_DDP_NVLS_FUSED_MIN_BYTES"] = "0"
+        # single kernel that also updates and multicasts the parameters, or all-reduce followed by the flat SGD kernel
+        os.environ["DMP_DDP_NVLS_SPLIT_MIN_BYTES"] = "0" if mode == "kernels_nvls_split" else str(1 << 40)
     base = (MobileNetV2() if use_graph else _tiny_net()).cuda()
     sgd = dict(lr=0.05, momentum=0.9, weight_decay=1e-4)
     ctx = OF.use_reference_ops() if mode == "reference_ops" else contextlib.nullcontext()
@@ -353,10 +355,12 @@ def _w_ddp(rank, world, port, mode):
             mode, rel, losses[-1], len(ours.reducer.buckets), getattr(ours.backend, "nvls_fused_launches", None)), flush=True)
     if mode == "reference_ops":   # fp32 library ops: only the summation order of the all-reduce differs
         assert rel < 1e-2, rel
-    elif mode in ("kernels", "kernels_nvls"):  # bf16 kernels with fp32 atomics on both sides, small network
+    elif mode in ("kernels", "kernels_nvls", "kernels_nvls_split"):  # bf16 kernels with fp32 atomics on both sides, small network
         assert rel < 0.12, rel
         if mode == "kernels_nvls" and ours.backend.nvls_fused:  # (stays False where the platform has no multicast)
             assert ours.backend.nvls_fused_launches > 0 and all(bk.fused.nvls is not None for bk in ours.reducer.buckets)
+        if mode == "kernels_nvls_split" and ours.backend.nvls_fused:
+            assert ours.backend.nvls_split_launches > 0 and ours.backend.nvls_fused_launches == 0
     else:
         # full MobileNetV2, captured step against the eager torch-DDP twin: one bf16 gradient of this network has a cosine of
         # ~0.96 with its fp32 value (tests/test_gpu_models.py), i.e. two bf16 evaluations differ by up to ~0.3 of their norm
@@ -371,13 +375,13 @@ def _w_ddp(rank, world, port, mode):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("mode", ["reference_ops", "kernels", "kernels_nvls", "graph"])
+@pytest.mark.parametrize("mode", ["reference_ops", "kernels", "kernels_nvls", "kernels_nvls_split", "graph"])
 def test_ddp_peer_fused_end_to_end(mode):
     _spawn(_w_ddp, 2, mode)
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4+ GPUs")
-@pytest.mark.parametrize("mode", ["kernels", "kernels_nvls"])
+@pytest.mark.parametrize("mode", ["kernels", "kernels_nvls", "kernels_nvls_split"])
 def test_ddp_peer_fused_all_gpus(mode):
     """The same end-to-end comparison on every GPU of the box (4 or 8 ranks): peer-load one-shot / two-shot kernels, and every
     bucket reduced and updated inside the switch (multimem.ld_reduce / multimem.st)."""
