@@ -398,17 +398,36 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T*
     const double inv_count = 1.0 / count;
     float sc[VEC], sh[VEC];
     bool odd = false;  // folds every loaded sum into the barrier predicate below
+    extern __shared__ float s_coef[];  // [2][C] scale / shift when the launch provides it (C <= BN_APPLY_SMEM_MAX_C)
+    const bool coop = (relu & 8) != 0;
+    if (coop) {
+        // The block derives each channel's coefficients ONCE (C / 256 channels per thread) and its threads pick theirs out of
+        // shared memory; every thread doing its own 8 channels repeated the same 16 dependent fp64 operations 256 times per
+        // block and was the longest part of a launch on the small layers.
+        for (int c = threadIdx.x; c < C; c += BN_THREADS) {
+            const double m = sums[c] * inv_count;
+            double var = sums[C + c] * inv_count - m * m;
+            if (var < 0.0) var = 0.0;
+            const float is = 1.0f / sqrtf((float)var + eps);
+            const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+            const float scv = g * is, shv = b - (float)m * g * is;
+            s_coef[c] = scv;
+            s_coef[C + c] = shv;
+            odd |= !(scv == scv) && !(shv == shv) && (scv == shv);  // never true; depends on both loads
+        }
+    } else {
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) {
-        const int c = ch0 + j;
-        const double m = sums[c] * inv_count;
-        double var = sums[C + c] * inv_count - m * m;
-        if (var < 0.0) var = 0.0;
-        const float is = 1.0f / sqrtf((float)var + eps);
-        const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
-        sc[j] = g * is;
-        sh[j] = b - (float)m * g * is;
-        odd |= !(sc[j] == sc[j]) && !(sh[j] == sh[j]) && (sc[j] == sh[j]);  // never true; depends on both loads
+        for (int j = 0; j < VEC; ++j) {
+            const int c = ch0 + j;
+            const double m = sums[c] * inv_count;
+            double var = sums[C + c] * inv_count - m * m;
+            if (var < 0.0) var = 0.0;
+            const float is = 1.0f / sqrtf((float)var + eps);
+            const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+            sc[j] = g * is;
+            sh[j] = b - (float)m * g * is;
+            odd |= !(sc[j] == sc[j]) && !(sh[j] == sh[j]) && (sc[j] == sh[j]);  // never true; depends on both loads
+        }
     }
     // One channel per thread over the first ceil(C / BN_THREADS) blocks publishes mean / invstd / running statistics (a single
     // block looping over C channels of double divisions and square roots was the slowest block of every launch).
@@ -432,6 +451,13 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T*
     // predicate forces that use), so the ticket needs no memory fence: the last block to take one clears the buffer for the
     // producer's next accumulation (CUDA-graph replay included), and a cleared value can no longer reach any thread.
     const int any_odd = __syncthreads_or(odd ? 1 : 0);
+    if (coop) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            sc[j] = s_coef[ch0 + j];
+            sh[j] = s_coef[C + ch0 + j];
+        }
+    }
     if (threadIdx.x == 0) {
         int* ticket = (int*)(sums + 2 * (long long)C);
         s_last = (atomicAdd(ticket, 1 + any_odd) == (int)gridDim.x - 1);
@@ -462,7 +488,7 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T*
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) f[j] += r[j];
                 }
-                if (relu) {
+                if (relu & 1) {
 #pragma unroll
                     for (int j = 0; j < VEC; ++j) f[j] = fmaxf(f[j], 0.f);
                 }
@@ -472,7 +498,7 @@ bn_apply_sums_kernel(const T* __restrict__ x, const T* __restrict__ residual, T*
 }
 
 template <typename T>
-__global__ void __launch_bounds__(BN_THREADS)
+__global__ void __launch_bounds__(BN_THREADS, 2)  // two blocks per SM: at 148 registers (one block) the whole step lost 8 %
 bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta, double count,
                     T* __restrict__ dx, T* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta,
@@ -558,13 +584,19 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
                 s2 += accum[(long long)k * 2 * C + C + ch];
             }
             const float db = (float)s1, dg = (float)s2;
-            if (dgamma) dgamma[ch] = accumulate_params ? dgamma[ch] + dg : dg;
-            if (dbeta) dbeta[ch] = accumulate_params ? dbeta[ch] + db : db;
+            if (dgamma) dgamma[ch] = (accumulate_params & 1) ? dgamma[ch] + dg : dg;
+            if (dbeta) dbeta[ch] = (accumulate_params & 1) ? dbeta[ch] + db : db;
         }
         if (threadIdx.x == 0) *parity_p = parity ^ 1;
     }
     for (long long i = tid; i < 2 * (long long)NSETS * C; i += stride) other[i] = 0.0;
-    for (long long v0 = tid; v0 < nvec; v0 += U * stride) {
+    // second pass in REVERSE order: the tail of the first pass is what the L2 still holds (tensors larger than the L2 would
+    // otherwise be evicted just ahead of their re-use, front to back)
+    const long long n_iter = (nvec - tid + U * stride - 1) / (U * stride);
+    const bool reverse = (accumulate_params & 2) != 0;
+    for (long long k = 0; k < n_iter; ++k) {
+        const long long it = reverse ? n_iter - 1 - k : k;
+        const long long v0 = tid + it * (U * stride);
         int4 rg[U], rx[U], ry[U];
 #pragma unroll
         for (int u = 0; u < U; ++u)
@@ -1058,14 +1090,17 @@ DMP_API int dmp_bn_apply_sums(const void* x, int dtype, const void* residual, vo
     const long long nvec = M * C / vec;
     // no reduction at the end of a block here, so thin blocks: 4 vectors per thread are one batch of loads in flight
     const int grid = bn_grid(nvec, C, vec, 4);
+    // bit 0: ReLU; bit 3: coefficients derived once per block into shared memory (2*C floats, C <= 4096)
+    const int flags = (relu ? 1 : 0) | (C <= 4096 ? 8 : 0);
+    const size_t smem = C <= 4096 ? (size_t)2 * C * sizeof(float) : 0;
     if (dtype == 1)
-        bn_apply_sums_kernel<bf16><<<grid, BN_THREADS, 0, stream>>>((const bf16*)x, (const bf16*)residual, (bf16*)y, nvec, C, (double)M,
-                                                                    gamma, beta, running_mean, running_var, num_batches_tracked,
-                                                                    momentum, eps, mean, invstd, sums, relu);
+        bn_apply_sums_kernel<bf16><<<grid, BN_THREADS, smem, stream>>>((const bf16*)x, (const bf16*)residual, (bf16*)y, nvec, C, (double)M,
+                                                                       gamma, beta, running_mean, running_var, num_batches_tracked,
+                                                                       momentum, eps, mean, invstd, sums, flags);
     else
-        bn_apply_sums_kernel<float><<<grid, BN_THREADS, 0, stream>>>((const float*)x, (const float*)residual, (float*)y, nvec, C, (double)M,
-                                                                     gamma, beta, running_mean, running_var, num_batches_tracked,
-                                                                     momentum, eps, mean, invstd, sums, relu);
+        bn_apply_sums_kernel<float><<<grid, BN_THREADS, smem, stream>>>((const float*)x, (const float*)residual, (float*)y, nvec, C, (double)M,
+                                                                        gamma, beta, running_mean, running_var, num_batches_tracked,
+                                                                        momentum, eps, mean, invstd, sums, flags);
     DMP_LAUNCH_CHECK();
     DMP_COUNT_LAUNCH(1);
     return 0;
@@ -1114,6 +1149,10 @@ DMP_API int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int d
         }
         const int grid = bn_coop_grid(bn_bwd_fused_kernel<bf16>, nvec, C, vec, smem);
         if (grid < 0) return 1;
+        // the second pass walks backwards when dy + x exceed what the 126 MB L2 keeps of the first pass (DMP_BN_BWD_REVERSE_MB,
+        // default 64; 0 = never)
+        static const long long rev_mb = [] { const char* e = getenv("DMP_BN_BWD_REVERSE_MB"); return e ? atoll(e) : 64ll; }();
+        if (rev_mb > 0 && nvec * 32 > (rev_mb << 20)) accumulate_params |= 2;
         DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_fused_kernel<bf16>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
     } else {
         const int grid = bn_coop_grid(bn_bwd_fused_kernel<float>, nvec, C, vec, smem);
