@@ -414,6 +414,158 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
     if (BNIN == 1) dw_bn_publish_and_release(aux, C);  // this block read its coefficients long ago: the ticket goes last
 }
 
+// Branch-free strip stencil (forward, and the stride-1 data gradient with FLIP): the default path of the training step.
+// What the kernel above does under branches -- skip rows and columns that fall into the padding -- this one does with clamped
+// addresses and a select: all 3 x NC input vectors of a strip are fetched by independent loads issued back to back (the
+// compiler cannot hoist a load out of the branch that guards it, so the branchy version paid up to 18 L2 round trips one after
+// the other), the 9 x C weights are staged once per block in shared memory as fp32 [tap][C] (72 registers per thread in the
+// version above, which spilled), and all index arithmetic is 32-bit (the 64-bit divisions were function calls).
+// Shared memory: max(9 * C floats, the statistics scratch) -- the scratch reuses the weight area once the taps are consumed.
+constexpr int DW_STAT_SCRATCH_BYTES = DW_THREADS * 17 * 4 + DW_THREADS * 4;
+
+template <typename WT, int STRIDE, int TW, bool FLIP, bool STATS>
+__global__ void __launch_bounds__(DW_THREADS, 2)
+dw_strip_bf_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
+                   int Ho, int Wo, double* __restrict__ stats) {
+    constexpr int NC = (TW - 1) * STRIDE + 3;
+    extern __shared__ __align__(16) float dw_smem[];
+    float* s_w = dw_smem;  // [9][C]
+    for (int i = threadIdx.x; i < 9 * C; i += DW_THREADS) {
+        const int c = i / 9, tap = i - c * 9;
+        s_w[(FLIP ? 8 - tap : tap) * C + c] = to_f32<WT>(w[i]);
+    }
+    const unsigned P = (unsigned)C >> 3;
+    const unsigned tiles_w = (unsigned)(Wo + TW - 1) / TW;
+    const unsigned idx = blockIdx.x * (unsigned)DW_THREADS + threadIdx.x;
+    const unsigned total = (unsigned)N * Ho * tiles_w * P;  // < 2^31, checked by the host
+    const bool active = idx < total;
+    const unsigned cidx = active ? idx : 0u;
+    const unsigned cv = cidx % P;
+    unsigned t = cidx / P;
+    const int wt_ = (int)(t % tiles_w); t /= tiles_w;
+    const int ho = (int)(t % (unsigned)Ho);
+    const int n = (int)(t / (unsigned)Ho);
+    const int ch0 = (int)cv * 8;
+    const int wo0 = wt_ * TW;
+    const int wi0 = wo0 * STRIDE - 1;
+    int4 raw[3][NC];
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+        const int hi = ho * STRIDE + kh - 1;
+        const bool okh = (unsigned)hi < (unsigned)H;
+        const bf16* row = x + ((size_t)((size_t)n * H + min(max(hi, 0), H - 1)) * W) * C + ch0;
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            const int wi = wi0 + c;
+            const bool ok = okh && (unsigned)wi < (unsigned)W;
+            int4 v = *(const int4*)(row + (size_t)min(max(wi, 0), W - 1) * C);
+            if (!ok) v = make_int4(0, 0, 0, 0);
+            raw[kh][c] = v;
+        }
+    }
+    __syncthreads();  // weights staged
+    float acc[TW][8];
+#pragma unroll
+    for (int i = 0; i < TW; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+#pragma unroll
+    for (int kh = 0; kh < 3; ++kh) {
+        float wk[3][8];
+#pragma unroll
+        for (int kw = 0; kw < 3; ++kw) {
+            const float4 a = *(const float4*)(s_w + (kh * 3 + kw) * C + ch0), b = *(const float4*)(s_w + (kh * 3 + kw) * C + ch0 + 4);
+            wk[kw][0] = a.x; wk[kw][1] = a.y; wk[kw][2] = a.z; wk[kw][3] = a.w;
+            wk[kw][4] = b.x; wk[kw][5] = b.y; wk[kw][6] = b.z; wk[kw][7] = b.w;
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+            float v[8];
+            bf16x8_to_float(*(const bf16x8*)&raw[kh][c], v);
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                // input column c feeds output i with i * STRIDE + kw == c
+                if ((c - kw) >= 0 && (c - kw) % STRIDE == 0 && (c - kw) / STRIDE < TW) {
+                    const int i = (c - kw) / STRIDE;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[i][j] += v[j] * wk[kw][j];
+                }
+            }
+        }
+    }
+    float st[STATS ? 16 : 1];
+    if (STATS) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) st[i] = 0.f;
+    }
+    if (active) {
+#pragma unroll
+        for (int i = 0; i < TW; ++i)
+            if (wo0 + i < Wo) {
+                store8(y + (((size_t)n * Ho + ho) * Wo + wo0 + i) * C + ch0, acc[i]);
+                if (STATS) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const float q = __bfloat162float(__float2bfloat16_rn(acc[i][j]));
+                        st[j] += q;
+                        st[8 + j] += q * q;
+                    }
+                }
+            }
+    }
+    if (STATS) {
+        __syncthreads();  // every thread is done with the staged weights: the scratch below overlays them
+        float* s_part = dw_smem;                              // [DW_THREADS][17]
+        int* s_ch0 = (int*)(dw_smem + DW_THREADS * 17);       // [DW_THREADS]
+#pragma unroll
+        for (int i = 0; i < 16; ++i) s_part[threadIdx.x * 17 + i] = st[i];
+        s_ch0[threadIdx.x] = ch0;
+        __syncthreads();
+        const int Pi = (int)P;
+        const int ngroups = Pi < DW_THREADS ? Pi : DW_THREADS;
+        for (int item = threadIdx.x; item < ngroups * 16; item += DW_THREADS) {
+            const int g = item >> 4, i = item & 15;
+            float sacc = 0.f;
+            for (int tt = g; tt < DW_THREADS; tt += Pi) sacc += s_part[tt * 17 + i];
+            atomicAdd(&stats[(long long)(i >> 3) * C + s_ch0[g] + (i & 7)], (double)sacc);
+        }
+    }
+}
+
+// Launches dw_strip_bf_kernel when the problem fits its limits (weights <= 64 KB of shared memory, < 2^31 threads); returns
+// false when the caller should use the general kernel.
+template <bool FLIP, bool STATS>
+static bool launch_dw_strip_bf(const void* x, const void* w, int w_dtype, void* y, int N, int H, int W, int C, int Ho, int Wo,
+                               int stride, double* stats, cudaStream_t stream, int* rc_out) {
+    static const bool enabled = [] { const char* e = getenv("DMP_DW_BRANCHFREE"); return e == nullptr || e[0] != '0'; }();
+    *rc_out = 0;
+    if (!enabled) return false;
+    size_t smem = (size_t)9 * C * sizeof(float);
+    if (STATS && smem < (size_t)DW_STAT_SCRATCH_BYTES) smem = DW_STAT_SCRATCH_BYTES;
+    const int TW = stride == 1 ? 4 : 2;
+    const long long total = (long long)N * Ho * ((Wo + TW - 1) / TW) * (C / 8);
+    if (smem > 64 * 1024 || total >= (1ll << 31) || (stride != 1 && stride != 2)) return false;
+    const int grid = dmp_ceil_div(total, DW_THREADS);
+#define DW_BF_LAUNCH(WT, S, T)                                                                                                   \
+    do {                                                                                                                         \
+        auto kern = dw_strip_bf_kernel<WT, S, T, FLIP, STATS>;                                                                   \
+        if (smem > 48 * 1024) {                                                                                                  \
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);                  \
+            if (e != cudaSuccess) { dmp_set_error("dw_strip_bf: cudaFuncSetAttribute -> %s", cudaGetErrorString(e)); *rc_out = (int)e; return true; } \
+        }                                                                                                                        \
+        kern<<<grid, DW_THREADS, smem, stream>>>((const bf16*)x, (const WT*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);             \
+    } while (0)
+    if (stride == 1) {
+        if (w_dtype == 0) DW_BF_LAUNCH(float, 1, 4); else DW_BF_LAUNCH(bf16, 1, 4);
+    } else {
+        if (w_dtype == 0) DW_BF_LAUNCH(float, 2, 2); else DW_BF_LAUNCH(bf16, 2, 2);
+    }
+#undef DW_BF_LAUNCH
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) { dmp_set_error("dw_strip_bf launch -> %s", cudaGetErrorString(e)); *rc_out = (int)e; }
+    return true;
+}
+
 // Strip version of the weight gradient.  A warp owns TWO adjacent channel vectors (lane & 1) and its 16 lane pairs walk
 // 16 different (n, ho, strip) work items at a time, so a lane pair reads 32 contiguous bytes (one full sector) and all
 // partial sums that must be combined live in the same warp: 4 xor-shuffle rounds fold the 16 items, then lanes 0/1 issue
@@ -592,6 +744,13 @@ DMP_API int dmp_dwconv3x3_fwd(const void* x, const void* w, int w_dtype, void* y
                               cudaStream_t stream) {
     if (int rc = dw_check("dmp_dwconv3x3_fwd", N, H, W, C, stride)) return rc;
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    {
+        int rc = 0;
+        if (launch_dw_strip_bf<false, false>(x, w, w_dtype, y, N, H, W, C, Ho, Wo, stride, nullptr, stream, &rc)) {
+            if (rc == 0) DMP_COUNT_LAUNCH(1);
+            return rc;
+        }
+    }
     if (stride == 1) {
         const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
@@ -615,6 +774,13 @@ DMP_API int dmp_dwconv3x3_fwd_colstats(const void* x, const void* w, int w_dtype
     if (int rc = dw_check("dmp_dwconv3x3_fwd_colstats", N, H, W, C, stride)) return rc;
     DMP_REQUIRE(stats != nullptr, "dmp_dwconv3x3_fwd_colstats: null stats");
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
+    {
+        int rc = 0;
+        if (launch_dw_strip_bf<false, true>(x, w, w_dtype, y, N, H, W, C, Ho, Wo, stride, stats, stream, &rc)) {
+            if (rc == 0) DMP_COUNT_LAUNCH(1);
+            return rc;
+        }
+    }
     if (stride == 1) {
         const long long total = (long long)N * Ho * ((Wo + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
@@ -636,6 +802,11 @@ DMP_API int dmp_dwconv3x3_dgrad(const void* dy, const void* w, int w_dtype, void
     if (int rc = dw_check("dmp_dwconv3x3_dgrad", N, H, W, C, stride)) return rc;
     const int Ho = (H + 2 - 3) / stride + 1, Wo = (W + 2 - 3) / stride + 1;
     if (stride == 1) {  // dx = dy (*) flipped taps: the forward strip stencil applied to dy (Ho == H, Wo == W)
+        int rc = 0;
+        if (launch_dw_strip_bf<true, false>(dy, w, w_dtype, dx, N, H, W, C, H, W, 1, nullptr, stream, &rc)) {
+            if (rc == 0) DMP_COUNT_LAUNCH(1);
+            return rc;
+        }
         const long long total = (long long)N * H * ((W + 3) / 4) * (C / 8);
         const int grid = dmp_ceil_div(total, DW_THREADS);
         if (w_dtype == 0) dw_strip_kernel<float, 1, 4, true, false><<<grid, DW_THREADS, 0, stream>>>((const bf16*)dy, (const float*)w, (bf16*)dx, N, H, W, C, H, W, nullptr, DwBn{});
