@@ -418,30 +418,39 @@ dw_strip_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __re
 // What the kernel above does under branches -- skip rows and columns that fall into the padding -- this one does with clamped
 // addresses and a select: all 3 x NC input vectors of a strip are fetched by independent loads issued back to back (the
 // compiler cannot hoist a load out of the branch that guards it, so the branchy version paid up to 18 L2 round trips one after
-// the other), the 9 x C weights are staged once per block in shared memory as fp32 [tap][C] (72 registers per thread in the
-// version above, which spilled), and all index arithmetic is 32-bit (the 64-bit divisions were function calls).
-// Shared memory: max(9 * C floats, the statistics scratch) -- the scratch reuses the weight area once the taps are consumed.
-constexpr int DW_STAT_SCRATCH_BYTES = DW_THREADS * 17 * 4 + DW_THREADS * 4;
+// the other), the taps of the block's own channels are staged once per block in shared memory as fp32 (72 registers per thread
+// in the version above, which spilled), and all index arithmetic is 32-bit (the 64-bit divisions were function calls).
+// Shared memory: the taps of the block's channels, overlaid by the statistics scratch once they are consumed.
+constexpr int DW_STAT_SCRATCH_BYTES = DW_THREADS * 17 * 4;
 
 template <typename WT, int STRIDE, int TW, bool FLIP, bool STATS>
 __global__ void __launch_bounds__(DW_THREADS, 2)
 dw_strip_bf_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* __restrict__ y, int N, int H, int W, int C,
-                   int Ho, int Wo, double* __restrict__ stats) {
+                   int Ho, int Wo, double* __restrict__ stats, int cvb) {
     constexpr int NC = (TW - 1) * STRIDE + 3;
     extern __shared__ __align__(16) float dw_smem[];
-    float* s_w = dw_smem;  // [9][C]
-    for (int i = threadIdx.x; i < 9 * C; i += DW_THREADS) {
-        const int c = i / 9, tap = i - c * 9;
-        s_w[(FLIP ? 8 - tap : tap) * C + c] = to_f32<WT>(w[i]);
+    float* s_w = dw_smem;  // [9][CB]: the taps of this block's CB = 8 * cvb channels
+    const int CB = cvb * 8;
+    {
+        const int cbase = (int)(blockIdx.x % (((unsigned)C >> 3) / (unsigned)cvb)) * CB;
+        for (int i = threadIdx.x; i < 9 * CB; i += DW_THREADS) {
+            const int c = i / 9, tap = i - c * 9;
+            s_w[(FLIP ? 8 - tap : tap) * CB + c] = to_f32<WT>(w[(size_t)cbase * 9 + i]);
+        }
     }
+    // A block owns `cvb` adjacent channel vectors (cvb divides C/8, at most 8: 128 contiguous bytes per pixel) and
+    // DW_THREADS / cvb strips.  With the channel vector as the fastest index over ALL of C (the general kernel's mapping) every
+    // block touches every channel and ends with 2*C atomics on the same 2*C addresses as every other block; here a block adds
+    // 16 * cvb values and a channel's accumulator is shared by 1 / (C/8/cvb) of the blocks.
     const unsigned P = (unsigned)C >> 3;
     const unsigned tiles_w = (unsigned)(Wo + TW - 1) / TW;
-    const unsigned idx = blockIdx.x * (unsigned)DW_THREADS + threadIdx.x;
-    const unsigned total = (unsigned)N * Ho * tiles_w * P;  // < 2^31, checked by the host
-    const bool active = idx < total;
-    const unsigned cidx = active ? idx : 0u;
-    const unsigned cv = cidx % P;
-    unsigned t = cidx / P;
+    const unsigned nstrips = (unsigned)N * Ho * tiles_w;  // < 2^31, checked by the host
+    const unsigned ucvb = (unsigned)cvb, spb = (unsigned)DW_THREADS / ucvb, cvgroups = P / ucvb;
+    const unsigned cvl = threadIdx.x % ucvb, sl = threadIdx.x / ucvb;
+    const unsigned strip = (blockIdx.x / cvgroups) * spb + sl;
+    const bool active = sl < spb && strip < nstrips;
+    const unsigned cv = (blockIdx.x % cvgroups) * ucvb + cvl;
+    unsigned t = active ? strip : 0u;
     const int wt_ = (int)(t % tiles_w); t /= tiles_w;
     const int ho = (int)(t % (unsigned)Ho);
     const int n = (int)(t / (unsigned)Ho);
@@ -474,7 +483,8 @@ dw_strip_bf_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* _
         float wk[3][8];
 #pragma unroll
         for (int kw = 0; kw < 3; ++kw) {
-            const float4 a = *(const float4*)(s_w + (kh * 3 + kw) * C + ch0), b = *(const float4*)(s_w + (kh * 3 + kw) * C + ch0 + 4);
+            const float* wp = s_w + (kh * 3 + kw) * CB + (int)cvl * 8;
+            const float4 a = *(const float4*)wp, b = *(const float4*)(wp + 4);
             wk[kw][0] = a.x; wk[kw][1] = a.y; wk[kw][2] = a.z; wk[kw][3] = a.w;
             wk[kw][4] = b.x; wk[kw][5] = b.y; wk[kw][6] = b.z; wk[kw][7] = b.w;
         }
@@ -516,18 +526,15 @@ dw_strip_bf_kernel(const bf16* __restrict__ x, const WT* __restrict__ w, bf16* _
     if (STATS) {
         __syncthreads();  // every thread is done with the staged weights: the scratch below overlays them
         float* s_part = dw_smem;                              // [DW_THREADS][17]
-        int* s_ch0 = (int*)(dw_smem + DW_THREADS * 17);       // [DW_THREADS]
 #pragma unroll
-        for (int i = 0; i < 16; ++i) s_part[threadIdx.x * 17 + i] = st[i];
-        s_ch0[threadIdx.x] = ch0;
+        for (int i = 0; i < 16; ++i) s_part[threadIdx.x * 17 + i] = st[i];  // idle threads hold zeros
         __syncthreads();
-        const int Pi = (int)P;
-        const int ngroups = Pi < DW_THREADS ? Pi : DW_THREADS;
-        for (int item = threadIdx.x; item < ngroups * 16; item += DW_THREADS) {
+        const int cvg0 = (int)((blockIdx.x % cvgroups) * ucvb) * 8;   // first channel of this block
+        for (int item = threadIdx.x; item < cvb * 16; item += DW_THREADS) {
             const int g = item >> 4, i = item & 15;
             float sacc = 0.f;
-            for (int tt = g; tt < DW_THREADS; tt += Pi) sacc += s_part[tt * 17 + i];
-            atomicAdd(&stats[(long long)(i >> 3) * C + s_ch0[g] + (i & 7)], (double)sacc);
+            for (unsigned q = 0; q < spb; ++q) sacc += s_part[(q * ucvb + g) * 17 + i];
+            atomicAdd(&stats[(long long)(i >> 3) * C + cvg0 + g * 8 + (i & 7)], (double)sacc);
         }
     }
 }
@@ -540,12 +547,18 @@ static bool launch_dw_strip_bf(const void* x, const void* w, int w_dtype, void* 
     static const bool enabled = [] { const char* e = getenv("DMP_DW_BRANCHFREE"); return e == nullptr || e[0] != '0'; }();
     *rc_out = 0;
     if (!enabled) return false;
-    size_t smem = (size_t)9 * C * sizeof(float);
+    size_t smem = (size_t)9 * 64 * sizeof(float);  // the taps of at most 8 channel vectors
     if (STATS && smem < (size_t)DW_STAT_SCRATCH_BYTES) smem = DW_STAT_SCRATCH_BYTES;
     const int TW = stride == 1 ? 4 : 2;
-    const long long total = (long long)N * Ho * ((Wo + TW - 1) / TW) * (C / 8);
-    if (smem > 64 * 1024 || total >= (1ll << 31) || (stride != 1 && stride != 2)) return false;
-    const int grid = dmp_ceil_div(total, DW_THREADS);
+    const long long nstrips = (long long)N * Ho * ((Wo + TW - 1) / TW);
+    if (smem > 64 * 1024 || nstrips >= (1ll << 31) || (stride != 1 && stride != 2)) return false;
+    const int P = C / 8;
+    int cvb = 8;
+    while (cvb > 1 && P % cvb != 0) --cvb;  // largest divisor of C/8 up to 8
+    const int spb = DW_THREADS / cvb;
+    const long long grid_ll = ((nstrips + spb - 1) / spb) * (P / cvb);
+    if (grid_ll >= (1ll << 31)) return false;
+    const int grid = (int)grid_ll;
 #define DW_BF_LAUNCH(WT, S, T)                                                                                                   \
     do {                                                                                                                         \
         auto kern = dw_strip_bf_kernel<WT, S, T, FLIP, STATS>;                                                                   \
@@ -553,7 +566,7 @@ static bool launch_dw_strip_bf(const void* x, const void* w, int w_dtype, void* 
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);                  \
             if (e != cudaSuccess) { dmp_set_error("dw_strip_bf: cudaFuncSetAttribute -> %s", cudaGetErrorString(e)); *rc_out = (int)e; return true; } \
         }                                                                                                                        \
-        kern<<<grid, DW_THREADS, smem, stream>>>((const bf16*)x, (const WT*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats);             \
+        kern<<<grid, DW_THREADS, smem, stream>>>((const bf16*)x, (const WT*)w, (bf16*)y, N, H, W, C, Ho, Wo, stats, cvb);        \
     } while (0)
     if (stride == 1) {
         if (w_dtype == 0) DW_BF_LAUNCH(float, 1, 4); else DW_BF_LAUNCH(bf16, 1, 4);
