@@ -563,6 +563,19 @@ int wgrad_max_ctas() {
     return v;
 }
 
+// DMP_GEMM_SMALLK_BN64: largest K for which forward / data-gradient GEMMs with N > 64 use 64-wide tiles (0 = never).
+// Measured (bench/chain_bench.py, MobileNetV2 shapes, B200): 131072 x 144 x 24 forward + statistics 40.0 -> 24.3 us,
+// 131072 x 96 x 16 21.0 -> 15.1, 32768 x 192 x 32 13.6 -> 8.4; whole step 3.67 -> 3.53 ms with K <= 160 (no further gain beyond).
+int small_k_bn64_max_k() {
+    static const int v = [] { const char* e = getenv("DMP_GEMM_SMALLK_BN64"); return e ? atoi(e) : 160; }();
+    return v;
+}
+
+int small_k_bn64_min_m() {
+    static const int v = [] { const char* e = getenv("DMP_GEMM_SMALLK_MIN_M"); return e ? atoi(e) : 0; }();
+    return v;
+}
+
 // DMP_GEMM_CHAIN_MAX_SMS: SMs the forward / data-gradient GEMMs size their persistent grid for (0 = all).
 int chain_max_sms() {
     static const int v = [] { const char* e = getenv("DMP_GEMM_CHAIN_MAX_SMS"); return e ? atoi(e) : 0; }();
@@ -656,6 +669,8 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
     const bool b_mn = (layout != 0);
     int bn = N > 64 ? 128 : (N > 32 ? 64 : 32);
     if (b_mn && bn < 64) bn = 64;
+    // forward / data-gradient GEMMs with a short reduction: 64-wide tiles, two CTAs per SM (see dmp_gemm_bf16_colstats)
+    if (layout != 2 && out_mode == 0 && bn == 128 && K <= small_k_bn64_max_k() && M >= small_k_bn64_min_m()) bn = 64;
 
     CUtensorMap tmA, tmB;
     int rc;
@@ -707,7 +722,10 @@ DMP_API int dmp_gemm_bf16(int layout, const void* A, long long lda, const void* 
 DMP_API int dmp_gemm_bf16_colstats(const void* A, long long lda, const void* B, long long ldb, void* D, long long ldd, int M,
                                    int N, int K, double* stats, cudaStream_t stream) {
     DMP_REQUIRE(M > 0 && N > 0 && K > 0 && stats != nullptr, "dmp_gemm_bf16_colstats: bad arguments");
-    const int bn = N > 64 ? 128 : (N > 32 ? 64 : 32);
+    int bn = N > 64 ? 128 : (N > 32 ? 64 : 32);
+    // One K block (K <= 64) and many rows: the tile is all epilogue (TMEM -> registers -> staging -> TMA store, plus the column
+    // statistics), and a 128-wide tile keeps one CTA -- four epilogue warps -- per SM.  64-wide tiles run two CTAs per SM.
+    if (bn == 128 && K <= small_k_bn64_max_k() && M >= small_k_bn64_min_m()) bn = 64;
     CUtensorMap tmA, tmB;
     if (int rc = make_tmap_2d(&tmA, A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM)) return rc;
     if (int rc = make_tmap_2d(&tmB, B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)bn)) return rc;

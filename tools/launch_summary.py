@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Summarises an `ncu --metrics gpu__time_duration.sum[,dram__bytes_read.sum,dram__bytes_write.sum] --csv --log-file X`
-launch list: per-kernel count, total time, share and (when the DRAM counters were collected) bytes moved and GB/s.
+launch list: per-kernel count, total time, share and (when collected) DRAM bytes moved, GB/s, time-weighted SM throughput % of
+peak, active warps % of peak and tensor-pipe instructions (non-zero only for the tcgen05 kernels).
 
     python tools/launch_summary.py gpurun_out/launches.csv [--steps N] [--list] > profiles/launches_summary.txt
 
@@ -42,7 +43,7 @@ def main():
         lid = d.get("ID")
         if lid not in launches:
             launches[lid] = {"name": short(d["Kernel Name"]), "grid": d.get("Grid Size", ""), "block": d.get("Block Size", ""),
-                             "us": 0.0, "rd": 0.0, "wr": 0.0}
+                             "us": 0.0, "rd": 0.0, "wr": 0.0, "smpct": None, "tensor": 0.0, "warps": None}
             order.append(lid)
         m = d.get("Metric Name")
         try:
@@ -56,20 +57,31 @@ def main():
             launches[lid]["rd"] = v * BYTES.get(u, 1.0)
         elif m == "dram__bytes_write.sum":
             launches[lid]["wr"] = v * BYTES.get(u, 1.0)
+        elif m == "sm__throughput.avg.pct_of_peak_sustained_elapsed":
+            launches[lid]["smpct"] = v
+        elif m == "sm__inst_executed_pipe_tensor.sum":
+            launches[lid]["tensor"] = v
+        elif m == "sm__warps_active.avg.pct_of_peak_sustained_active":
+            launches[lid]["warps"] = v
     tot, cnt, byt = defaultdict(float), defaultdict(int), defaultdict(float)
+    smw, wrw, tens = defaultdict(float), defaultdict(float), defaultdict(float)
     for l in launches.values():
         tot[l["name"]] += l["us"]
         cnt[l["name"]] += 1
         byt[l["name"]] += l["rd"] + l["wr"]
+        smw[l["name"]] += (l["smpct"] or 0.0) * l["us"]   # time-weighted
+        wrw[l["name"]] += (l["warps"] or 0.0) * l["us"]
+        tens[l["name"]] += l["tensor"]
     total = sum(tot.values())
     n = sum(cnt.values())
     allb = sum(byt.values())
     print("# window: %d launches, %.1f us total (%d step(s): %.1f us and %.0f launches per step), DRAM %.1f MB per step" % (
         n, total, steps, total / max(steps, 1), n / max(steps, 1), allb / max(steps, 1) / 1e6))
-    print("%-78s %6s %10s %7s %9s %9s %8s" % ("kernel", "count", "total_us", "share", "us/launch", "DRAM_MB", "GB/s"))
+    print("%-70s %6s %10s %7s %9s %9s %8s %7s %8s %10s" % ("kernel", "count", "total_us", "share", "us/launch", "DRAM_MB", "GB/s", "SM%", "warps%", "tensor_ops"))
     for k in sorted(tot, key=lambda k: -tot[k]):
-        print("%-78s %6d %10.1f %6.1f%% %9.1f %9.1f %8.0f" % (k[:78], cnt[k], tot[k], 100.0 * tot[k] / max(total, 1e-9), tot[k] / cnt[k],
-                                                          byt[k] / 1e6, byt[k] / max(tot[k], 1e-9) / 1e3))
+        print("%-70s %6d %10.1f %6.1f%% %9.1f %9.1f %8.0f %7.1f %8.1f %10.0f" % (
+            k[:70], cnt[k], tot[k], 100.0 * tot[k] / max(total, 1e-9), tot[k] / cnt[k], byt[k] / 1e6, byt[k] / max(tot[k], 1e-9) / 1e3,
+            smw[k] / max(tot[k], 1e-9), wrw[k] / max(tot[k], 1e-9), tens[k]))
     if "--list" in sys.argv:
         print("\n# launches in issue order")
         for lid in order:
