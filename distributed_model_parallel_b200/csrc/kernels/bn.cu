@@ -78,6 +78,36 @@ __device__ void block_channel_reduce(const float* vals, int ch0, int C, double* 
     }
 }
 
+
+// Slab mapping of the cooperative BatchNorm kernels: a block owns `cvb` adjacent channel vectors (cvb divides C / VEC, at most 8:
+// 128 contiguous bytes of a row) and BN_THREADS / cvb rows per sweep; thread t has channel vector t % cvb and row t / cvb.  Every
+// block then contributes NSTAT * VEC * cvb values, to accumulators shared only with the blocks of the same slab -- with the
+// flat mapping (consecutive threads over the whole tensor) every block ended with NSTAT * C atomics on the same NSTAT * C
+// addresses as every other block.  vals[k*VEC + j]: k-th statistic of the thread's channel j.  sm: [BN_THREADS][NSTAT*VEC + 1].
+template <int VEC, int NSTAT>
+__device__ void block_slab_reduce(const float* vals, int cvb, int C, int slab_ch0, double* __restrict__ accum, float* sm) {
+    constexpr int W = NSTAT * VEC;
+    float* mine = sm + threadIdx.x * (W + 1);
+#pragma unroll
+    for (int i = 0; i < W; ++i) mine[i] = vals[i];  // threads without a row hold zeros
+    __syncthreads();
+    const int items = cvb * W;                      // <= 128
+    const int rpb = BN_THREADS / cvb;
+    int T = 1;                                      // threads per item: a power of two, item-major so partners are adjacent lanes
+    while (T * 2 * items <= BN_THREADS && T < 32) T *= 2;
+    const int item = threadIdx.x / T, k = threadIdx.x % T;
+    float s = 0.f;
+    if (item < items) {
+        const int g = item / W, i = item % W;
+        for (int q = k; q < rpb; q += T) s += sm[(q * cvb + g) * (W + 1) + i];
+    }
+    for (int o = T >> 1; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (item < items && k == 0) {
+        const int g = item / W, i = item % W;
+        atomicAdd(&accum[(long long)(i / VEC) * C + slab_ch0 + g * VEC + (i % VEC)], (double)s);
+    }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(BN_THREADS)
 bn_stats_kernel(const T* __restrict__ x, long long nvec, int C, double* __restrict__ accum) {
@@ -502,7 +532,7 @@ __global__ void __launch_bounds__(BN_THREADS, 2)  // two blocks per SM: at 148 r
 bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* __restrict__ x, const float* __restrict__ mean,
                     const float* __restrict__ invstd, const float* __restrict__ gamma, const float* __restrict__ beta, double count,
                     T* __restrict__ dx, T* __restrict__ dres, float* __restrict__ dgamma, float* __restrict__ dbeta,
-                    int accumulate_params, long long nvec, int C, int relu, double* __restrict__ ws) {
+                    int accumulate_params, long long nvec, int C, int relu, double* __restrict__ ws, int cvb) {
     constexpr int VEC = Vec<T>::N;
     constexpr int U = 4;
     extern __shared__ float sm[];
@@ -511,9 +541,16 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
     const int parity = *parity_p;
     double* accum = ws + (long long)parity * 2 * NSETS * C;
     double* other = ws + (long long)(parity ^ 1) * 2 * NSETS * C;
-    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
-    const long long stride = (long long)gridDim.x * BN_THREADS;
-    const int ch0 = (int)((tid * VEC) % C);
+    // slab mapping (see block_slab_reduce): this thread's vectors are vfirst, vfirst + stride, ... (all of one channel vector)
+    const long long gtid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long gstride = (long long)gridDim.x * BN_THREADS;
+    const int P = C / VEC, cvgroups = P / cvb, rpb = BN_THREADS / cvb;
+    const int cvl = threadIdx.x % cvb, rl = threadIdx.x / cvb;
+    const int cv = (blockIdx.x % cvgroups) * cvb + cvl;
+    const int row_blocks = gridDim.x / cvgroups;
+    const long long stride = (long long)row_blocks * rpb * P;
+    const long long tid = rl < rpb ? ((long long)(blockIdx.x / cvgroups) * rpb + rl) * P + cv : nvec;  // no row: nothing to do
+    const int ch0 = cv * VEC;
     // ReLU mask: from the saved output when given, otherwise recomputed from x (y = relu(xhat*gamma + beta) without a
     // residual), which saves reading a third tensor in both passes
     const bool mask_from_x = relu && (y == nullptr);
@@ -560,7 +597,7 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
                 }
             }
     }
-    block_channel_reduce<VEC, 2>(acc, ch0, C, accum + (long long)(blockIdx.x % NSETS) * 2 * C, sm);
+    block_slab_reduce<VEC, 2>(acc, cvb, C, (int)(blockIdx.x % cvgroups) * cvb * VEC, accum, sm);
     grid.sync();
     const double inv_count = 1.0 / count;
     float a[VEC], b[VEC], c[VEC];
@@ -589,7 +626,7 @@ bn_bwd_fused_kernel(const T* __restrict__ dy, const T* __restrict__ y, const T* 
         }
         if (threadIdx.x == 0) *parity_p = parity ^ 1;
     }
-    for (long long i = tid; i < 2 * (long long)NSETS * C; i += stride) other[i] = 0.0;
+    for (long long i = gtid; i < 2 * (long long)NSETS * C; i += gstride) other[i] = 0.0;
     // second pass in REVERSE order: the tail of the first pass is what the L2 still holds (tensors larger than the L2 would
     // otherwise be evicted just ahead of their re-use, front to back)
     const long long n_iter = (nvec - tid + U * stride - 1) / (U * stride);
@@ -649,7 +686,7 @@ bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, 
                        const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
                        const float* __restrict__ beta, double count, bf16* __restrict__ dx, bf16* __restrict__ dres,
                        float* __restrict__ dgamma, float* __restrict__ dbeta, int accumulate_params, long long nvec, int C, int relu,
-                       double* __restrict__ ws, int vpt) {
+                       double* __restrict__ ws, int vpt, int cvb) {
     constexpr int VEC = 8;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     cg::grid_group grid = cg::this_grid();
@@ -658,8 +695,13 @@ bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, 
     const int NT = need_y ? 3 : 2;
     int4* stash = (int4*)smem_raw;                                                      // [vpt][NT][BN_THREADS]
     float* sm = (float*)(smem_raw + (size_t)vpt * NT * BN_THREADS * sizeof(int4));      // block_channel_reduce scratch
-    const long long tid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
-    const long long stride = (long long)gridDim.x * BN_THREADS;
+    const long long gtid = blockIdx.x * (long long)BN_THREADS + threadIdx.x;
+    const long long gstride = (long long)gridDim.x * BN_THREADS;
+    const int P = C / VEC, cvgroups = P / cvb, rpb = BN_THREADS / cvb;
+    const int cvl = threadIdx.x % cvb, rl = threadIdx.x / cvb;
+    const int cv = (blockIdx.x % cvgroups) * cvb + cvl;
+    const long long stride = (long long)(gridDim.x / cvgroups) * rpb * P;
+    const long long tid = rl < rpb ? ((long long)(blockIdx.x / cvgroups) * rpb + rl) * P + cv : nvec;
     for (int u = 0; u < vpt; ++u) {
         const long long v = tid + u * stride;
         if (v < nvec) {
@@ -674,7 +716,7 @@ bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, 
     const int parity = *parity_p;
     double* accum = ws + (long long)parity * 2 * NSETS * C;
     double* other = ws + (long long)(parity ^ 1) * 2 * NSETS * C;
-    const int ch0 = (int)(((unsigned)tid * (unsigned)VEC) % (unsigned)C);
+    const int ch0 = cv * VEC;
     float mu[VEC], is[VEC], gs[VEC], bs[VEC], acc[2 * VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
@@ -710,7 +752,7 @@ bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, 
             }
         }
     }
-    block_channel_reduce<VEC, 2>(acc, ch0, C, accum + (long long)(blockIdx.x % NSETS) * 2 * C, sm);
+    block_slab_reduce<VEC, 2>(acc, cvb, C, (int)(blockIdx.x % cvgroups) * cvb * VEC, accum, sm);
     grid.sync();
     const double inv_count = 1.0 / count;
     float a[VEC], b[VEC], c[VEC];
@@ -726,8 +768,8 @@ bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, 
         b[j] = (float)(s1 * inv_count);
         c[j] = (float)(s2 * inv_count);
     }
-    if (tid < C) {  // one channel per thread over the first blocks
-        const int ch = (int)tid;
+    if (gtid < C) {  // one channel per thread over the first blocks
+        const int ch = (int)gtid;
         double s1 = 0.0, s2 = 0.0;
         for (int k = 0; k < NSETS; ++k) {
             s1 += accum[(long long)k * 2 * C + ch];
@@ -738,7 +780,7 @@ bn_bwd_resident_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ y, 
         if (dbeta) dbeta[ch] = accumulate_params ? dbeta[ch] + db : db;
         if (ch == 0) *parity_p = parity ^ 1;
     }
-    for (long long i = tid; i < 2 * (long long)NSETS * C; i += stride) other[i] = 0.0;
+    for (long long i = gtid; i < 2 * (long long)NSETS * C; i += gstride) other[i] = 0.0;
     for (int u = 0; u < vpt; ++u) {
         const long long v = tid + u * stride;
         if (v < nvec) {
@@ -864,6 +906,19 @@ int bn_coop_grid(K kernel, long long nvec, int C, int vec, size_t smem) {
     return (int)g;
 }
 
+// Largest cooperative grid of `kernel` that is co-resident next to the side-stream kernels: occupancy (at most two blocks per
+// SM) times the SMs left to the chain (DMP_BN_COOP_MAX_BLOCKS, see bn_coop_grid).  -1 if the kernel cannot run at all.
+template <typename K>
+long long bn_coop_cap(K kernel, size_t smem) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BN_THREADS, smem) != cudaSuccess || per_sm < 1) return -1;
+    if (per_sm > 2) per_sm = 2;
+    long long cap = (long long)dmp_num_sms() * per_sm;
+    static const int coop_cap = [] { const char* e = getenv("DMP_BN_COOP_MAX_BLOCKS"); return e ? atoi(e) : 2 * (dmp_num_sms() - dmp_num_sms() / 3); }();
+    if (coop_cap > 0 && cap > coop_cap) cap = coop_cap;
+    return cap;
+}
+
 int bn_grid(long long nvec, int C, int vec, int vecs_per_thread = 8) {
     // smallest multiple q of blocks such that (blocks * BN_THREADS * vec) % C == 0
     long long per_block = (long long)BN_THREADS * vec;
@@ -886,6 +941,22 @@ int bn_coop_sms() {  // SMs a cooperative BatchNorm grid is sized for (see DMP_B
     return (cap > 0 && cap / 2 < sms) ? (cap / 2 > 0 ? cap / 2 : 1) : sms;
 }
 
+// Grid of a slab-mapped cooperative kernel (block_slab_reduce): cvb = largest divisor of C / vec up to 8, C / vec / cvb slabs,
+// `rows_per_thread` rows per thread where the co-residency cap allows.  Returns the grid (a multiple of the slab count) or -1
+// when even one block per slab does not fit the cap.
+int bn_slab_grid(long long M, int C, int vec, long long cap_blocks, int rows_per_thread, int* cvb_out) {
+    const int P = C / vec;
+    int cvb = 8;
+    while (cvb > 1 && P % cvb != 0) --cvb;
+    const int cvgroups = P / cvb, rpb = BN_THREADS / cvb;
+    if (cvgroups > cap_blocks) return -1;
+    long long row_blocks = (M + (long long)rpb * rows_per_thread - 1) / ((long long)rpb * rows_per_thread);
+    if (row_blocks * cvgroups > cap_blocks) row_blocks = cap_blocks / cvgroups;
+    if (row_blocks < 1) row_blocks = 1;
+    *cvb_out = cvb;
+    return (int)(row_blocks * cvgroups);
+}
+
 int bn_bwd_try_resident(const void* dy, const void* y, const void* x, const float* mean, const float* invstd, const float* gamma,
                         const float* beta, double count, void* dx, void* dres, float* dgamma, float* dbeta, int accumulate_params,
                         long long nvec, int C, int relu, double* ws, cudaStream_t stream) {
@@ -896,13 +967,9 @@ int bn_bwd_try_resident(const void* dy, const void* y, const void* x, const floa
     // for few rows of many channels (2048 x 960).  Larger tensors keep the two-pass kernel.
     if (nvec * 16 > (3ll << 20)) return 1;
     const int NT = (relu && y != nullptr) ? 3 : 2;
-    const size_t scratch = (size_t)BN_THREADS * 2 * 8 * sizeof(float);
+    const size_t scratch = (size_t)BN_THREADS * (2 * 8 + 1) * sizeof(float);
     const size_t per_vec = (size_t)NT * BN_THREADS * sizeof(int4);
-    // alignment: the grid must be a multiple of q so that every thread keeps its channels across its vectors
-    long long per_block = (long long)BN_THREADS * 8;
-    long long a = C, b = per_block;
-    while (b) { long long t = a % b; a = b; b = t; }
-    const int q = (int)(C / a);
+    const long long M = nvec / (C / 8);
     const int sms = bn_coop_sms();
     static std::atomic<unsigned long long> configured{0};
     int dev = 0;
@@ -915,19 +982,12 @@ int bn_bwd_try_resident(const void* dy, const void* y, const void* x, const floa
     for (int per_sm = 2; per_sm >= 1; --per_sm) {
         const size_t budget = per_sm == 2 ? 100 * 1024 : 200 * 1024;
         const int vpt_max = (int)((budget - scratch) / per_vec);
-        long long cap = (long long)sms * per_sm;
-        long long g = (cap / q) * q;
-        if (g < q) continue;
-        // as few vectors per thread as the grid allows, but at least 4 (fewer, fatter blocks: each ends with 2*C atomics)
-        long long vpt = (nvec + g * BN_THREADS - 1) / (g * BN_THREADS);
+        int cvb = 1;
+        const int g = bn_slab_grid(M, C, 8, (long long)sms * per_sm, 4, &cvb);  // 4 rows per thread where the cap allows
+        if (g < 0) continue;
+        const int rpb = BN_THREADS / cvb, row_blocks = g / ((C / 8) / cvb);
+        const long long vpt = (M + (long long)row_blocks * rpb - 1) / ((long long)row_blocks * rpb);
         if (vpt > vpt_max) continue;
-        if (vpt < 4) {
-            long long want = (nvec + BN_THREADS * 4 - 1) / (BN_THREADS * 4);
-            g = (want / q) * q;
-            if (g < q) g = q;
-            vpt = (nvec + g * BN_THREADS - 1) / (g * BN_THREADS);
-            if (vpt > vpt_max) continue;
-        }
         const size_t smem = (size_t)vpt * per_vec + scratch;
         int occ = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, bn_bwd_resident_kernel, BN_THREADS, smem) != cudaSuccess || occ < 1) continue;
@@ -935,7 +995,7 @@ int bn_bwd_try_resident(const void* dy, const void* y, const void* x, const floa
         int vpt_i = (int)vpt;
         void* args[] = {(void*)&dy, (void*)&y, (void*)&x, (void*)&mean, (void*)&invstd, (void*)&gamma, (void*)&beta, (void*)&count,
                         (void*)&dx, (void*)&dres, (void*)&dgamma, (void*)&dbeta, (void*)&accumulate_params, (void*)&nvec, (void*)&C,
-                        (void*)&relu, (void*)&ws, (void*)&vpt_i};
+                        (void*)&relu, (void*)&ws, (void*)&vpt_i, (void*)&cvb};
         DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_resident_kernel, dim3((unsigned)g), dim3(BN_THREADS), args, smem, stream));
         return 0;
     }
@@ -1134,11 +1194,12 @@ DMP_API int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int d
     if (int rc = bn_check("dmp_bn_bwd_fused", M, C, dtype)) return rc;
     const int vec = dtype == 1 ? 8 : 4;
     long long nvec = M * C / vec;
-    size_t smem = (size_t)BN_THREADS * 2 * vec * sizeof(float);
+    size_t smem = (size_t)BN_THREADS * (2 * vec + 1) * sizeof(float);
     double count = (double)M;
+    int cvb = 1;
     void* args[] = {(void*)&dy, (void*)&y, (void*)&x, (void*)&mean, (void*)&invstd, (void*)&gamma, (void*)&beta, (void*)&count, (void*)&dx,
                     (void*)&dres, (void*)&dgamma, (void*)&dbeta, (void*)&accumulate_params, (void*)&nvec, (void*)&C, (void*)&relu,
-                    (void*)&ws};
+                    (void*)&ws, (void*)&cvb};
     if (dtype == 1) {
         if (int rc = bn_bwd_try_resident(dy, y, x, mean, invstd, gamma, beta, count, dx, dres, dgamma, dbeta, accumulate_params, nvec, C,
                                          relu, ws, stream)) {
@@ -1147,7 +1208,7 @@ DMP_API int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int d
             DMP_COUNT_LAUNCH(1);
             return 0;
         }
-        const int grid = bn_coop_grid(bn_bwd_fused_kernel<bf16>, nvec, C, vec, smem);
+        const int grid = bn_slab_grid(M, C, vec, bn_coop_cap(bn_bwd_fused_kernel<bf16>, smem), 8, &cvb);
         if (grid < 0) return 1;
         // the second pass walks backwards when dy + x exceed what the 126 MB L2 keeps of the first pass (DMP_BN_BWD_REVERSE_MB,
         // default 64; 0 = never)
@@ -1155,7 +1216,7 @@ DMP_API int dmp_bn_bwd_fused(const void* dy, const void* y, const void* x, int d
         if (rev_mb > 0 && nvec * 32 > (rev_mb << 20)) accumulate_params |= 2;
         DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_fused_kernel<bf16>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
     } else {
-        const int grid = bn_coop_grid(bn_bwd_fused_kernel<float>, nvec, C, vec, smem);
+        const int grid = bn_slab_grid(M, C, vec, bn_coop_cap(bn_bwd_fused_kernel<float>, smem), 8, &cvb);
         if (grid < 0) return 1;
         DMP_CHECK_CUDA(cudaLaunchCooperativeKernel((void*)bn_bwd_fused_kernel<float>, dim3(grid), dim3(BN_THREADS), args, smem, stream));
     }
