@@ -92,7 +92,7 @@ for mb in sizes:
     res["nccl_plus_sgd_s"] = timed(lambda: (dist.all_reduce(ref), lib.dmp_sgd_flat(master.data_ptr(), shadow.data_ptr(), ref.data_ptr(), 0, mom.data_ptr(), n, hp.data_ptr(), 0, 1, sp)), iters)
     f = 2.0 * (world - 1) / world
     for k in [k for k in res if k.endswith("_s")]:
-        res[k.replace("_s", "_busGBs")] = S / res[k] * f / 1e9
+        res[k[:-2] + "_busGBs"] = S / res[k] * f / 1e9
     if "oneshot_s" in res:
         res["oneshot_roofline_frac"] = ((world - 1) * S / LINK) / res["oneshot_s"]
     res["twoshot_roofline_frac"] = (2.0 * S * (world - 1) / world / LINK) / res["twoshot_s"]

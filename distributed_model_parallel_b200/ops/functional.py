@@ -224,6 +224,9 @@ def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
         if conv.stride == (2, 2) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and cout % 64 == 0:
             return "igemm"
     if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
+            and cin * kh * kw > 27 and _STEM_GEMM:
+        return "stem_gemm"  # large stems (7x7): im2col rows + tcgen05 GEMMs
+    if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
             and cin * kh * kw * cout * 4 <= 48 * 1024:
         return "stem"
     return "generic"
@@ -280,6 +283,28 @@ def _conv_fwd_cuda(x, w, conv, kind, stats=None):
                                   s, p, sp), "stem conv fwd")
         _note("conv_stem:direct")
         return y, x
+    if kind == "stem_gemm":
+        _, cin, H, W = x.shape
+        kh, kw = conv.kernel_size
+        s, p = conv.stride[0], conv.padding[0]
+        cout = conv.out_channels
+        Ho, Wo = (H + 2 * p - kh) // s + 1, (W + 2 * p - kw) // s + 1
+        if x.dtype == torch.float32 and x.is_contiguous():
+            layout = 0
+        else:
+            x = _as_cl_bf16(x)
+            layout = 1
+        T = cin * kh * kw
+        Kp = (T + 7) // 8 * 8
+        npix = N * Ho * Wo
+        cols = torch.empty((npix, Kp), device=x.device, dtype=torch.bfloat16)
+        _ck(lib.dmp_stem_im2col(x.data_ptr(), layout, cols.data_ptr(), N, cin, H, W, kh, kw, s, p, Kp, sp), "stem im2col")
+        wpad = torch.empty((cout, Kp), device=x.device, dtype=torch.bfloat16)
+        _ck(lib.dmp_pack_rows_bf16(w.data_ptr(), 0 if w.dtype == torch.float32 else 1, wpad.data_ptr(), cout, T, Kp, sp), "stem filter pack")
+        y = _cl_empty(N, cout, Ho, Wo, x.device)
+        _ck(lib.dmp_gemm_bf16(0, cols.data_ptr(), Kp, wpad.data_ptr(), Kp, y.data_ptr(), cout, npix, cout, T, None, 0, 1, sp), "stem gemm fwd")
+        _note("conv_stem:im2col+tcgen05")
+        return y, cols  # the weight gradient re-uses the patch rows
     if kind == "igemm":
         _, cin, H, W = x.shape
         kh, kw = conv.kernel_size
@@ -371,6 +396,22 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx, link_in=None):
                                         kh, kw, s, p, 1 if accumulate else 0, _sp()), "stem conv wgrad")
 
         return None, write_dw
+    if kind == "stem_gemm":
+        if need_dx:
+            raise RuntimeError("stem convolution does not provide an input gradient")
+        cols = x  # [pixels, Kp] patch rows saved by the forward
+        cout = conv.out_channels
+        T = conv.in_channels * conv.kernel_size[0] * conv.kernel_size[1]
+        npix, Kp = cols.shape
+        dy2 = dy if dy.is_contiguous(memory_format=torch.channels_last) else dy.contiguous(memory_format=torch.channels_last)
+
+        def write_dw(dst, accumulate):
+            if not accumulate:
+                dst.zero_()
+            _ck(lib.dmp_gemm_bf16(2, dy2.data_ptr(), cout, cols.data_ptr(), Kp, dst.data_ptr(), T, cout, T, npix, None, 2, 0, _sp()),
+                "stem gemm wgrad")
+
+        return None, write_dw
     if kind == "igemm":
         _, cin, H, W = x.shape
         kh, kw = conv.kernel_size
@@ -445,6 +486,8 @@ _FUSE_BN_BWD = os.environ.get("DMP_FUSE_BN_BWD", "0") == "1"
 # path of backward, every kernel of a batch-128 step is latency- rather than throughput-bound, and the weight gradient of a
 # layer depends on nothing that follows it -- so it overlaps with the next BatchNorm backward / data gradient.
 _WGRAD_SIDE = os.environ.get("DMP_WGRAD_SIDE_STREAM", "1") == "1"
+# Stems with more than 27 taps (ResNet's 7x7) run as im2col rows + tcgen05 GEMMs (DMP_STEM_GEMM=0: the per-tap kernels).
+_STEM_GEMM = os.environ.get("DMP_STEM_GEMM", "1") == "1"
 
 
 class _BnLink:
@@ -700,7 +743,7 @@ class _ConvBNAct(torch.autograd.Function):
         ctx.link_out, ctx.link_in = None, link_in
         if link_in is not None:
             link_in.consumers += 1
-        if kind != "stem":
+        if kind not in ("stem", "stem_gemm"):
             x = _as_cl_bf16(x)
         if kind == "pw" and conv.stride != (1, 1):
             conv._dmp_in_hw = (x.shape[2], x.shape[3])

@@ -188,6 +188,12 @@ int dmp_stem_conv_fwd(const void* x, int x_layout, const void* w, int w_dtype, v
                       int Cout, int KH, int KW, int stride, int pad, dmp_stream_t stream);
 int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, float* dw, int N, int Cin, int H, int W, int Cout,
                         int KH, int KW, int stride, int pad, int accumulate, dmp_stream_t stream);
+/* Large stems (7x7) as GEMMs on the tensor cores: bf16 im2col rows [pixel][Kp] (Kp % 8 == 0, zero beyond Cin*KH*KW) for
+ * dmp_gemm_bf16 (forward: layout 0 with the filter packed by dmp_pack_rows_bf16; weight gradient: layout 2, fp32 accumulate).
+ * Same op as dmp_stem_conv_*: R/data_parallel.py:58-73 lists ResNet, whose first layer is the 7x7 stride-2 convolution. */
+int dmp_stem_im2col(const void* x, int x_layout, void* cols, int N, int Cin, int H, int W, int KH, int KW, int stride, int pad,
+                    int Kp, dmp_stream_t stream);
+int dmp_pack_rows_bf16(const void* src, int src_dtype, void* dst, int rows, int cols, int dst_pitch, dmp_stream_t stream);
 int dmp_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int relu, dmp_stream_t stream);
 int dmp_avgpool_bwd(const void* dy, const void* x, void* dx, int N, int HW, int C, int relu, dmp_stream_t stream);
 int dmp_linear_small_fwd(const void* x, const void* w, int w_dtype, const float* bias, float* y, int B, int N, int K,

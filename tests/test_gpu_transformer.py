@@ -174,6 +174,8 @@ def test_dense_conv_paths_without_library_kernels(N, H, Cin, Cout, k, stride):
     OF.path_counts.clear()
     y = OF.conv_bn_act(xk if stem else xk.bfloat16().contiguous(memory_format=torch.channels_last), conv, None, relu=False)
     assert "conv_generic:cudnn" not in OF.path_counts, dict(OF.path_counts)
+    if stem and k == 7:  # large stems: im2col rows + tensor-core GEMMs, not the per-tap kernels
+        assert OF.path_counts.get("conv_stem:im2col+tcgen05"), dict(OF.path_counts)
     xr = x.bfloat16().float().requires_grad_(True) if not stem else x.clone().requires_grad_(True)
     wr = conv.weight.detach().bfloat16().float().requires_grad_(True) if not stem else conv.weight.detach().clone().requires_grad_(True)
     yr = F.conv2d(xr, wr, None, stride, k // 2)
