@@ -278,6 +278,27 @@ void dmp_reducer_unused_flags(void* h, int32_t* out);
  * ctypes structures in parallel/reducer.py).  dmp_reducer_grad_ready is the whole autograd hook: mark, decide, order the
  * communication stream, call the collective's entry point -- c10d's Reducer::autograd_hook -> mark_variable_ready ->
  * all_reduce_bucket, which the reference README dissects (/root/reference/Readme.md:145-157). */
+struct DmpLaunchFns { /* entry points of libdmp_b200.so (or stand-ins with the same signatures) */
+    int (*fork)(dmp_stream_t cur, dmp_stream_t comm, const dmp_stream_t* side, int n_side);
+    int (*join)(dmp_stream_t cur, dmp_stream_t comm);
+    int (*allreduce_fused)(int algo, int dtype, void* bufs, void* state, int rank, int world, long long n, float scale, void* out,
+                           void* master, void* momentum, void* shadow, void* hp, int nesterov, void* master_ptrs, void* shadow_ptrs,
+                           int zero_after, int max_blocks, dmp_stream_t stream);
+    int (*allreduce_nvls)(void* mc, void* state, int rank, int world, long long n, float scale, int max_blocks, dmp_stream_t stream);
+    int (*allreduce_nvls_sgd)(void* mc_grad, void* mc_master, void* mc_shadow, void* master, void* momentum, void* hp, int nesterov,
+                              void* state, int rank, int world, long long n, float scale, int max_blocks, dmp_stream_t stream);
+    int (*sgd_flat)(void* master, void* shadow, void* grad, int grad_dtype, void* momentum, long long n, void* hp, int nesterov,
+                    int zero_grad, dmp_stream_t stream);
+};
+struct DmpBucketPlan { /* kind: 0 caller launches, 1 peer all-reduce (+SGD), 2 switch-side all-reduce, 3 switch-side all-reduce + SGD in
+                          one kernel, 4 flat SGD only (one rank), 5 nothing, 6 switch-side all-reduce then flat SGD */
+    int kind, algo, dtype, rank, world, nesterov, zero_after, max_blocks;
+    long long numel;
+    float scale;
+    void *bufs, *state, *out, *master, *momentum, *shadow, *hp, *master_ptrs, *shadow_ptrs;
+    void *mc_grad, *mc_master, *mc_shadow;
+    void* grad;
+};
 int dmp_reducer_set_plans(void* h, const void* fns, const void* plans, int n_plans, dmp_stream_t comm, const dmp_stream_t* side,
                           int n_side);
 void dmp_reducer_clear_plans(void* h);
