@@ -34,26 +34,31 @@ _tls = threading.local()
 grad_ready_callbacks: list = []
 
 
-_force_reference = False
+_ref_lock = threading.Lock()
+_ref_depth = 0  # > 0 while some thread is inside use_reference_ops()
 
 
 class use_reference_ops:
-    """Context manager: run the plain PyTorch restatement even for CUDA tensors (numerics oracle / A-B timing)."""
+    """Context manager: run the plain PyTorch restatement even for CUDA tensors (numerics oracle / A-B timing).  The switch is
+    process-wide on purpose -- DataParallel's replica threads, started inside the context, must see it -- so it is a counter
+    under a lock rather than a saved-and-restored flag: contexts entered and left by different threads in any order cannot leave
+    it stuck on or off."""
 
     def __enter__(self):
-        global _force_reference
-        self._old = _force_reference
-        _force_reference = True
+        global _ref_depth
+        with _ref_lock:
+            _ref_depth += 1
         return self
 
     def __exit__(self, *exc):
-        global _force_reference
-        _force_reference = self._old
+        global _ref_depth
+        with _ref_lock:
+            _ref_depth -= 1
         return False
 
 
 def _use_kernels(x: torch.Tensor) -> bool:
-    return x.is_cuda and not _force_reference
+    return x.is_cuda and _ref_depth == 0
 
 
 def _note(key: str) -> None:
@@ -224,7 +229,7 @@ def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
         if conv.stride == (2, 2) and x.shape[2] % 2 == 0 and x.shape[3] % 2 == 0 and cout % 64 == 0:
             return "igemm"
     if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
-            and cin * kh * kw > 27 and _STEM_GEMM:
+            and cin * kh * kw >= _STEM_GEMM_MIN_TAPS and _STEM_GEMM:
         return "stem_gemm"  # large stems (7x7): im2col rows + tcgen05 GEMMs
     if g == 1 and cin <= 4 and cout % 8 == 0 and conv.stride[0] == conv.stride[1] and conv.padding[0] == conv.padding[1] \
             and cin * kh * kw * cout * 4 <= 48 * 1024:
@@ -488,6 +493,7 @@ _FUSE_BN_BWD = os.environ.get("DMP_FUSE_BN_BWD", "0") == "1"
 _WGRAD_SIDE = os.environ.get("DMP_WGRAD_SIDE_STREAM", "1") == "1"
 # Stems with more than 27 taps (ResNet's 7x7) run as im2col rows + tcgen05 GEMMs (DMP_STEM_GEMM=0: the per-tap kernels).
 _STEM_GEMM = os.environ.get("DMP_STEM_GEMM", "1") == "1"
+_STEM_GEMM_MIN_TAPS = int(os.environ.get("DMP_STEM_GEMM_MIN_TAPS", "28"))  # Cin*KH*KW from which a stem takes the GEMM path
 
 
 class _BnLink:

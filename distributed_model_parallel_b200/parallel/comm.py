@@ -18,6 +18,8 @@ from __future__ import annotations
 from collections import defaultdict
 from typing import Dict, Iterable, List, Optional, Sequence
 
+import threading
+
 import torch
 import torch.distributed as dist
 
@@ -105,7 +107,7 @@ def _all_cuda(devs) -> bool:
 
 
 _peer_enabled = set()
-_active_arena = None  # MulticastArena used by broadcast_coalesced while a DataParallel forward is replicating
+_arena_tls = threading.local()  # .arena: MulticastArena used by broadcast_coalesced while THIS thread's DataParallel forward replicates
 
 
 class use_multicast_arena:
@@ -115,16 +117,14 @@ class use_multicast_arena:
         self.arena = arena
 
     def __enter__(self):
-        global _active_arena
-        self._old = _active_arena
-        _active_arena = self.arena
+        self._old = getattr(_arena_tls, "arena", None)
+        _arena_tls.arena = self.arena
         if self.arena is not None:
             self.arena.reset()
         return self
 
     def __exit__(self, *exc):
-        global _active_arena
-        _active_arena = self._old
+        _arena_tls.arena = self._old
         return False
 
 
@@ -177,7 +177,7 @@ def _broadcast_coalesced_impl(tensors, devs, outputs, buffer_size):
             ev.record(torch.cuda.current_stream(d))
             src_stream.wait_event(ev)
         with torch.cuda.device(src_dev):
-            arena = _active_arena
+            arena = getattr(_arena_tls, "arena", None)
             if arena is not None and [d.index for d in devs] != arena.devices[: len(devs)]:
                 arena = None
             for chunk in chunks:

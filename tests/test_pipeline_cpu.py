@@ -163,3 +163,26 @@ def _w_reject(rank, world):
 
 def test_1f1b_with_loss_on_first_is_rejected():
     run_gloo(_w_reject, 2)
+
+
+def test_layer_costs_by_time_and_measured_boundaries_single_process():
+    """Per-layer timing leaves the network input without a gradient (stem convolutions provide none on the kernel path) and
+    restores BatchNorm buffers; measured_boundaries without a process group is the rank-0 measurement itself."""
+    import torch.nn as nn
+    from distributed_model_parallel_b200.parallel.pipeline import layer_costs, measured_boundaries
+
+    torch.manual_seed(0)
+    seq = nn.Sequential(nn.Conv2d(3, 8, 3, padding=1), nn.BatchNorm2d(8), nn.ReLU(), nn.Conv2d(8, 8, 3, padding=1), nn.Flatten(),
+                        nn.Linear(8 * 8 * 8, 4))
+    x = torch.randn(2, 3, 8, 8)
+    seen = []
+    seq[0].register_forward_hook(lambda m, inp, out: seen.append(inp[0].requires_grad))
+    costs = layer_costs(seq, "time", sample=x, repeats=1)
+    assert len(costs) == len(seq) and all(c > 0 for c in costs)
+    assert seen and not any(seen), "the network input must not require a gradient"
+    assert all(p.grad is None for p in seq.parameters())
+    before = [b.clone() for b in seq.buffers()]
+    bounds = measured_boundaries(seq, 2, x, torch.device("cpu"), rank=0, mode="time")
+    assert bounds[0] == 0 and bounds[-1] == len(seq) and len(bounds) == 3 and bounds[1] in range(1, len(seq))
+    for a, b in zip(before, seq.buffers()):
+        assert torch.equal(a, b), "train-mode timing passes leaked into BatchNorm statistics"
