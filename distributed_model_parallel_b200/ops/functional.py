@@ -493,7 +493,9 @@ _FUSE_BN_BWD = os.environ.get("DMP_FUSE_BN_BWD", "0") == "1"
 _WGRAD_SIDE = os.environ.get("DMP_WGRAD_SIDE_STREAM", "1") == "1"
 # Stems with more than 27 taps (ResNet's 7x7) run as im2col rows + tcgen05 GEMMs (DMP_STEM_GEMM=0: the per-tap kernels).
 _STEM_GEMM = os.environ.get("DMP_STEM_GEMM", "1") == "1"
-_STEM_GEMM_MIN_TAPS = int(os.environ.get("DMP_STEM_GEMM_MIN_TAPS", "28"))  # Cin*KH*KW from which a stem takes the GEMM path
+# Cin*KH*KW from which a stem takes the GEMM path: 27 = also the 3x3 RGB stems (MobileNetV2 step 3.33 -> 3.29 ms); the per-tap
+# kernels (fp32 input, no bf16 rounding of the image) remain for smaller stems and behind DMP_STEM_GEMM_MIN_TAPS=28.
+_STEM_GEMM_MIN_TAPS = int(os.environ.get("DMP_STEM_GEMM_MIN_TAPS", "27"))
 
 
 class _BnLink:

@@ -7,11 +7,10 @@ tail -3 gpurun_out/pytest_1gpu.log
 timeout 120 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?"; tail -1 gpurun_out/smoke.log | cut -c1-300
 timeout 200 python bench.py --steps 100 --warmup 10 > gpurun_out/bench_1gpu.json 2> gpurun_out/bench_1gpu.err; echo "bench rc=$?"
 timeout 200 python bench.py --steps 30 --warmup 5 --batch-per-gpu 512 > gpurun_out/bench_1gpu_b512.json 2>> gpurun_out/bench_1gpu.err
-timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref_1gpu.json 2> gpurun_out/bench_ref_1gpu.err; echo "ref rc=$?"
+[ -n "$SKIP_REF" ] || { timeout 300 python bench.py --impl reference --steps 20 --warmup 5 > gpurun_out/bench_ref_1gpu.json 2> gpurun_out/bench_ref_1gpu.err; echo "ref rc=$?"; }
 timeout 200 python bench.py --model resnet18 --steps 30 --warmup 5 > gpurun_out/bench_resnet18_1gpu.json 2>> gpurun_out/bench_1gpu.err
 timeout 300 python bench.py --model resnet50 --batch-per-gpu 64 --steps 10 --warmup 3 > gpurun_out/bench_resnet50_1gpu.json 2>> gpurun_out/bench_1gpu.err
-timeout 300 python bench/chain_bench.py > gpurun_out/chain_b128_final.txt 2>&1
-timeout 400 python bench/batch_size_sweep.py --samples 32768 --out gpurun_out/batch_size_sweep.json > gpurun_out/batch_size_sweep.txt 2>&1; echo "sweep rc=$?"
+[ -n "$WITH_SWEEPS" ] && { timeout 300 python bench/chain_bench.py > gpurun_out/chain_b128_final.txt 2>&1; timeout 400 python bench/batch_size_sweep.py --samples 32768 --out gpurun_out/batch_size_sweep.json > gpurun_out/batch_size_sweep.txt 2>&1; echo "sweep rc=$?"; }
 python - <<'PY'
 import json, glob
 for f in sorted(glob.glob("gpurun_out/bench_*1gpu*.json")):
@@ -21,4 +20,4 @@ for f in sorted(glob.glob("gpurun_out/bench_*1gpu*.json")):
     except Exception as e:
         print(f, "ERR", e)
 PY
-tail -14 gpurun_out/batch_size_sweep.txt
+if [ -n "$WITH_SWEEPS" ]; then tail -14 gpurun_out/batch_size_sweep.txt; fi
