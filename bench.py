@@ -371,6 +371,19 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def bubble_report(kind, stages, microbatches):
+    """Idle fraction of the schedule from the native event simulator (equal stages, backward = 2x forward): what the pipeline
+    loses to fill and drain even with perfectly balanced stages and free communication -- the floor the measured step sits on."""
+    from distributed_model_parallel_b200.parallel.pipeline import simulate_schedule
+
+    try:
+        makespan, peak = simulate_schedule(kind, stages, microbatches, 1.0, 2.0)
+        busy = microbatches * 3.0
+        return {"schedule": kind, "ideal_bubble_fraction": 1.0 - busy / makespan, "peak_in_flight_per_stage": peak}
+    except Exception as e:  # noqa: BLE001
+        return {"error": repr(e)[:200]}
+
+
 # ---------------------------------------------------------------------------------------------------------
 def run_ours_mp(args):
     """Layer-split pipeline (one stage per GPU) with micro-batches: strong scaling, global batch 512 like the reference's
@@ -450,6 +463,7 @@ def run_ours_mp(args):
                     "h2d_bytes_per_step": gb * (4 * shape[0] * shape[1] * shape[2] + 8), "d2h_bytes_per_step": 4,
                     "note": "the timed loop copies each batch from pinned host memory and reads the loss back: it is the end-to-end number"},
             "gpu_launches": int(launches), "graph_replays_rank0": stage.stats["graph_replays"], "final_loss": float(lv[0]),
+            "bubble": bubble_report(args.schedule if args.microbatches > 1 else "naive", world, max(1, args.microbatches)),
         }))
     if world > 1:
         dist.destroy_process_group()
