@@ -91,6 +91,7 @@ _KERNEL_SIGS = {
     "dmp_stem_conv_wgrad": (i32, [vp, vp, i32, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "dmp_stem_im2col": (i32, [vp, i32, vp, i32, i32, i32, i32, i32, i32, i32, i32, i32, vp]),
     "dmp_pack_rows_bf16": (i32, [vp, i32, vp, i32, i32, i32, vp]),
+    "dmp_pack_filter": (i32, [vp, i32, vp, i32, i32, i32, i32, i32, vp]),
     "dmp_avgpool_fwd": (i32, [vp, vp, i32, i32, i32, i32, vp]),
     "dmp_avgpool_bwd": (i32, [vp, vp, vp, i32, i32, i32, i32, vp]),
     "dmp_linear_small_fwd": (i32, [vp, vp, i32, vp, vp, i32, i32, i32, vp]),

@@ -237,6 +237,21 @@ def conv_kind(conv: nn.Conv2d, x: torch.Tensor) -> str:
     return "generic"
 
 
+def _pack_filter(w, cout, cin, kh, kw, mode):
+    """bf16 operand of the implicit-GEMM kernels from the [Cout][Cin][KH][KW] parameter (its bf16 shadow when the optimizer keeps
+    one), in one launch: mode 0 [Cout][kh][kw][Cin]; 1 [Cin][kh][kw][Cout]; 2 the same with flipped taps."""
+    src = getattr(w, "_dmp_shadow", None)
+    if src is None:
+        src = w.detach()
+    if not src.is_contiguous():
+        src = src.contiguous()
+    rows = cout if mode == 0 else cin
+    out = torch.empty((rows, kh * kw * (cin if mode == 0 else cout)), device=w.device, dtype=torch.bfloat16)
+    _ck(_k().dmp_pack_filter(src.data_ptr(), 1 if src.dtype == torch.bfloat16 else 0, out.data_ptr(), cout, cin, kh, kw, mode, _sp()),
+        "filter pack")
+    return out
+
+
 def _conv_fwd_cuda(x, w, conv, kind, stats=None):
     """``stats``: optional {double[2C]; ticket} buffer -- the producer then also accumulates the BatchNorm batch sums of its
     output (only the "pw" and "dw" kinds have such an epilogue)."""
@@ -314,7 +329,7 @@ def _conv_fwd_cuda(x, w, conv, kind, stats=None):
         _, cin, H, W = x.shape
         kh, kw = conv.kernel_size
         cout = conv.out_channels
-        wp = weight_bf16(w).permute(0, 2, 3, 1).reshape(cout, kh * kw * cin).contiguous()  # [Cout][kh][kw][Cin]
+        wp = _pack_filter(w, cout, cin, kh, kw, 0)  # [Cout][kh][kw][Cin]
         st, pd = conv.stride[0], conv.padding[0]
         y = _cl_empty(N, cout, (H + 2 * pd - kh) // st + 1, (W + 2 * pd - kw) // st + 1, x.device)
         _ck(lib.dmp_conv_igemm_fwd_strided(x.data_ptr(), wp.data_ptr(), None, y.data_ptr(), N, H, W, cin, cout, kh, kw, pd, st, sp),
@@ -425,13 +440,13 @@ def _conv_bwd_cuda(dy, x, w, conv, kind, need_dx, link_in=None):
         if need_dx:
             if st == 2:
                 # four output-parity implicit GEMMs over dy, each with the taps that reach that parity (no inserted zeros)
-                wd = weight_bf16(w).permute(1, 2, 3, 0).reshape(cin, kh * kw * cout).contiguous()
+                wd = _pack_filter(w, cout, cin, kh, kw, 1)
                 dx = _cl_empty(N, cin, H, W, x.device)
                 _ck(lib.dmp_conv_igemm_dgrad_s2(dy.data_ptr(), wd.data_ptr(), dx.data_ptr(), N, H, W, cin, cout, kh, kw,
                                                 conv.padding[0], sp), "conv igemm dgrad (stride 2)")
             elif cout % 64 == 0:
                 # dx = conv(dy, flipped filter with in/out channels swapped): the same implicit-GEMM kernel
-                wd = weight_bf16(w).permute(1, 2, 3, 0).flip(1, 2).reshape(cin, kh * kw * cout).contiguous()
+                wd = _pack_filter(w, cout, cin, kh, kw, 2)
                 dx = _cl_empty(N, cin, H, W, x.device)
                 _ck(lib.dmp_conv_igemm_fwd(dy.data_ptr(), wd.data_ptr(), None, dx.data_ptr(), N, H, W, cout, cin, kh, kw,
                                            conv.padding[0], sp), "conv igemm dgrad")

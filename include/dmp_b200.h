@@ -194,6 +194,10 @@ int dmp_stem_conv_wgrad(const void* dy, const void* x, int x_layout, float* dw, 
 int dmp_stem_im2col(const void* x, int x_layout, void* cols, int N, int Cin, int H, int W, int KH, int KW, int stride, int pad,
                     int Kp, dmp_stream_t stream);
 int dmp_pack_rows_bf16(const void* src, int src_dtype, void* dst, int rows, int cols, int dst_pitch, dmp_stream_t stream);
+/* w[Cout][Cin][KH][KW] (fp32 0 / bf16 1) -> bf16 operand of the implicit-GEMM convolutions: mode 0 [Cout][KH][KW][Cin],
+ * 1 [Cin][KH][KW][Cout], 2 [Cin][flipped KH][flipped KW][Cout] (data gradients).  The dense 3x3 convolutions of the ResNet / VGG
+ * models the reference lists (R/data_parallel.py:58-73). */
+int dmp_pack_filter(const void* w, int w_dtype, void* out, int Cout, int Cin, int KH, int KW, int mode, dmp_stream_t stream);
 int dmp_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int relu, dmp_stream_t stream);
 int dmp_avgpool_bwd(const void* dy, const void* x, void* dx, int N, int HW, int C, int relu, dmp_stream_t stream);
 int dmp_linear_small_fwd(const void* x, const void* w, int w_dtype, const float* bias, float* y, int B, int N, int K,
