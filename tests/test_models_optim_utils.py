@@ -169,7 +169,9 @@ def test_ops_reference_path_and_cross_entropy_stats():
     assert torch.allclose(loss, F.cross_entropy(logits, t)) and stats[1].item() == (logits.argmax(1) == t).sum().item()
     assert OF.conv_kind(nn.Conv2d(16, 32, 1, bias=False), x) == "pw"
     assert OF.conv_kind(nn.Conv2d(16, 16, 3, padding=1, groups=16, bias=False), x) == "dw"
-    assert OF.conv_kind(nn.Conv2d(3, 32, 3, padding=1, bias=False), x) == "stem"
+    assert OF.conv_kind(nn.Conv2d(3, 32, 3, padding=1, bias=False), x) == "stem_gemm"      # 27 taps: im2col rows + tcgen05 GEMMs
+    assert OF.conv_kind(nn.Conv2d(3, 64, 7, stride=2, padding=3, bias=False), x) == "stem_gemm"
+    assert OF.conv_kind(nn.Conv2d(1, 32, 3, padding=1, bias=False), x) == "stem"           # 9 taps: the per-tap kernels
     assert OF.conv_kind(nn.Conv2d(64, 64, 3, padding=1, bias=False), x) == "igemm"
     assert OF.conv_kind(nn.Conv2d(48, 64, 3, padding=1, bias=False), x) == "generic"
 
