@@ -186,3 +186,18 @@ def test_layer_costs_by_time_and_measured_boundaries_single_process():
     assert bounds[0] == 0 and bounds[-1] == len(seq) and len(bounds) == 3 and bounds[1] in range(1, len(seq))
     for a, b in zip(before, seq.buffers()):
         assert torch.equal(a, b), "train-mode timing passes leaked into BatchNorm statistics"
+
+
+def test_bench_bubble_report_matches_the_schedule_simulator():
+    """bench.py's pipeline line carries the schedule's ideal idle fraction (equal stages, backward = 2 x forward)."""
+    import importlib.util
+    import os
+
+    spec = importlib.util.spec_from_file_location("dmp_bench", os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    assert abs(bench.bubble_report("naive", 4, 1)["ideal_bubble_fraction"] - 0.75) < 1e-9        # one stage busy at a time
+    r4, r8 = bench.bubble_report("1f1b", 4, 4), bench.bubble_report("1f1b", 4, 8)
+    assert abs(r4["ideal_bubble_fraction"] - (1 - 12.0 / 21.0)) < 1e-9 and r4["peak_in_flight_per_stage"] == [4, 3, 2, 1]
+    assert r8["ideal_bubble_fraction"] < r4["ideal_bubble_fraction"]
+    assert bench.bubble_report("gpipe", 4, 8)["peak_in_flight_per_stage"] == [8, 8, 8, 8]     # GPipe holds every micro-batch
